@@ -1,0 +1,82 @@
+// device_types.cuh -- device-side views of the topology tables, the cutoffs and the output buffers.
+// Built with -fmad=false: every float multiply/add below rounds separately, which is what the
+// float32 recipes of SURVEY.md Appendix A (VMD's measure contacts / hbonds / bond) require.
+// Fused multiply-adds are used only where written explicitly (__fmaf_rn) for conservative prefilters.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/chacra_b200.h"
+
+// bits of the per-pair-atom info word (mirror of chacra_b200/topology.py INFO_*)
+#define I_ELEM   0xFu
+#define I_S1     (1u << 4)
+#define I_S2     (1u << 5)
+#define I_HBU    (1u << 6)
+#define I_HASH   (1u << 7)
+#define I_ANION  (1u << 8)
+#define I_CATION (1u << 9)
+#define I_HP1    (1u << 10)   // static: base carbon in sele1; in shared memory: member of H1 for this fragment
+#define I_HP2    (1u << 11)   // static: base carbon in sele2; in shared memory: member of H2 for this fragment
+#define I_LIG    (1u << 12)
+#define I_BB     (1u << 13)
+#define I_CYS    (1u << 14)
+#define I_XBOND  (1u << 15)
+#define I_VDW    (1u << 16)
+#define I_PIDX_SHIFT 17        // the sorted copy keeps the pair index in the bits above the flags
+#define MAX_PAIR_SMALL (1 << 15)
+
+// pair classes handed from the exact-distance stage to the emit stage
+#define C_VDW   1u
+#define C_HP    2u
+#define C_SB    4u
+#define C_HB    8u
+#define C_NEARV 16u   // within near_dist_tol of the vdW cutoff
+#define C_NEARH 32u   // ... of the hydrophobic (same) cutoff
+
+struct DevTopo {
+    int n_atoms, n_pair, n_aux, n_h, n_rings, n_cat, n_dis, K, R, n_hp_base, same;
+    const int* pair_atom; const unsigned* pair_info; const int* pair_lkey; const int* pair_res; const int* pair_resid;
+    const int* pair_h_start; const int* pair_bond_start; const int* pair_bond_adj;
+    const int* aux_atom;
+    const int* ring_aux; const int* ring_pc_aux; const int* ring_sel_aux; const unsigned char* ring_sel_flags;
+    const int* ring_atoms; const int* ring_res; const int* ring_rep; const int* ring_rep_aux;
+    const int* cat_aux; const int* cat_atom; const unsigned char* cat_flags; const int* cat_res; const int* cat_excl;
+    const int* disulfide;
+    const float* tv;       // [K][K] min(vdw_d2max, soft^2)
+    const float* th;       // [K][K] min(vdw_d2max, hp^2)
+    const double* vcut;    // [K][K]
+    const int* hp_base; const unsigned char* atom_class;
+};
+
+struct DevParams {
+    unsigned itypes;
+    int vdw_rd, hb_rd;
+    int emit, track_near;
+    float cell;            // cell edge (>= every pair cutoff, padded)
+    float pre2;            // padded cmax^2 for the fused prefilter
+    float sb2, hb2, hp2, soft2;   // float32(c)*float32(c)
+    float hb_angle;        // float32 cutoff of measure hbonds
+    float ring_pre2;       // conservative centroid prefilter for pc/ps/ts
+    float ps_soft2, ts_soft2, pc_soft2;
+    double pc_dist, pc_angle, ps_dist, ps_angle, ps_psi, ts_dist, ts_angle, ts_psi;
+    double sb_dist, hb_dist, hp_dist, soft;
+    double near_d, near_a;
+};
+
+struct DevOut {
+    int* counts;                 // [P] of the state being processed
+    long long n_pairs;
+    chc_contact* contacts; unsigned long long* contact_n; long long contact_cap;
+    chc_near* near; unsigned long long* near_n; long long near_cap;
+};
+
+__device__ __forceinline__ float dist2_exact(float ax, float ay, float az, float bx, float by, float bz) {
+    // (dx*dx + dy*dy) + dz*dz, each operation rounded to binary32 (no contraction: -fmad=false)
+    float dx = ax - bx, dy = ay - by, dz = az - bz;
+    return (dx * dx + dy * dy) + dz * dz;
+}
+
+__device__ __forceinline__ long long pair_index(int ra, int rb, int R) {
+    int lo = min(ra, rb), hi = max(ra, rb);
+    return (long long)lo * R - ((long long)lo * (lo - 1)) / 2 + (hi - lo);
+}

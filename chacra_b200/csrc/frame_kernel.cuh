@@ -1,0 +1,107 @@
+// frame_kernel.cuh -- one CTA per frame: cell list in shared memory + every interaction type.
+//
+// Phases per frame (persistent CTA, frames strided over the grid):
+//   A  bounding box of the pair atoms                      (coordinates from HBM / staging buffer)
+//   B  cell of every pair atom, per-cell counts            (shared-memory atomics = counting sort, pass 1)
+//   C  exclusive scan of the cell counts                   (block scan)
+//   D  scatter into the sorted float4 array, copy aux atoms (counting sort, pass 2), clear the bitset
+//   R  ring interactions pc / ps / ts                      (float prefilter, float64 geometry)
+//   E1 half-shell neighbour enumeration, thread per atom   (fused-multiply prefilter, survivors -> warp queue)
+//   E2 exact float32 d2 + class tests, one survivor per lane
+//   E3 bonded / disulfide / hydrogen-angle tests, residue-pair dedup (bitset), counts, records
+// Reference semantics: SURVEY.md Appendix A / D; file:line citations are in include/chacra_b200.h.
+#pragma once
+#include "device_types.cuh"
+
+#define Q1_CAP 192
+#define Q2_CAP 64
+#define FULL 0xffffffffu
+
+struct SmemLayout {
+    int off_spos, off_slk, off_tmp, off_aux, off_cells, off_bits, off_q1, off_q2, off_tv, off_th, off_misc;
+    int max_cells;       // capacity of the cell array (entries), <= 16384
+    int bits_words;      // words of the residue-pair bitset
+    int bits_in_smem;
+    int total;
+};
+
+struct FrameMisc {
+    int bb_min[3], bb_max[3];
+    int chunk;            // dynamic work counter of the pair phase
+    int ring_task;
+    int scan_carry[33];
+};
+
+__device__ __forceinline__ int f2ord(float f) { int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7fffffff; }
+__device__ __forceinline__ float ord2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
+
+// ---- output helpers ---------------------------------------------------------------------------
+__device__ __forceinline__ void emit_contact(const DevOut& O, int frame, int itype, int a1, int a2, float dist) {
+    unsigned m = __activemask();
+    int lane = threadIdx.x & 31;
+    int leader = __ffs(m) - 1;
+    unsigned long long base = 0;
+    if (lane == leader) base = atomicAdd(O.contact_n, (unsigned long long)__popc(m));
+    base = __shfl_sync(m, base, leader);
+    unsigned long long pos = base + __popc(m & ((1u << lane) - 1));
+    if (pos < (unsigned long long)O.contact_cap) {
+        int4* dst = reinterpret_cast<int4*>(O.contacts + pos);
+        dst[0] = make_int4(frame, itype, a1, a2);
+        dst[1] = make_int4(-1, -1, __float_as_int(dist), 0);
+    }
+}
+
+__device__ __forceinline__ void emit_near(const DevOut& O, int frame, int kind, int a1, int a2, double delta) {
+    unsigned long long pos = atomicAdd(O.near_n, 1ull);
+    if (pos < (unsigned long long)O.near_cap) {
+        chc_near r; r.frame = frame; r.kind = kind; r.atom1 = a1; r.atom2 = a2; r.delta = delta; r.reserved = 0;
+        O.near[pos] = r;
+    }
+}
+
+// set the (ra, rb) bit of this frame's residue-pair set; first setter bumps the frequency count
+__device__ __forceinline__ void count_pair(const DevOut& O, unsigned* bits, int ra, int rb, int R) {
+    long long idx = pair_index(ra, rb, R);
+    unsigned bit = 1u << (idx & 31);
+    unsigned old = atomicOr(&bits[idx >> 5], bit);
+    if (!(old & bit)) atomicAdd(&O.counts[idx], 1);
+}
+
+__device__ __forceinline__ bool is_bonded(const DevTopo& T, int pi, int atom_j) {
+    int b = T.pair_bond_start[pi], e = T.pair_bond_start[pi + 1];
+    for (int k = b; k < e; ++k) if (T.pair_bond_adj[k] == atom_j) return true;
+    return false;
+}
+
+__device__ __forceinline__ bool is_disulfide(const DevTopo& T, int resid_i, int resid_j) {
+    for (int k = 0; k < T.n_dis; ++k) {
+        int a = T.disulfide[2 * k], b = T.disulfide[2 * k + 1];
+        if ((a == resid_i && b == resid_j) || (a == resid_j && b == resid_i)) return true;
+    }
+    return false;
+}
+
+// measure hbonds angle: 57.2958f * (float)atan2(|u x v|, u.v), u = h-d, v = a-h, float32 products
+__device__ __forceinline__ float hbond_angle(float dx, float dy, float dz, float hx, float hy, float hz,
+                                             float ax, float ay, float az) {
+    float ux = hx - dx, uy = hy - dy, uz = hz - dz;
+    float vx = ax - hx, vy = ay - hy, vz = az - hz;
+    float cx = uy * vz - uz * vy, cy = uz * vx - ux * vz, cz = ux * vy - uy * vx;
+    float psin = sqrtf((cx * cx + cy * cy) + cz * cz);
+    float pcos = (ux * vx + uy * vy) + uz * vz;
+    return 57.2958f * (float)atan2((double)psin, (double)pcos);
+}
+
+// ---- float64 ring geometry (contact_utils.py:958-1061) ---------------------------------------------
+struct D3 { double x, y, z; };
+__device__ __forceinline__ D3 d3(const float* p) { return D3{(double)p[0], (double)p[1], (double)p[2]}; }
+__device__ __forceinline__ D3 sub3(D3 a, D3 b) { return D3{a.x - b.x, a.y - b.y, a.z - b.z}; }
+__device__ __forceinline__ double dot3(D3 a, D3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+__device__ __forceinline__ D3 cross3(D3 a, D3 b) { return D3{a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+__device__ __forceinline__ D3 centroid3(D3 a, D3 b, D3 c) { return D3{((a.x + b.x) + c.x) / 3.0, ((a.y + b.y) + c.y) / 3.0, ((a.z + b.z) + c.z) / 3.0}; }
+__device__ __forceinline__ D3 normal3(D3 p1, D3 p2, D3 p3) { return cross3(sub3(p3, p1), sub3(p2, p1)); }
+__device__ __forceinline__ double angle_deg(D3 a, D3 b) {
+    double c = dot3(a, b) / (sqrt(dot3(a, a)) * sqrt(dot3(b, b)));
+    return acos(c) * (180.0 / 3.14159265358979323846);
+}
+__device__ __forceinline__ double fold180(double t) { return fmin(fabs(t), fabs(t - 180.0)); }

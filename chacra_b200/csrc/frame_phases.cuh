@@ -1,0 +1,221 @@
+// frame_phases.cuh -- ring phase (pc / ps / ts) and the two dense survivor stages E2 / E3.
+#pragma once
+#include "frame_kernel.cuh"
+
+struct FrameCtx {            // per-CTA view of the current frame (all pointers are shared memory)
+    const float4* spos;      // sorted pair atoms: x, y, z, (info | pair_index << 17)
+    const int* slk;          // locality key, same order
+    const float* aux;        // [NA][3] donor hydrogens, ring atoms, cations
+    unsigned* bits;          // residue-pair set of this frame (shared or global)
+    const float* tv; const float* th;
+    int frame;               // frame id reported in records
+};
+
+// ---- R: pi-cation ----------------------------------------------------------------------------------
+__device__ __forceinline__ void ring_pc_task(const DevTopo& T, const DevParams& P, const DevOut& O, const FrameCtx& F,
+                                             int c, int r) {
+    const int* pa = T.ring_pc_aux + 3 * r;
+    if (pa[0] < 0 || T.cat_excl[c] == r) return;     // bonded pairs never pass measure contacts
+    const float* xc = F.aux + 3 * T.cat_aux[c];
+    const float* p1 = F.aux + 3 * pa[0]; const float* p2 = F.aux + 3 * pa[1]; const float* p3 = F.aux + 3 * pa[2];
+    // conservative float prefilter on the centroid distance
+    float cx = (p1[0] + p2[0] + p3[0]) * (1.0f / 3.0f), cy = (p1[1] + p2[1] + p3[1]) * (1.0f / 3.0f),
+          cz = (p1[2] + p2[2] + p3[2]) * (1.0f / 3.0f);
+    float dx = xc[0] - cx, dy = xc[1] - cy, dz = xc[2] - cz;
+    if (dx * dx + dy * dy + dz * dz > P.ring_pre2) return;
+    // measure contacts 10.0: every ring atom must be selected against the cation, within the soft cutoff, unbonded
+    unsigned cf = T.cat_flags[c];
+    int catom = T.cat_atom[c];
+    for (int k = 0; k < 3; ++k) {
+        // ring_pc_aux is a permutation of ring_sel_aux; find the matching selection flags / atom index
+        int slot = pa[k], q = 0;
+        while (q < 2 && T.ring_sel_aux[3 * r + q] != slot) ++q;
+        unsigned rf = T.ring_sel_flags[3 * r + q];
+        int ratom = T.ring_atoms[3 * r + q];
+        bool dir = ((cf & 1u) && (rf & 2u)) || (!T.same && (cf & 2u) && (rf & 1u));
+        if (!dir || ratom == catom) return;
+        const float* pr = F.aux + 3 * slot;
+        if (dist2_exact(xc[0], xc[1], xc[2], pr[0], pr[1], pr[2]) > P.pc_soft2) return;
+    }
+    D3 a = d3(p1), b = d3(p2), cc = d3(p3), x = d3(xc);
+    D3 cen = centroid3(a, b, cc);
+    D3 v = sub3(x, cen);
+    double d = sqrt(dot3(v, v));
+    int rep = T.ring_rep[r];
+    if (P.track_near && fabs(d - P.pc_dist) < P.near_d) emit_near(O, F.frame, CHC_NEAR_PC_DIST, catom, rep, d - P.pc_dist);
+    if (d > P.pc_dist) return;
+    double t = fold180(angle_deg(normal3(a, b, cc), v));
+    if (P.track_near && fabs(t - P.pc_angle) < P.near_a) emit_near(O, F.frame, CHC_NEAR_PC_ANGLE, catom, rep, t - P.pc_angle);
+    if (t > P.pc_angle) return;
+    count_pair(O, F.bits, T.cat_res[c], T.ring_res[r], T.R);
+    if (P.emit) {
+        const float* pr = F.aux + 3 * T.ring_rep_aux[r];
+        emit_contact(O, F.frame, CHC_PC, catom, rep, sqrtf(dist2_exact(xc[0], xc[1], xc[2], pr[0], pr[1], pr[2])));
+    }
+}
+
+// ---- R: pi-stacking and T-stacking ---------------------------------------------------------------------
+__device__ __forceinline__ void ring_stack_task(const DevTopo& T, const DevParams& P, const DevOut& O, const FrameCtx& F,
+                                                int r1, int r2) {
+    if (T.ring_res[r1] == T.ring_res[r2]) return;
+    const int* t1 = T.ring_aux + 3 * r1; const int* t2 = T.ring_aux + 3 * r2;
+    // soft-cutoff stage on the selected ring atoms: which of the two searches finds this residue pair?
+    bool hit_ps = false, hit_ts = false;
+    float best = 3.0e38f;
+    for (int i = 0; i < 3; ++i) {
+        int si = T.ring_sel_aux[3 * r1 + i];
+        if (si < 0) continue;
+        unsigned fi = T.ring_sel_flags[3 * r1 + i];
+        const float* pi = F.aux + 3 * si;
+        for (int j = 0; j < 3; ++j) {
+            int sj = T.ring_sel_aux[3 * r2 + j];
+            if (sj < 0) continue;
+            unsigned fj = T.ring_sel_flags[3 * r2 + j];
+            if (!(((fi & 1u) && (fj & 2u)) || ((fi & 2u) && (fj & 1u)))) continue;
+            const float* pj = F.aux + 3 * sj;
+            best = fminf(best, dist2_exact(pi[0], pi[1], pi[2], pj[0], pj[1], pj[2]));
+        }
+    }
+    hit_ps = (P.itypes & CHC_IT_PS) && best <= P.ps_soft2;
+    hit_ts = (P.itypes & CHC_IT_TS) && best <= P.ts_soft2;
+    if (!(hit_ps || hit_ts) || t1[0] < 0 || t2[0] < 0) return;
+    D3 a1 = d3(F.aux + 3 * t1[0]), a2 = d3(F.aux + 3 * t1[1]), a3 = d3(F.aux + 3 * t1[2]);
+    D3 b1 = d3(F.aux + 3 * t2[0]), b2 = d3(F.aux + 3 * t2[1]), b3 = d3(F.aux + 3 * t2[2]);
+    D3 c1 = centroid3(a1, a2, a3), c2 = centroid3(b1, b2, b3);
+    D3 cc = sub3(c1, c2);
+    double d = sqrt(dot3(cc, cc));
+    int rep1 = T.ring_rep[r1], rep2 = T.ring_rep[r2];
+    D3 n1 = normal3(a1, a2, a3), n2 = normal3(b1, b2, b3);
+    double ang = 0.0, psi = 0.0;
+    bool have_ang = false;
+    for (int which = 0; which < 2; ++which) {
+        bool on = which == 0 ? hit_ps : hit_ts;
+        if (!on) continue;
+        double dcut = which == 0 ? P.ps_dist : P.ts_dist, acut = which == 0 ? P.ps_angle : P.ts_angle,
+               pcut = which == 0 ? P.ps_psi : P.ts_psi;
+        if (P.track_near && fabs(d - dcut) < P.near_d)
+            emit_near(O, F.frame, which == 0 ? CHC_NEAR_PS_DIST : CHC_NEAR_TS_DIST, rep1, rep2, d - dcut);
+        if (d > dcut) continue;
+        if (!have_ang) {
+            ang = angle_deg(n1, n2);
+            psi = fmin(fold180(angle_deg(n1, cc)), fold180(angle_deg(n2, D3{-cc.x, -cc.y, -cc.z})));
+            have_ang = true;
+        }
+        double v = which == 0 ? fold180(ang) : fabs(ang - 90.0);
+        if (P.track_near && fabs(v - acut) < P.near_a)
+            emit_near(O, F.frame, which == 0 ? CHC_NEAR_PS_ANGLE : CHC_NEAR_TS_ANGLE, rep1, rep2, v - acut);
+        if (v > acut) continue;
+        if (P.track_near && fabs(psi - pcut) < P.near_a)
+            emit_near(O, F.frame, which == 0 ? CHC_NEAR_PS_PSI : CHC_NEAR_TS_PSI, rep1, rep2, psi - pcut);
+        if (psi > pcut) continue;
+        count_pair(O, F.bits, T.ring_res[r1], T.ring_res[r2], T.R);
+        if (P.emit) {
+            const float* q1 = F.aux + 3 * T.ring_rep_aux[r1]; const float* q2 = F.aux + 3 * T.ring_rep_aux[r2];
+            emit_contact(O, F.frame, which == 0 ? CHC_PS : CHC_TS, rep1, rep2,
+                         sqrtf(dist2_exact(q1[0], q1[1], q1[2], q2[0], q2[1], q2[2])));
+        }
+    }
+}
+
+// ---- E2: exact float32 d2 and class tests for one prefilter survivor ---------------------------------------
+__device__ __forceinline__ unsigned e2_classify(const DevTopo& T, const DevParams& P, const FrameCtx& F, int i, int j,
+                                                float& d2_out) {
+    float4 a = F.spos[i], b = F.spos[j];
+    float d2 = dist2_exact(a.x, a.y, a.z, b.x, b.y, b.z);
+    d2_out = d2;
+    unsigned wi = __float_as_uint(a.w), wj = __float_as_uint(b.w);
+    bool dual = ((wi & I_S1) && (wj & I_S2)) || ((wi & I_S2) && (wj & I_S1));
+    if (!dual) return 0u;
+    int dl = abs(F.slk[i] - F.slk[j]);
+    int e = (wi & I_ELEM) * T.K + (wj & I_ELEM);
+    unsigned cls = 0;
+    if (dl >= P.vdw_rd) {
+        if ((P.itypes & CHC_IT_VDW) && (wi & wj & I_VDW)) {
+            if (d2 <= F.tv[e]) cls |= C_VDW;
+            if (P.track_near && d2 <= P.soft2 && fabs((double)sqrtf(d2) - T.vcut[e]) < P.near_d) cls |= C_NEARV;
+        }
+        if (P.itypes & CHC_IT_HP) {
+            bool hp = T.same ? ((wi & wj & I_HP1) != 0)
+                             : (((wi & I_HP1) && (wj & I_HP2)) || ((wj & I_HP1) && (wi & I_HP2)));
+            if (hp) {
+                if (d2 <= F.th[e]) cls |= C_HP;
+                if (P.track_near && d2 <= P.hp2 && fabs((double)sqrtf(d2) - T.vcut[e]) < P.near_d) cls |= C_NEARH;
+            }
+        }
+    }
+    if ((P.itypes & CHC_IT_SB) && d2 <= P.sb2 &&
+        (((wi & I_ANION) && (wj & I_CATION)) || ((wj & I_ANION) && (wi & I_CATION)))) cls |= C_SB;
+    if ((P.itypes & CHC_IT_HB) && d2 <= P.hb2 && (wi & wj & I_HBU) && ((wi | wj) & I_HASH) && dl >= P.hb_rd) cls |= C_HB;
+    return cls;
+}
+
+// does donor (sorted slot sd) see acceptor (sorted slot sa) under the angle rule, for any of its hydrogens?
+__device__ __forceinline__ bool hb_direction(const DevTopo& T, const DevParams& P, const DevOut& O, const FrameCtx& F,
+                                             float4 d, float4 a, int pd, int atom_d, int atom_a) {
+    bool ok = false;
+    int hb = T.pair_h_start[pd], he = T.pair_h_start[pd + 1];
+    for (int h = hb; h < he; ++h) {
+        const float* ph = F.aux + 3 * h;
+        float ang = hbond_angle(d.x, d.y, d.z, ph[0], ph[1], ph[2], a.x, a.y, a.z);
+        if (P.track_near && fabs((double)ang - (double)P.hb_angle) < P.near_a)
+            emit_near(O, F.frame, CHC_NEAR_HB_ANGLE, atom_d, atom_a, (double)ang - (double)P.hb_angle);
+        ok |= ang < P.hb_angle;
+    }
+    return ok;
+}
+
+// ---- E3: everything that needs the global tables, for one classified pair ---------------------------------------
+__device__ __forceinline__ void e3_finish(const DevTopo& T, const DevParams& P, const DevOut& O, const FrameCtx& F,
+                                          int i, int j, unsigned cls, float d2) {
+    float4 a = F.spos[i], b = F.spos[j];
+    unsigned wi = __float_as_uint(a.w), wj = __float_as_uint(b.w);
+    int pi = wi >> I_PIDX_SHIFT, pj = wj >> I_PIDX_SHIFT;
+    int ai = T.pair_atom[pi], aj = T.pair_atom[pj];
+    // directly bonded pairs are excluded by measure contacts / measure hbonds (Appendix A.4, A.5)
+    bool need_bond = (cls & (C_SB | C_HB)) || ((wi & I_XBOND) && (wj & I_XBOND));
+    if (need_bond && is_bonded(T, pi, aj)) return;
+    int ri = T.pair_res[pi], rj = T.pair_res[pj];
+    float dist = sqrtf(d2);
+    if (cls & (C_VDW | C_HP | C_NEARV | C_NEARH)) {
+        bool ss = (wi & I_CYS) && (wj & I_CYS) && is_disulfide(T, T.pair_resid[pi], T.pair_resid[pj]);
+        if (!ss) {
+            int e = (wi & I_ELEM) * T.K + (wj & I_ELEM);
+            if (cls & C_NEARV) emit_near(O, F.frame, CHC_NEAR_VDW_DIST, ai, aj, (double)dist - T.vcut[e]);
+            if (cls & C_NEARH) emit_near(O, F.frame, CHC_NEAR_HP_DIST, ai, aj, (double)dist - T.vcut[e]);
+            if (cls & C_VDW) {
+                count_pair(O, F.bits, ri, rj, T.R);
+                if (P.emit) emit_contact(O, F.frame, CHC_VDW, ai, aj, dist);
+            }
+            if ((cls & C_HP) && P.emit) {     // hp is not a counted type (get_contact_frequencies.py:107-109)
+                bool li = wi & I_LIG, lj = wj & I_LIG;
+                emit_contact(O, F.frame, (li || lj) ? ((li != lj) ? CHC_HPLP : CHC_HPLL) : CHC_HP, ai, aj, dist);
+            }
+        }
+    }
+    if (cls & C_SB) {
+        // orient as (anion, cation); salt_bridges.py:90-97 appends a plain sb line unless both are ligand atoms
+        bool ij = (wi & I_ANION) && (wj & I_CATION);
+        unsigned wa = ij ? wi : wj, wc = ij ? wj : wi;
+        int aa = ij ? ai : aj, ac = ij ? aj : ai;
+        bool al = wa & I_LIG, cl = wc & I_LIG;
+        if (!(al && cl)) count_pair(O, F.bits, ri, rj, T.R);
+        if (P.emit) emit_contact(O, F.frame, al ? (cl ? CHC_SBLL : CHC_SBLP) : (cl ? CHC_SBPL : CHC_SB), aa, ac, dist);
+    }
+    if (cls & C_HB) {
+        bool ok = false;
+        if (wi & I_HASH) ok |= hb_direction(T, P, O, F, a, b, pi, ai, aj);
+        if (wj & I_HASH) ok |= hb_direction(T, P, O, F, b, a, pj, aj, ai);
+        if (ok) {
+            bool li = wi & I_LIG, lj = wj & I_LIG, bi = wi & I_BB, bj = wj & I_BB;
+            int t;
+            if (li && lj) t = CHC_HBLL;
+            else if (li) t = bj ? CHC_HBLB : CHC_HBLS;
+            else if (lj) t = bi ? CHC_HBLB : CHC_HBLS;
+            else if (bi && bj) t = CHC_HBBB;
+            else if (!bi && !bj) t = CHC_HBSS;
+            else t = CHC_HBSB;
+            if (t != CHC_HBLL) count_pair(O, F.bits, ri, rj, T.R);
+            if (P.emit) emit_contact(O, F.frame, t, ai, aj, dist);
+        }
+    }
+}

@@ -1,0 +1,203 @@
+/* chacra_b200.h -- C ABI of the B200 contact-detection engine (libchacra_b200.so).
+ *
+ * The reference (Dan-Burns/ChACRA -> external/getcontacts) has no FFI: its hot path is Python that
+ * drives VMD through Tcl strings.  The entry points below are therefore the surface a maintainer
+ * binds with ctypes from the two reference functions that own the path:
+ *
+ *   chc_create            <- the one-off setup of compute_contacts()
+ *                            (external/getcontacts/contact_calc/compute_contacts.py:226-238)
+ *   chc_submit_frames*    <- compute_fragment_contacts() + compute_frame_contacts()
+ *                            (compute_contacts.py:106-180 and :50-103; the per-itype detectors
+ *                            salt_bridges.py:33-99, pi_cation.py:34-129, aromatics.py:116-257,
+ *                            vanderwaals.py:34-96, hbonds.py:29-206, hydrophobics.py:44-123)
+ *   chc_drain_contacts    <- the result queue feeding contact_consumer() (compute_contacts.py:306-359)
+ *   chc_read_counts       <- res_contacts_xl()/gen_counts() of the frequency step
+ *                            (external/getcontacts/contact_calc/transformations.py:70-150, :446-470;
+ *                            driver external/getcontacts/get_contact_frequencies.py:58-134)
+ *   chc_drain_near_cutoff <- new: the "within 1e-4 A / 1e-3 deg of a cutoff" side channel
+ *
+ * Conventions: plain C types only; 0 = success, negative = error (chc_last_error gives the text);
+ * nothing throws or exits; the caller owns every buffer it passes in; the library owns what it
+ * allocates until chc_destroy.  A context is bound to one CUDA device and is not thread-safe.
+ * All device work is enqueued on the stream the caller passes (NULL = the legacy default stream).
+ */
+#ifndef CHACRA_B200_H
+#define CHACRA_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CHC_ABI_VERSION 1
+
+/* interaction-type bits of chc_params.itype_mask (compute order of compute_contacts.py:85-101) */
+#define CHC_IT_SB  (1u << 0)
+#define CHC_IT_PC  (1u << 1)
+#define CHC_IT_PS  (1u << 2)
+#define CHC_IT_TS  (1u << 3)
+#define CHC_IT_VDW (1u << 4)
+#define CHC_IT_HB  (1u << 5)
+#define CHC_IT_HP  (1u << 6)
+#define CHC_IT_ALL 0x7Fu
+
+/* chc_contact.itype codes; the text tokens are the ones of SURVEY.md Appendix B.4 */
+enum chc_itype {
+    CHC_SB = 0, CHC_SBLP, CHC_SBPL, CHC_SBLL, CHC_PC, CHC_PS, CHC_TS, CHC_VDW,
+    CHC_HBBB, CHC_HBSB, CHC_HBSS, CHC_HBLL, CHC_HBLB, CHC_HBLS,
+    CHC_WB, CHC_WB2, CHC_LWB, CHC_LWB2, CHC_HP, CHC_HPLP, CHC_HPLL, CHC_N_ITYPES
+};
+
+/* kinds of chc_near records */
+enum chc_near_kind {
+    CHC_NEAR_VDW_DIST = 0, CHC_NEAR_HP_DIST, CHC_NEAR_HB_ANGLE, CHC_NEAR_PC_DIST, CHC_NEAR_PC_ANGLE,
+    CHC_NEAR_PS_DIST, CHC_NEAR_PS_ANGLE, CHC_NEAR_PS_PSI, CHC_NEAR_TS_DIST, CHC_NEAR_TS_ANGLE,
+    CHC_NEAR_TS_PSI, CHC_NEAR_SB_DIST, CHC_NEAR_HB_DIST
+};
+
+/* error codes */
+#define CHC_OK              0
+#define CHC_E_INVALID      -1   /* bad argument */
+#define CHC_E_CUDA         -2   /* CUDA runtime error */
+#define CHC_E_TOO_LARGE    -3   /* topology does not fit any kernel path */
+#define CHC_E_ORDER        -4   /* frames submitted off a fragment boundary */
+#define CHC_E_NOMEM        -5
+
+/* One emitted contact (32 bytes).  atom1/atom2 (+ water1/water2 for bridges) are 0-based atom
+ * indices of the topology; `frame` is the index the caller passed (first_index + k). */
+typedef struct chc_contact {
+    int32_t frame;
+    int32_t itype;      /* enum chc_itype */
+    int32_t atom1;
+    int32_t atom2;
+    int32_t water1;     /* -1 when unused */
+    int32_t water2;     /* -1 when unused */
+    float   distance;   /* float32 sqrtf(d2) between atom1 and atom2 (--distout) */
+    int32_t reserved;
+} chc_contact;
+
+/* One near-cutoff observation (32 bytes): value - cutoff, Angstrom or degree */
+typedef struct chc_near {
+    int32_t frame;
+    int32_t kind;       /* enum chc_near_kind */
+    int32_t atom1;
+    int32_t atom2;
+    double  delta;
+    int64_t reserved;
+} chc_near;
+
+/* Static tables produced by the host-side topology compiler (chacra_b200/topology.py).
+ * All pointers are HOST pointers; chc_create copies them to the device. */
+typedef struct chc_topology {
+    int32_t n_atoms;          /* atoms per frame (every stored atom, hydrogens and solvent included) */
+    int32_t n_pair;           /* NP: heavy atoms the cell-list pair search sees */
+    int32_t n_aux;            /* NA: atoms copied verbatim next to the cell list (donor H, rings, cations) */
+    int32_t n_h_slots;        /* the first n_h_slots aux entries are donor hydrogens (CSR pair_h_start) */
+    int32_t n_rings;
+    int32_t n_cations;
+    int32_t n_disulfide;
+    int32_t n_elem;           /* K <= 15 element classes among pair atoms */
+    int32_t n_residues;       /* R distinct residue labels, ranked in string order */
+    int32_t n_hp_base;
+    int32_t n_bond_adj;
+    int32_t same_selection;   /* 1 when the --sele and --sele2 strings are equal */
+    const int32_t*  pair_atom;        /* [NP] atom index */
+    const uint32_t* pair_info;        /* [NP] element class | flag bits (topology.py INFO_*) */
+    const int32_t*  pair_lkey;        /* [NP] locality key: same chain & |dresid|<k <=> |dlkey|<k */
+    const int32_t*  pair_res;         /* [NP] residue rank */
+    const int32_t*  pair_resid;       /* [NP] resid (disulfide rule) */
+    const int32_t*  pair_h_start;     /* [NP+1] CSR into aux slots [0, n_h_slots) */
+    const int32_t*  pair_bond_start;  /* [NP+1] */
+    const int32_t*  pair_bond_adj;    /* [n_bond_adj] bonded atom indices */
+    const int32_t*  aux_atom;         /* [NA] */
+    const int32_t*  ring_aux;         /* [NR][3] geometry triplet (aux slots) or -1 */
+    const int32_t*  ring_pc_aux;      /* [NR][3] pi-cation triplet in label order or -1 */
+    const int32_t*  ring_sel_aux;     /* [NR][3] ring atoms inside sele1|sele2, -1 padded */
+    const uint8_t*  ring_sel_flags;   /* [NR][3] bit0 sele1, bit1 sele2 */
+    const int32_t*  ring_atoms;       /* [NR][3] atom indices matching ring_sel_aux */
+    const int32_t*  ring_res;         /* [NR] residue rank */
+    const int32_t*  ring_rep;         /* [NR] representative atom (smallest name) */
+    const int32_t*  ring_rep_aux;     /* [NR] its aux slot */
+    const int32_t*  cation_aux;       /* [NC] */
+    const int32_t*  cation_atom;      /* [NC] */
+    const uint8_t*  cation_flags;     /* [NC] bit0 sele1, bit1 sele2 */
+    const int32_t*  cation_res;       /* [NC] */
+    const int32_t*  cation_excl_ring; /* [NC] ring holding an atom bonded to the cation, or -1 */
+    const int32_t*  disulfide;        /* [ND][2] resid pairs */
+    const float*    vdw_d2max;        /* [K][K] largest accepted float32 d2 (pure r1+r2+eps rule) */
+    const double*   vdw_cut;          /* [K][K] r1+r2+eps */
+    const int32_t*  hp_base;          /* [n_hp_base] pair indices of hydrophobic base carbons */
+    const uint8_t*  atom_class;       /* [n_atoms] 1 = element C, 2 = element H, 0 = other */
+} chc_topology;
+
+typedef struct chc_params {
+    uint32_t itype_mask;
+    int32_t  n_states;
+    int32_t  fragment_frames;     /* 100 = TRAJ_FRAG_SIZE (compute_contacts.py:43) */
+    int32_t  emit_contacts;       /* 1: fill the contact-record buffer */
+    int32_t  hbond_res_diff;
+    int32_t  vdw_res_diff;
+    int32_t  track_near;          /* 1: fill the near-cutoff buffer */
+    int32_t  reserved0;
+    int64_t  contact_capacity;    /* records */
+    int64_t  near_capacity;       /* records */
+    double sb_dist, pc_dist, pc_angle, ps_dist, ps_angle, ps_psi, ts_dist, ts_angle, ts_psi;
+    double hb_dist, hb_angle, vdw_epsilon;
+    double vdw_soft_cutoff;       /* max radius(sele1) + max radius(sele2) + epsilon (vanderwaals.py:24-31) */
+    double hp_dist;               /* epsilon + 2*1.7 (hydrophobics.py:83) */
+    double near_dist_tol;         /* 1e-4 */
+    double near_angle_tol;        /* 1e-3 */
+} chc_params;
+
+typedef struct chc_stats {
+    int64_t frames_submitted;
+    int64_t kernel_launches;      /* contact kernels + prepass kernels launched so far */
+    int64_t contacts_emitted;     /* including dropped ones */
+    int64_t contacts_dropped;     /* beyond contact_capacity */
+    int64_t near_total;
+    int32_t path;                 /* 1 = one CTA per frame (shared-memory cell list) */
+    int32_t smem_bytes;
+    int32_t threads;
+    int32_t grid;
+    int32_t staged;               /* 1: frames are staged through shared memory with bulk async copies */
+    int32_t bitset_in_smem;
+    double  last_kernel_ms;       /* main contact kernel of the last chc_submit_frames (needs timing on) */
+} chc_stats;
+
+typedef struct chc_ctx chc_ctx;
+
+int  chc_abi_version(void);
+int  chc_create(chc_ctx** out, const chc_topology* topo, const chc_params* params, int device);
+void chc_destroy(chc_ctx* ctx);
+const char* chc_last_error(const chc_ctx* ctx);
+
+/* Use a caller-owned device buffer int32 [n_states][n_pairs] for the count tables (so that the host
+ * side can all-reduce it with NCCL).  n_elems must equal n_states * chc_n_pairs(). */
+int     chc_bind_counts(chc_ctx* ctx, int32_t* d_counts, int64_t n_elems);
+int64_t chc_n_pairs(const chc_ctx* ctx);     /* R*(R+1)/2, index = lo*R - lo*(lo-1)/2 + (hi-lo) */
+int     chc_reset_counts(chc_ctx* ctx, void* stream);
+int     chc_counts_device(chc_ctx* ctx, int32_t** d_counts, int64_t* n_pairs);
+int     chc_read_counts(chc_ctx* ctx, int state, int32_t* h_counts, int64_t n_pairs, void* stream);
+
+/* d_xyz: DEVICE float32 [n_frames][n_atoms][3] (Angstrom), frame k at d_xyz + k*frame_stride floats
+ * (frame_stride 0 = 3*n_atoms).  first_index: position of the first frame in the caller's selected
+ * frame sequence; a chunk must start on a multiple of fragment_frames or continue the previous chunk. */
+int chc_submit_frames(chc_ctx* ctx, int state, const float* d_xyz, int64_t n_frames, int64_t first_index,
+                      int64_t frame_stride, void* stream);
+/* Same with HOST coordinates: the library stages them through pinned memory and copies them to
+ * the device itself (double buffered). */
+int chc_submit_frames_host(chc_ctx* ctx, int state, const float* h_xyz, int64_t n_frames, int64_t first_index,
+                           void* stream);
+int chc_synchronize(chc_ctx* ctx, void* stream);
+
+/* Copy out (and clear) the records accumulated so far.  *n = records copied. */
+int chc_drain_contacts(chc_ctx* ctx, chc_contact* host_buf, int64_t cap, int64_t* n, void* stream);
+int chc_drain_near_cutoff(chc_ctx* ctx, chc_near* host_buf, int64_t cap, int64_t* n, int64_t* n_total, void* stream);
+int chc_get_stats(chc_ctx* ctx, chc_stats* out);
+int chc_set_timing(chc_ctx* ctx, int on);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -578,8 +578,13 @@ def hbond_angle_f32(xd, xh, xa) -> np.float32:
     return F32(F32(57.2958) * F32(math.atan2(float(psin), float(pcos))))
 
 
-def measure_hbonds(top: Topology, xyz, mD, mA, cutoff: float, ang: float, one_selection=False, near=None):
-    """Appendix A.5.  Returns a set of (donor, acceptor) heavy-atom index pairs."""
+def measure_hbonds(top: Topology, xyz, mD, mA, cutoff: float, ang: float, one_selection=False, near=None,
+                   near_filter=None):
+    """Appendix A.5.  Returns a set of (donor, acceptor) heavy-atom index pairs.
+
+    ``near`` (oracle-only side channel, not reference behaviour): every (donor, H, acceptor) angle within
+    1e-3 degree of the cutoff is recorded, for every hydrogen of the donor, when ``near_filter(d, a)``
+    holds (the caller passes the non-geometric filters so that only decisive pairs are listed)."""
     iD = np.nonzero(mD & ~top.is_h)[0]
     iA = iD if one_selection else np.nonzero(mA & ~top.is_h)[0]
     out = set()
@@ -598,11 +603,10 @@ def measure_hbonds(top: Topology, xyz, mD, mA, cutoff: float, ang: float, one_se
                 if not top.is_h[h]:
                     continue
                 t = hbond_angle_f32(xyz[d], xyz[h], xyz[acc])
-                if near is not None and abs(float(t) - float(angf)) < 1e-3:
+                if near is not None and abs(float(t) - float(angf)) < 1e-3 and (near_filter is None or near_filter(d, acc)):
                     near.append(("hb_angle", d, acc, float(t) - float(angf)))
                 if t < angf:
                     out.add((d, acc))
-                    break
     return out
 
 
@@ -683,12 +687,12 @@ def compute_pi_cation(S: Setup, xyz, geom, near=None):
         cen = _centroid(p1, p2, p3)
         d = float(np.linalg.norm(x64[c] - cen))
         if near is not None and abs(d - cd) < 1e-4:
-            near.append(("pc_dist", c, p[0], d - cd))
+            near.append(("pc_dist", c, _ring_rep(top, p), d - cd))
         if d > cd:
             continue
         t = _fold(_angle_between(_normal(p1, p2, p3), x64[c] - cen))
         if near is not None and abs(t - ca) < 1e-3:
-            near.append(("pc_angle", c, p[0], t - ca))
+            near.append(("pc_angle", c, _ring_rep(top, p), t - ca))
         if t > ca:
             continue
         out.append(("pc", c, _ring_rep(top, p)))
@@ -735,19 +739,19 @@ def compute_aromatics(S: Setup, xyz, itype, soft, dist_cut, ang_cut, psi_cut, ne
         c1, c2 = _centroid(a1, a2, a3), _centroid(b1, b2, b3)
         d = float(np.linalg.norm(c1 - c2))
         if near is not None and abs(d - dist_cut) < 1e-4:
-            near.append((itype + "_dist", t1[0], t2[0], d - dist_cut))
+            near.append((itype + "_dist", _ring_rep(top, t1), _ring_rep(top, t2), d - dist_cut))
         if d > dist_cut:
             continue
         n1, n2 = _normal(a1, a2, a3), _normal(b1, b2, b3)
         ang = _angle_between(n1, n2)
         v = _fold(ang) if itype == "ps" else math.fabs(ang - 90)
         if near is not None and abs(v - ang_cut) < 1e-3:
-            near.append((itype + "_angle", t1[0], t2[0], v - ang_cut))
+            near.append((itype + "_angle", _ring_rep(top, t1), _ring_rep(top, t2), v - ang_cut))
         if v > ang_cut:
             continue
         psi = min(_psi(c1, c2, n1), _psi(c2, c1, n2))
         if near is not None and abs(psi - psi_cut) < 1e-3:
-            near.append((itype + "_psi", t1[0], t2[0], psi - psi_cut))
+            near.append((itype + "_psi", _ring_rep(top, t1), _ring_rep(top, t2), psi - psi_cut))
         if psi > psi_cut:
             continue
         out.append((itype, _ring_rep(top, t1), _ring_rep(top, t2)))
@@ -854,7 +858,8 @@ def compute_hydrogen_bonds(S: Setup, xyz, geom, near=None):
     U = selany & ~(S.carbon | S.sulfur | S.solv)
     W = within(xyz, S.solv, selany, 3.5) if S.solv.any() else np.zeros(top.n, dtype=bool)
     dual = lambda a, b: (S.sele1[a] and S.sele2[b]) or (S.sele2[a] and S.sele1[b])
-    SS = measure_hbonds(top, xyz, U, U, cd, ca, one_selection=True, near=near)
+    SS = measure_hbonds(top, xyz, U, U, cd, ca, one_selection=True, near=near,
+                        near_filter=lambda d, a: dual(d, a) and not _local(top, d, a, rd))
     out = []
     for d, a in sorted(SS):
         if not dual(d, a):
@@ -878,8 +883,8 @@ def compute_hydrogen_bonds(S: Setup, xyz, geom, near=None):
         out.append((t, d, a))
     if not W.any():
         return out
-    SW = measure_hbonds(top, xyz, U, W, cd, ca, near=near) | measure_hbonds(top, xyz, W, U, cd, ca, near=near)
-    WW = measure_hbonds(top, xyz, W, W, cd, ca, one_selection=True, near=near)
+    SW = measure_hbonds(top, xyz, U, W, cd, ca) | measure_hbonds(top, xyz, W, U, cd, ca)
+    WW = measure_hbonds(top, xyz, W, W, cd, ca, one_selection=True)
     wd = defaultdict(set)
     for d, a in sorted(SW | WW):
         if top.chain[d] == top.chain[a] and top.resid[d] == top.resid[a]:
