@@ -1,0 +1,284 @@
+#!/usr/bin/env python
+"""bench.py -- contact frames/s (all interaction types) on the BASELINE.json config-2 shape.
+
+Workload (`config.workload`): "1tnf solvated HREMD synthetic: 20 states x 10k frames, ~7k protein atoms,
+all itypes, 1 GPU" -> 4 tiled copies of the hydrogenated 5xnd fixture (6 516 atoms, 448 residues),
+20 states x 10 000 frames of float32 coordinates resident in HBM (15.6 GB >> 126 MB of L2).
+One "step" = one pass of the hot path over all 20 state trajectories (count tables reset first).
+With N > 1 every rank runs the same shape on its own frames (weak scaling) and the per-state count
+tables are merged with one NCCL all-reduce inside the step.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--states S] [--frames F]
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+ITYPES = ["sb", "pc", "ps", "ts", "vdw", "hb", "hp"]
+WORKLOAD = "1tnf solvated HREMD synthetic: 20 states x 10k frames, ~7k protein atoms, all itypes, 1 GPU"
+METRIC = "contact frames/sec (all itypes)"
+
+
+def make_topology(copies=4):
+    from chacra_b200.synthetic import tile_pdb
+    from chacra_b200 import read_pdb
+    path = os.path.join(tempfile.gettempdir(), "chacra_bench_%d_%d.pdb" % (copies, os.getpid()))
+    tile_pdb(os.path.join(GOLDEN, "5xnd_topology.pdb"), path, copies)
+    return path, read_pdb(path)
+
+
+def state_amplitude(state, n_states):
+    return 0.8 * (1.0 + 0.6 * state / max(1, n_states - 1))       # "heating": 1.0 -> 1.6 across states
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], threading.Event()
+
+    def run(self):
+        while not self.stop_flag.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self.stop_flag.wait(0.2)
+
+    def summary(self):
+        self.stop_flag.set()
+        self.join(timeout=6)
+        sm = sorted(int(float(r[0])) for r in self.rows if r and r[0].replace(".", "").isdigit())
+        reasons = set()
+        for r in self.rows:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        mx = [int(float(r[1])) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(self.rows)}
+
+
+def oracle_frames_per_second(pdb_path, frames, procs):
+    """CPU restatement of the reference semantics (oracle/, numpy) on `frames`, `procs` worker processes."""
+    import multiprocessing as mp
+    chunks = [frames[k::procs] for k in range(procs) if len(frames[k::procs])]
+    t0 = time.perf_counter()
+    if len(chunks) == 1:
+        _oracle_worker((pdb_path, chunks[0]))
+    else:
+        with mp.get_context("fork").Pool(len(chunks)) as pool:
+            pool.map(_oracle_worker, [(pdb_path, c) for c in chunks])
+    dt = time.perf_counter() - t0
+    return len(frames) / dt, dt
+
+
+def _oracle_worker(args):
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import getcontacts_oracle as o
+    pdb_path, frames = args
+    res = o.run(pdb_path, pdb_path, ITYPES, frames=frames)
+    o.intended_counts(res)
+    return len(res["contacts"])
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path.  vmd-python is not installable here (no network), so the
+    reference itself cannot run; the arm times the oracle port on all host cores (kind = "port")."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import numpy as np
+    from chacra_b200.synthetic import FrameGenerator
+    path, atoms = make_topology()
+    cores = os.cpu_count() or 1
+    per_step = max(cores, min(4 * cores, 64))
+    gen = FrameGenerator(atoms.xyz, 2000, amplitude=state_amplitude(0, args.states))
+    frames = gen.frames(per_step).numpy()
+    for _ in range(min(args.warmup, 1)):
+        oracle_frames_per_second(path, frames[:cores], cores)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        oracle_frames_per_second(path, frames, cores)
+    dt = time.perf_counter() - t0
+    fps = args.steps * per_step / dt
+    line = {"impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "atoms": int(atoms.n), "itypes": ITYPES, "frames_per_step": per_step},
+            "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port",
+                             "sample": "%d frames per step of the config-2 shape, numpy oracle, %d processes; the reference "
+                                       "itself needs vmd-python (absent, no network)" % (per_step, cores)},
+            "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="chacra_b200")
+    ap.add_argument("--states", type=int, default=20)
+    ap.add_argument("--frames", type=int, default=10000, help="frames per state")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    args.warmup = max(args.warmup, 3)
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from chacra_b200 import compile_topology
+    from chacra_b200.engine import ContactEngine
+    from chacra_b200.synthetic import FrameGenerator
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    S, F = args.states, args.frames
+    path, atoms = make_topology()
+    topo = compile_topology(atoms)
+    eng = ContactEngine(topo, ITYPES, n_states=S, device=local)
+    N = atoms.n
+    # ---- synthetic state trajectories, generated straight into HBM ---------------------------------------
+    traj = []
+    for s in range(S):
+        gen = FrameGenerator(atoms.xyz, 1000 * 2 + s + 100 * rank, amplitude=state_amplitude(s, S), device=dev)
+        buf = torch.empty((F, N, 3), dtype=torch.float32, device=dev)
+        for b in range(0, F, 1000):
+            buf[b:b + 1000] = gen.frames(min(1000, F - b))
+        traj.append(buf)
+    del gen
+    torch.cuda.synchronize()
+
+    def step():
+        eng.reset_counts()
+        for s in range(S):
+            eng.submit(traj[s], s, 0)
+        if world > 1:
+            dist.all_reduce(eng.counts_tensor)          # the path's one exchange step (int32 sum, order-free)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    launches0 = eng.stats()["kernel_launches"]
+    eng.set_timing(True)
+    sampler = ClockSampler(local)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    st = eng.stats()
+    eng.set_timing(False)
+    clocks = sampler.summary()
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    launches = st["kernel_launches"] - launches0 + (args.steps if world > 1 else 0)
+    frames_per_step = S * F * world
+    value = args.steps * frames_per_step / (ms * 1e-3)
+    counts_dev = eng.counts_tensor.clone()
+
+    # ---- e2e: the same job through the host-buffer entry point (H2D + counts D2H inside the timed region) ----
+    host = torch.empty((F, N, 3), dtype=torch.float32, pin_memory=True)
+    host.copy_(traj[0])
+
+    def e2e_step():
+        eng.reset_counts()
+        for s in range(S):
+            eng.submit(host, s, 0)
+        if world > 1:
+            dist.all_reduce(eng.counts_tensor)
+        return eng.counts_tensor.cpu()
+
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.e2e_steps):
+        table = e2e_step()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    e2e_value = args.e2e_steps * frames_per_step / e2e_s
+    # host path and device path must agree bit for bit on the state they share
+    if world == 1:
+        assert torch.equal(table[0], counts_dev[0].cpu()), "host-buffer path and device path disagree"
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak, which = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+        n_main = max(1, st["timed_launches"])
+        avg_ms = st["kernel_ms_total"] / n_main
+        bytes_per_launch = 12.0 * N * F                    # algorithmic: every stored coordinate read once
+        achieved = bytes_per_launch / (avg_ms * 1e-3) / 1e9
+        line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic",
+                "config": {"workload": WORKLOAD, "atoms": int(N), "pair_atoms": int(len(topo.pair_atom)),
+                           "residues": int(topo.n_residues), "states": S, "frames_per_state": F, "itypes": ITYPES,
+                           "l2": "inputs (%.1f GB per GPU) are larger than L2" % (S * F * N * 12 / 1e9),
+                           "outputs": "int32 residue-pair frame counts [states][pairs]",
+                           "parallelism": "frames sharded, %d rank(s), one int32 all-reduce" % world},
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                             "traffic": None, "kernel": "frame_contacts_kernel", "peak_source": which,
+                             "avg_launch_ms": avg_ms, "launches_timed": n_main, "algorithmic_bytes_per_launch": bytes_per_launch,
+                             "kernel_share_of_step": st["kernel_ms_total"] / ms},
+                "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": int(S * F * N * 12),
+                        "d2h_bytes_per_step": int(eng.counts_tensor.numel() * 4), "steps": args.e2e_steps},
+                "gpu_launches": int(launches), "clocks": clocks,
+                "engine": {k: st[k] for k in ("path", "smem_bytes", "threads", "grid", "staged", "bitset_in_smem")}}
+        if world == 1 and not args.no_cpu_baseline:
+            gen = FrameGenerator(atoms.xyz, 2000, amplitude=state_amplitude(0, S))
+            sample = gen.frames(16).numpy()
+            fps, dt = oracle_frames_per_second(path, sample, 1)
+            line["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": 1, "kind": "port",
+                                    "sample": "16 frames of the same shape, numpy oracle, 1 process, %.1f s" % dt}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

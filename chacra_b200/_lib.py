@@ -71,7 +71,7 @@ class ChcStats(C.Structure):
     _fields_ = [(n, C.c_int64) for n in ("frames_submitted", "kernel_launches", "contacts_emitted",
                                          "contacts_dropped", "near_total")] + \
                [(n, C.c_int32) for n in ("path", "smem_bytes", "threads", "grid", "staged", "bitset_in_smem")] + \
-               [("last_kernel_ms", C.c_double)]
+               [("last_kernel_ms", C.c_double), ("kernel_ms_total", C.c_double), ("timed_launches", C.c_int64)]
 
 
 # every symbol include/chacra_b200.h declares: name -> (restype, argtypes)

@@ -26,8 +26,9 @@ struct chc_ctx {
     unsigned char* hpmask = nullptr; int64_t hpmask_frags = 0;
     unsigned* gbits = nullptr;
     float* dev_stage[2] = {nullptr, nullptr}; float* pin_stage[2] = {nullptr, nullptr};
-    int64_t stage_frames = 0; cudaEvent_t stage_done[2] = {nullptr, nullptr}; cudaStream_t copy_stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr; bool timing = false; bool timed_pending = false;
+    int64_t stage_frames = 0; cudaEvent_t stage_done[2] = {nullptr, nullptr}; cudaEvent_t copied[2] = {nullptr, nullptr}; cudaStream_t copy_stream = nullptr;
+    bool timing = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_pending, ev_free;   // CUDA-event pairs around main kernels
     int64_t last_state = -1, next_index = -1;          // for fragment continuation checks
     int hp_last_slot = 0;
     chc_stats st{};
@@ -63,7 +64,7 @@ static int plan_small(chc_ctx* ctx) {
     L.off_slk = (int)off;  off = al(off + 4 * (size_t)T.n_pair);
     L.off_tmp = (int)off;  off = al(off + 4 * (size_t)T.n_pair);
     L.off_aux = (int)off;  off = al(off + 12 * (size_t)std::max(T.n_aux, 1));
-    L.off_q1 = (int)off;   off = al(off + 4 * (size_t)warps * Q1_CAP);
+    L.off_q1 = (int)off;   off = al(off + 2 * (size_t)warps * LQ_CAP * 32);
     L.off_q2 = (int)off;   off = al(off + 12 * (size_t)warps * Q2_CAP);
     L.off_tv = (int)off;   off = al(off + 4 * (size_t)T.K * T.K);
     L.off_th = (int)off;   off = al(off + 4 * (size_t)T.K * T.K);
@@ -100,10 +101,11 @@ extern "C" void chc_destroy(chc_ctx* ctx) {
     for (int k = 0; k < 2; ++k) {
         cudaFree(ctx->dev_stage[k]); if (ctx->pin_stage[k]) cudaFreeHost(ctx->pin_stage[k]);
         if (ctx->stage_done[k]) cudaEventDestroy(ctx->stage_done[k]);
+        if (ctx->copied[k]) cudaEventDestroy(ctx->copied[k]);
     }
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
-    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
-    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    for (auto& e : ctx->ev_pending) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
+    for (auto& e : ctx->ev_free) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
     delete ctx;
 }
 
@@ -183,7 +185,6 @@ extern "C" int chc_create(chc_ctx** out, const chc_topology* t, const chc_params
     CK(cudaMalloc(&ctx->near_n, 8)); CK(cudaMemset(ctx->near_n, 0, 8));
     CK(cudaMalloc(&ctx->contacts, std::max<int64_t>(p->contact_capacity, 1) * sizeof(chc_contact)));
     CK(cudaMalloc(&ctx->near, std::max<int64_t>(p->near_capacity, 1) * sizeof(chc_near)));
-    CK(cudaEventCreate(&ctx->ev0)); CK(cudaEventCreate(&ctx->ev1));
     ctx->st.path = 1; ctx->st.smem_bytes = ctx->L.total; ctx->st.threads = THREADS_SMALL; ctx->st.staged = 0;
     ctx->st.bitset_in_smem = ctx->L.bits_in_smem;
     return CHC_OK;
@@ -275,11 +276,16 @@ extern "C" int chc_submit_frames(chc_ctx* ctx, int state, const float* d_xyz, in
     O.contacts = ctx->contacts; O.contact_n = ctx->contact_n; O.contact_cap = ctx->prm.contact_capacity;
     O.near = ctx->near; O.near_n = ctx->near_n; O.near_cap = ctx->prm.near_capacity;
     int grid = (int)std::min<int64_t>(n_frames, ctx->sm_count);
-    if (ctx->timing) CK(cudaEventRecord(ctx->ev0, stream));
+    std::pair<cudaEvent_t, cudaEvent_t> ev{nullptr, nullptr};
+    if (ctx->timing) {
+        if (!ctx->ev_free.empty()) { ev = ctx->ev_free.back(); ctx->ev_free.pop_back(); }
+        else { CK(cudaEventCreate(&ev.first)); CK(cudaEventCreate(&ev.second)); }
+        CK(cudaEventRecord(ev.first, stream));
+    }
     frame_contacts_kernel<THREADS_SMALL><<<grid, THREADS_SMALL, ctx->L.total, stream>>>(
         ctx->T, ctx->P, O, ctx->L, d_xyz, frame_stride, (int)n_frames, first_index, F, frag0, ctx->hpmask, ctx->gbits);
     CK(cudaGetLastError());
-    if (ctx->timing) { CK(cudaEventRecord(ctx->ev1, stream)); ctx->timed_pending = true; }
+    if (ctx->timing) { CK(cudaEventRecord(ev.second, stream)); ctx->ev_pending.push_back(ev); }
     ctx->st.kernel_launches++;
     ctx->st.frames_submitted += n_frames;
     ctx->st.grid = grid;
@@ -307,19 +313,30 @@ extern "C" int chc_submit_frames_host(chc_ctx* ctx, int state, const float* h_xy
         }
         ctx->stage_frames = chunk;
     }
+    if (!ctx->copy_stream) {
+        CK(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+        for (int k = 0; k < 2; ++k) CK(cudaEventCreateWithFlags(&ctx->copied[k], cudaEventDisableTiming));
+    }
     cudaPointerAttributes attr;
     bool pinned = cudaPointerGetAttributes(&attr, h_xyz) == cudaSuccess && attr.type == cudaMemoryTypeHost;
     cudaGetLastError();
     int64_t done = 0; int buf = 0;
-    // a chunk that continues a fragment must first run up to the next fragment boundary
+    // copies run on their own stream so that the H2D of chunk k+1 overlaps the kernels of chunk k;
+    // a chunk that continues a fragment first runs up to the next fragment boundary
     while (done < n_frames) {
         int64_t idx = first_index + done;
         int64_t n = std::min<int64_t>(chunk, n_frames - done);
         if (idx % F) n = std::min<int64_t>(n, F - idx % F);
-        CK(cudaEventSynchronize(ctx->stage_done[buf]));        // buffer free again (trivially true when never recorded)
         const float* src = h_xyz + (size_t)done * 3 * ctx->T.n_atoms;
-        if (!pinned) { memcpy(ctx->pin_stage[buf], src, n * fbytes); src = ctx->pin_stage[buf]; }
-        CK(cudaMemcpyAsync(ctx->dev_stage[buf], src, n * fbytes, cudaMemcpyHostToDevice, stream));
+        if (!pinned) {
+            CK(cudaEventSynchronize(ctx->stage_done[buf]));    // pinned bounce buffer free again
+            memcpy(ctx->pin_stage[buf], src, n * fbytes);
+            src = ctx->pin_stage[buf];
+        }
+        CK(cudaStreamWaitEvent(ctx->copy_stream, ctx->stage_done[buf], 0));   // device buffer no longer read
+        CK(cudaMemcpyAsync(ctx->dev_stage[buf], src, n * fbytes, cudaMemcpyHostToDevice, ctx->copy_stream));
+        CK(cudaEventRecord(ctx->copied[buf], ctx->copy_stream));
+        CK(cudaStreamWaitEvent(stream, ctx->copied[buf], 0));
         int rc = chc_submit_frames(ctx, state, ctx->dev_stage[buf], n, idx, 0, stream);
         if (rc != CHC_OK) return rc;
         CK(cudaEventRecord(ctx->stage_done[buf], stream));
@@ -373,16 +390,25 @@ extern "C" int chc_drain_near_cutoff(chc_ctx* ctx, chc_near* host_buf, int64_t c
     return CHC_OK;
 }
 
-extern "C" int chc_set_timing(chc_ctx* ctx, int on) { if (!ctx) return CHC_E_INVALID; ctx->timing = on != 0; return CHC_OK; }
+extern "C" int chc_set_timing(chc_ctx* ctx, int on) {
+    if (!ctx) return CHC_E_INVALID;
+    ctx->timing = on != 0;
+    if (on) { ctx->st.kernel_ms_total = 0.0; ctx->st.timed_launches = 0; }
+    return CHC_OK;
+}
 
 extern "C" int chc_get_stats(chc_ctx* ctx, chc_stats* out) {
     if (!ctx || !out) return CHC_E_INVALID;
-    if (ctx->timed_pending) {
+    if (!ctx->ev_pending.empty()) {
         CK(cudaSetDevice(ctx->device));
-        CK(cudaEventSynchronize(ctx->ev1));
-        float ms = 0.f;
-        CK(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
-        ctx->st.last_kernel_ms = ms; ctx->timed_pending = false;
+        for (auto& e : ctx->ev_pending) {
+            CK(cudaEventSynchronize(e.second));
+            float ms = 0.f;
+            CK(cudaEventElapsedTime(&ms, e.first, e.second));
+            ctx->st.last_kernel_ms = ms; ctx->st.kernel_ms_total += ms; ctx->st.timed_launches++;
+            ctx->ev_free.push_back(e);
+        }
+        ctx->ev_pending.clear();
     }
     *out = ctx->st;
     return CHC_OK;

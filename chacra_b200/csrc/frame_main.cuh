@@ -1,69 +1,13 @@
 // frame_main.cuh -- the persistent one-CTA-per-frame contact kernel (see frame_kernel.cuh for the phases).
+//
+// Code-size note: the first version inlined E2/E3 at ~45 sites (36k SASS instructions) and spent 82 % of
+// its cycles in instruction-fetch stalls (profiles/r01_ncu_v0_summary.txt).  The pair phase is therefore
+// written as one loop nest in which the prefilter, the exact stage and the emit stage each appear at
+// exactly ONE place; the "final" pass of the outer loop only flushes the queues.
 #pragma once
 #include "frame_phases.cuh"
 
-struct WarpQueues {
-    unsigned* q1;          // prefilter survivors: (i << 16) | j, sorted slots
-    unsigned* q2ij; unsigned* q2cls; float* q2d;
-    int qn, q2n, lane;
-
-    __device__ __forceinline__ void e3_batch(const DevTopo& T, const DevParams& P, const DevOut& O, const FrameCtx& F,
-                                             int first, int n) {
-        if (lane < n) {
-            unsigned e = q2ij[first + lane];
-            e3_finish(T, P, O, F, e >> 16, e & 0xffff, q2cls[first + lane], q2d[first + lane]);
-        }
-        __syncwarp();
-    }
-    __device__ __forceinline__ void e2_batch(const DevTopo& T, const DevParams& P, const DevOut& O, const FrameCtx& F,
-                                             int first, int n) {
-        unsigned e = 0, cls = 0; float d2 = 0.f;
-        if (lane < n) {
-            e = q1[first + lane];
-            cls = e2_classify(T, P, F, e >> 16, e & 0xffff, d2);
-        }
-        unsigned bal = __ballot_sync(FULL, cls != 0);
-        if (cls) {
-            int idx = q2n + __popc(bal & ((1u << lane) - 1));
-            q2ij[idx] = e; q2cls[idx] = cls; q2d[idx] = d2;
-        }
-        q2n += __popc(bal);
-        __syncwarp();
-        if (q2n >= 32) { q2n -= 32; e3_batch(T, P, O, F, q2n, 32); }
-    }
-    __device__ __forceinline__ void drain_q1(const DevTopo& T, const DevParams& P, const DevOut& O, const FrameCtx& F) {
-        while (qn >= 32) { qn -= 32; e2_batch(T, P, O, F, qn, 32); }
-        if (qn > 0) { int n = qn; qn = 0; e2_batch(T, P, O, F, 0, n); }
-    }
-    __device__ __forceinline__ void drain_all(const DevTopo& T, const DevParams& P, const DevOut& O, const FrameCtx& F) {
-        drain_q1(T, P, O, F);
-        if (q2n > 0) { int n = q2n; q2n = 0; e3_batch(T, P, O, F, 0, n); }
-    }
-    // warp-uniform call: every lane brings the survivor bitmask of its atom i against slots jbase..jbase+31
-    __device__ __forceinline__ void push(const DevTopo& T, const DevParams& P, const DevOut& O, const FrameCtx& F,
-                                         unsigned mask, int i, int jbase) {
-        int cnt = __popc(mask), incl = cnt;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += t; }
-        int total = __shfl_sync(FULL, incl, 31);
-        if (total == 0) return;
-        if (qn + total > Q1_CAP) drain_q1(T, P, O, F);
-        if (total > Q1_CAP) {           // very dense neighbourhood: every lane finishes its own survivors
-            while (mask) {
-                int k = __ffs(mask) - 1; mask &= mask - 1;
-                float d2; unsigned cls = e2_classify(T, P, F, i, jbase + k, d2);
-                if (cls) e3_finish(T, P, O, F, i, jbase + k, cls, d2);
-            }
-            __syncwarp();
-            return;
-        }
-        int pos = qn + incl - cnt;
-        while (mask) { int k = __ffs(mask) - 1; mask &= mask - 1; q1[pos++] = ((unsigned)i << 16) | (unsigned)(jbase + k); }
-        qn += total;
-        __syncwarp();
-        while (qn >= 32) { qn -= 32; e2_batch(T, P, O, F, qn, 32); }
-    }
-};
+#define LQ_CAP 48          // per-lane survivor slots (lane-strided, conflict-free)
 
 __device__ __forceinline__ int cell_of(float x, float origin, float inv, int n) {
     int c = (int)((x - origin) * inv);
@@ -88,12 +32,10 @@ frame_contacts_kernel(DevTopo T, DevParams P, DevOut O, SmemLayout L, const floa
                                     : gbits + (size_t)blockIdx.x * L.bits_words;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int NP = T.n_pair;
-    WarpQueues Q;
-    Q.q1 = reinterpret_cast<unsigned*>(smem + L.off_q1) + warp * Q1_CAP;
-    Q.q2ij = reinterpret_cast<unsigned*>(smem + L.off_q2) + warp * (3 * Q2_CAP);
-    Q.q2cls = Q.q2ij + Q2_CAP;
-    Q.q2d = reinterpret_cast<float*>(Q.q2cls + Q2_CAP);
-    Q.lane = lane;
+    unsigned short* lq = reinterpret_cast<unsigned short*>(smem + L.off_q1) + warp * (LQ_CAP * 32) + lane;
+    unsigned* q2ij = reinterpret_cast<unsigned*>(smem + L.off_q2) + warp * (3 * Q2_CAP);
+    unsigned* q2cls = q2ij + Q2_CAP;
+    float* q2d = reinterpret_cast<float*>(q2cls + Q2_CAP);
     for (int k = tid; k < T.K * T.K; k += THREADS) { tv[k] = T.tv[k]; th[k] = T.th[k]; }
 
     for (int f = blockIdx.x; f < n_frames; f += gridDim.x) {
@@ -199,49 +141,82 @@ frame_contacts_kernel(DevTopo T, DevParams P, DevOut O, SmemLayout L, const floa
             }
         }
         // ---- E: pair interactions ------------------------------------------------------------------------
-        Q.qn = 0; Q.q2n = 0;
         const float pre2 = P.pre2;
-        for (;;) {
+        int q2n = 0;
+        bool final_pass = false;
+        do {
             int chunk = 0;
             if (lane == 0) chunk = atomicAdd(&M->chunk, 1);
             chunk = __shfl_sync(FULL, chunk, 0);
+            final_pass = chunk * 32 >= NP;
             const int i = chunk * 32 + lane;
-            if (chunk * 32 >= NP) break;
-            const bool valid = i < NP;
-            float4 me = valid ? spos[i] : make_float4(0.f, 0.f, 0.f, 0.f);
-            int rb[5], re[5];
-            if (valid) {
-                int c = (cell_of(me.z, org[2], inv, nc[2]) + 1) * pxy + (cell_of(me.y, org[1], inv, nc[1]) + 1) * px +
-                        cell_of(me.x, org[0], inv, nc[0]) + 1;
-                rb[0] = i + 1;                 re[0] = cells[c + 2];
-                rb[1] = cells[c + px - 1];     re[1] = cells[c + px + 2];
-                int u = c + pxy;
-                rb[2] = cells[u - px - 1];     re[2] = cells[u - px + 2];
-                rb[3] = cells[u - 1];          re[3] = cells[u + 2];
-                rb[4] = cells[u + px - 1];     re[4] = cells[u + px + 2];
-            } else {
-#pragma unroll
-                for (int r = 0; r < 5; ++r) { rb[r] = 0; re[r] = 0; }
-            }
-#pragma unroll
-            for (int r = 0; r < 5; ++r) {
-                const int len = re[r] - rb[r];
-                const int maxlen = __reduce_max_sync(FULL, len);
-                for (int off = 0; off < maxlen; off += 32) {
-                    const int jb = rb[r] + off;
-                    const int n = min(32, len - off);
-                    unsigned mask = 0;
-                    for (int k = 0; k < n; ++k) {
-                        float4 o = spos[jb + k];
-                        float dx = o.x - me.x, dy = o.y - me.y, dz = o.z - me.z;
-                        float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
-                        mask |= (d2 <= pre2 ? 1u : 0u) << k;
-                    }
-                    Q.push(T, P, O, F, mask, i, jb);
+            const bool valid = !final_pass && i < NP;
+            const float4 me = valid ? spos[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+            const int lki = valid ? slk[i] : 0;
+            int c0 = 0;
+            if (valid)
+                c0 = (cell_of(me.z, org[2], inv, nc[2]) + 1) * pxy + (cell_of(me.y, org[1], inv, nc[1]) + 1) * px +
+                     cell_of(me.x, org[0], inv, nc[0]) + 1;
+            int cnt = 0;
+            int r = 0;
+#pragma unroll 1
+            do {
+                // half shell: own row from i+1 to the end of cell x+1, then rows (y+1,z) (y-1,z+1) (y,z+1) (y+1,z+1)
+                int jb = 0, len = 0;
+                if (valid) {
+                    const int dy = (r == 1 || r == 4) - (r == 2), dz = r >= 2;
+                    const int base = c0 + dy * px + dz * pxy;
+                    jb = r == 0 ? i + 1 : cells[base - 1];
+                    len = cells[base + 2] - jb;
                 }
-            }
-        }
-        Q.drain_all(T, P, O, F);
+                const int maxlen = __reduce_max_sync(FULL, len);
+                int off = 0;
+#pragma unroll 1
+                do {
+                    // ---- E1: fused-multiply prefilter, survivors into the lane's own slots
+                    const int n = min(32, len - off);
+                    const float4* pj = spos + jb + off;
+#pragma unroll 4
+                    for (int k = 0; k < n; ++k) {
+                        const float4 o = pj[k];
+                        const float dx = o.x - me.x, dy = o.y - me.y, dz = o.z - me.z;
+                        const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
+                        if (d2 <= pre2) { lq[cnt * 32] = (unsigned short)(jb + off + k); ++cnt; }
+                    }
+                    off += 32;
+                    const bool last = off >= maxlen && r == 4;
+                    if (last || __any_sync(FULL, cnt > LQ_CAP - 32)) {
+                        // ---- E2: exact float32 d2 + class tests, one row of survivors per iteration
+                        const int rows = __reduce_max_sync(FULL, cnt);
+                        const bool flush = final_pass && last;
+#pragma unroll 1
+                        for (int s = 0; s < rows || (flush && s == 0); ++s) {
+                            unsigned cls = 0; float d2 = 0.f; int j = 0;
+                            if (s < cnt) { j = lq[s * 32]; cls = e2_classify(T, P, F, me, lki, j, d2); }
+                            const unsigned bal = __ballot_sync(FULL, cls != 0);
+                            if (cls) {
+                                const int idx = q2n + __popc(bal & ((1u << lane) - 1));
+                                q2ij[idx] = ((unsigned)i << 16) | (unsigned)j; q2cls[idx] = cls; q2d[idx] = d2;
+                            }
+                            q2n += __popc(bal);
+                            __syncwarp();
+                            // ---- E3: bonded / disulfide / hydrogen-angle tests, dedup, counts, records
+                            if (q2n >= 32 || (flush && s + 1 >= rows && q2n > 0)) {
+                                const int nb = min(q2n, 32);
+                                q2n -= nb;
+                                if (lane < nb) {
+                                    const unsigned e = q2ij[q2n + lane];
+                                    e3_finish(T, P, O, F, e >> 16, e & 0xffff, q2cls[q2n + lane], q2d[q2n + lane]);
+                                }
+                                __syncwarp();
+                            }
+                        }
+                        cnt = 0;
+                    }
+                } while (off < maxlen);
+                ++r;
+            } while (r < 5);
+        } while (!final_pass);
         __syncthreads();
     }
 }

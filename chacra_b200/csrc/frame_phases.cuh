@@ -118,15 +118,15 @@ __device__ __forceinline__ void ring_stack_task(const DevTopo& T, const DevParam
 }
 
 // ---- E2: exact float32 d2 and class tests for one prefilter survivor ---------------------------------------
-__device__ __forceinline__ unsigned e2_classify(const DevTopo& T, const DevParams& P, const FrameCtx& F, int i, int j,
-                                                float& d2_out) {
-    float4 a = F.spos[i], b = F.spos[j];
+__device__ __forceinline__ unsigned e2_classify(const DevTopo& T, const DevParams& P, const FrameCtx& F, float4 a, int lka,
+                                                int j, float& d2_out) {
+    float4 b = F.spos[j];
     float d2 = dist2_exact(a.x, a.y, a.z, b.x, b.y, b.z);
     d2_out = d2;
     unsigned wi = __float_as_uint(a.w), wj = __float_as_uint(b.w);
     bool dual = ((wi & I_S1) && (wj & I_S2)) || ((wi & I_S2) && (wj & I_S1));
     if (!dual) return 0u;
-    int dl = abs(F.slk[i] - F.slk[j]);
+    int dl = abs(lka - F.slk[j]);
     int e = (wi & I_ELEM) * T.K + (wj & I_ELEM);
     unsigned cls = 0;
     if (dl >= P.vdw_rd) {
@@ -203,8 +203,13 @@ __device__ __forceinline__ void e3_finish(const DevTopo& T, const DevParams& P, 
     }
     if (cls & C_HB) {
         bool ok = false;
-        if (wi & I_HASH) ok |= hb_direction(T, P, O, F, a, b, pi, ai, aj);
-        if (wj & I_HASH) ok |= hb_direction(T, P, O, F, b, a, pj, aj, ai);
+#pragma unroll 1
+        for (int dir = 0; dir < 2; ++dir) {            // both atoms are tried as donor (one-selection measure hbonds)
+            const unsigned wd = dir ? wj : wi;
+            if (!(wd & I_HASH)) continue;
+            const float4 xd = dir ? b : a, xa = dir ? a : b;
+            ok |= hb_direction(T, P, O, F, xd, xa, dir ? pj : pi, dir ? aj : ai, dir ? ai : aj);
+        }
         if (ok) {
             bool li = wi & I_LIG, lj = wj & I_LIG, bi = wi & I_BB, bj = wj & I_BB;
             int t;

@@ -162,7 +162,9 @@ typedef struct chc_stats {
     int32_t grid;
     int32_t staged;               /* 1: frames are staged through shared memory with bulk async copies */
     int32_t bitset_in_smem;
-    double  last_kernel_ms;       /* main contact kernel of the last chc_submit_frames (needs timing on) */
+    double  last_kernel_ms;       /* main contact kernel of the last timed chc_submit_frames */
+    double  kernel_ms_total;      /* sum over all timed main-kernel launches since chc_set_timing(1) */
+    int64_t timed_launches;
 } chc_stats;
 
 typedef struct chc_ctx chc_ctx;

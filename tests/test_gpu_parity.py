@@ -1,0 +1,114 @@
+"""CUDA path vs the oracle through the C ABI (run with -m gpu on a B200).
+
+Bit-exact bar: identical contact sets per (frame, itype) and identical integer residue-pair frame
+counts (SURVEY A.12 levels L1 and L2); the near-cutoff side channel must list the same observations.
+"""
+import os
+from collections import Counter
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, read_golden_tsv
+
+pytestmark = pytest.mark.gpu
+ALL = ["sb", "pc", "ps", "ts", "vdw", "hb", "hp"]
+
+
+def _engine_run(top_path, frames, itypes, sele1="protein", sele2=None, geometry=None, host=False, **kw):
+    import torch
+    from chacra_b200 import read_pdb, compile_topology
+    from chacra_b200.engine import ContactEngine, ITYPE_NAMES, NEAR_KINDS
+    atoms = read_pdb(top_path)
+    g = geometry or {}
+    topo = compile_topology(atoms, frames[0], sele1, sele2, vdw_res_diff=g.get("VDW_RES_DIFF", 2),
+                            hbond_res_diff=g.get("HBOND_RES_DIFF", 1))
+    eng = ContactEngine(topo, itypes, geometry, emit_contacts=True, track_near=True, **kw)
+    for s in range(0, len(frames), 300):
+        chunk = frames[s:s + 300]
+        eng.submit(chunk if host else torch.from_numpy(chunk).cuda(), 0, s)
+    eng.synchronize()
+    rec = eng.drain_contacts()
+    near, near_total = eng.drain_near()
+    counts = eng.counts(0)
+    contacts = set()
+    for r in rec:
+        a, b = int(r["atom1"]), int(r["atom2"])
+        contacts.add((int(r["frame"]), ITYPE_NAMES[r["itype"]], min(a, b), max(a, b)))
+    assert len(contacts) == len(rec), "the kernel emitted a duplicate record"
+    nears = {(int(r["frame"]), NEAR_KINDS[r["kind"]], min(int(r["atom1"]), int(r["atom2"])),
+              max(int(r["atom1"]), int(r["atom2"]))) for r in near}
+    return dict(engine=eng, topo=topo, records=rec, contacts=contacts, near=nears, counts=counts, near_total=near_total)
+
+
+def _oracle_sets(res):
+    contacts = set()
+    for c in res["contacts"]:
+        if len(c) == 4:
+            contacts.add((c[0], c[1], min(c[2], c[3]), max(c[2], c[3])))
+    nears = {(f, kind, min(a, b), max(a, b)) for f, kind, a, b, _ in res["near"]}   # the oracle lists (i,j) and (j,i)
+    return contacts, nears
+
+
+def _check_counts(run, oracle_res):
+    import getcontacts_oracle as o
+    topo, eng = run["topo"], run["engine"]
+    want = o.intended_counts(oracle_res)
+    rank = {lab: k for k, lab in enumerate(topo.residue_label)}
+    table = np.zeros(eng.n_pairs, np.int64)
+    for (r1, r2), c in want.items():
+        table[int(eng.pair_index(np.array(rank[r1]), np.array(rank[r2])))] = c
+    assert np.array_equal(run["counts"].astype(np.int64), table)
+
+
+def test_5xnd_all_itypes(oracle_5xnd):
+    frames = oracle_5xnd["frames"]
+    run = _engine_run(os.path.join(GOLDEN, "5xnd_topology.pdb"), frames, ALL)
+    want, want_near = _oracle_sets(oracle_5xnd)
+    got = run["contacts"]
+    for it in sorted({c[1] for c in want | got}):
+        w = {c for c in want if c[1] == it}
+        g = {c for c in got if c[1] == it}
+        assert g == w, "%s: missing %s extra %s" % (it, sorted(w - g)[:5], sorted(g - w)[:5])
+    assert run["near"] == want_near
+    _check_counts(run, oracle_5xnd)
+    # --distout: float32 sqrtf(d2) of the two labelled atoms (compute_contacts.py:161-167)
+    for r in run["records"][:2000]:
+        d = frames[r["frame"]][r["atom1"]] - frames[r["frame"]][r["atom2"]]
+        d2 = np.float32(np.float32(d[0] * d[0] + d[1] * d[1]) + d[2] * d[2])
+        assert np.float32(np.sqrt(d2)) == r["distance"]
+
+
+def test_5xnd_matches_reference_golden_file(oracle_5xnd):
+    """Straight against the reference's own expected output (atom labels, not indices)."""
+    from chacra_b200.engine import ITYPE_NAMES
+    run = _engine_run(os.path.join(GOLDEN, "5xnd_topology.pdb"), oracle_5xnd["frames"], ALL, host=True)
+    lab = run["topo"].atoms.atom_labels()
+    got = Counter()
+    for r in run["records"]:
+        a, b = sorted((lab[r["atom1"]], lab[r["atom2"]]))
+        got[(str(r["frame"]), ITYPE_NAMES[r["itype"]], a, b)] += 1
+    gold = Counter(tuple(x[:4]) for x in read_golden_tsv(os.path.join(GOLDEN, "test_5xnd_expected.tsv.gz")))
+    assert got == gold
+
+
+def test_5xnd_salt_bridges_subset_selection():
+    import getcontacts_oracle as o
+    top = os.path.join(GOLDEN, "5xnd_topology.pdb")
+    res = o.run(top, os.path.join(GOLDEN, "5xnd_trajectory.dcd"), ["sb"], sele1="resname ASP LYS", sele2="resname ASP LYS")
+    run = _engine_run(top, res["frames"], ["sb"], "resname ASP LYS", "resname ASP LYS")
+    assert run["contacts"] == _oracle_sets(res)[0]
+    assert {c[0] for c in run["contacts"]} == {1, 2, 3, 4, 5, 8, 12, 13, 15, 16, 18, 19}
+
+
+def test_fragment_boundaries_and_chunking(oracle_5xnd):
+    """250 frames (the 20 fixture frames cycled) = 3 fragments; the hydrophobic set is rebuilt per fragment."""
+    import getcontacts_oracle as o
+    base = oracle_5xnd["frames"]
+    frames = np.ascontiguousarray(base[np.arange(250) % 20][:, :, :])
+    frames[100:200] = base[(np.arange(100) + 7) % 20]
+    top = os.path.join(GOLDEN, "5xnd_topology.pdb")
+    res = o.run(top, top, ["hp", "vdw", "hb"], frames=frames)
+    run = _engine_run(top, frames, ["hp", "vdw", "hb"], host=True)
+    assert run["contacts"] == _oracle_sets(res)[0]
+    _check_counts(run, res)
