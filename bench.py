@@ -249,10 +249,12 @@ def main():
         except Exception:
             pass
         peak, which = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
-        n_main = max(1, st["timed_launches"])
-        avg_ms = st["kernel_ms_total"] / n_main
-        bytes_per_launch = 12.0 * N * F                    # algorithmic: every stored coordinate read once
-        achieved = bytes_per_launch / (avg_ms * 1e-3) / 1e9
+        n_chunks = max(1, st["timed_chunks"])
+        frames_per_chunk = args.steps * S * F / n_chunks          # per rank
+        pair_ms, bin_ms = st["pair_ms_total"] / n_chunks, st["bin_ms_total"] / n_chunks
+        bytes_per_launch = 12.0 * N * frames_per_chunk         # algorithmic: every stored coordinate read once
+        achieved = bytes_per_launch / (pair_ms * 1e-3) / 1e9
+        stream_gbs = bytes_per_launch / (bin_ms * 1e-3) / 1e9
         line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic",
@@ -261,14 +263,20 @@ def main():
                            "l2": "inputs (%.1f GB per GPU) are larger than L2" % (S * F * N * 12 / 1e9),
                            "outputs": "int32 residue-pair frame counts [states][pairs]",
                            "parallelism": "frames sharded, %d rank(s), one int32 all-reduce" % world},
+                # dominant kernel = the pair kernel (fp32-issue / shared-memory bound by construction);
+                # its HBM fraction is reported as the contract asks, the streaming kernel's beside it
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": None, "kernel": "frame_contacts_kernel", "peak_source": which,
-                             "avg_launch_ms": avg_ms, "launches_timed": n_main, "algorithmic_bytes_per_launch": bytes_per_launch,
-                             "kernel_share_of_step": st["kernel_ms_total"] / ms},
+                             "traffic": None, "kernel": "pair_frames_kernel", "peak_source": which,
+                             "avg_launch_ms": pair_ms, "launches_timed": n_chunks, "algorithmic_bytes_per_launch": bytes_per_launch,
+                             "kernel_share_of_step": st["pair_ms_total"] / ms},
+                "roofline_stream": {"bound": "hbm", "achieved": stream_gbs, "peak": peak, "unit": "GB/s", "frac": stream_gbs / peak,
+                                    "traffic": None, "kernel": "bin_frames_kernel", "avg_launch_ms": bin_ms,
+                                    "algorithmic_bytes_per_launch": bytes_per_launch,
+                                    "kernel_share_of_step": st["bin_ms_total"] / ms},
                 "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": int(S * F * N * 12),
                         "d2h_bytes_per_step": int(eng.counts_tensor.numel() * 4), "steps": args.e2e_steps},
                 "gpu_launches": int(launches), "clocks": clocks,
-                "engine": {k: st[k] for k in ("path", "smem_bytes", "threads", "grid", "staged", "bitset_in_smem")}}
+                "engine": {k: st[k] for k in ("path", "smem_bytes", "threads", "grid", "bin_smem_bytes", "bin_grid", "chunk_frames", "record_bytes")}}
         if world == 1 and not args.no_cpu_baseline:
             gen = FrameGenerator(atoms.xyz, 2000, amplitude=state_amplitude(0, S))
             sample = gen.frames(16).numpy()

@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(CSRC, "libchacra_b200.so")
 SOURCES = ["chacra_b200.cu"]
-HEADERS = ["device_types.cuh", "frame_kernel.cuh", "frame_phases.cuh", "frame_main.cuh", "prepass.cuh",
+HEADERS = ["device_types.cuh", "frame_kernel.cuh", "frame_phases.cuh", "bin_kernel.cuh", "pair_kernel.cuh",
            os.path.join("..", "..", "include", "chacra_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-fmad=false", "-std=c++17",
               "-shared", "-Xcompiler", "-fPIC"]
@@ -54,7 +54,7 @@ class ChcTopology(C.Structure):
         ("ring_atoms", i32p), ("ring_res", i32p), ("ring_rep", i32p), ("ring_rep_aux", i32p),
         ("cation_aux", i32p), ("cation_atom", i32p), ("cation_flags", u8p), ("cation_res", i32p),
         ("cation_excl_ring", i32p), ("disulfide", i32p), ("vdw_d2max", f32p), ("vdw_cut", f64p), ("hp_base", i32p),
-        ("atom_class", u8p)]
+        ("atom_class", u8p), ("elem_class", u8p)]
 
 
 class ChcParams(C.Structure):
@@ -70,8 +70,9 @@ class ChcParams(C.Structure):
 class ChcStats(C.Structure):
     _fields_ = [(n, C.c_int64) for n in ("frames_submitted", "kernel_launches", "contacts_emitted",
                                          "contacts_dropped", "near_total")] + \
-               [(n, C.c_int32) for n in ("path", "smem_bytes", "threads", "grid", "staged", "bitset_in_smem")] + \
-               [("last_kernel_ms", C.c_double), ("kernel_ms_total", C.c_double), ("timed_launches", C.c_int64)]
+               [(n, C.c_int32) for n in ("path", "smem_bytes", "threads", "grid", "bin_smem_bytes", "bin_grid")] + \
+               [("chunk_frames", C.c_int64), ("record_bytes", C.c_int64), ("pair_ms_total", C.c_double),
+                ("bin_ms_total", C.c_double), ("timed_chunks", C.c_int64)]
 
 
 # every symbol include/chacra_b200.h declares: name -> (restype, argtypes)

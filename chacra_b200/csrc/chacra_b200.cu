@@ -6,10 +6,11 @@
 #include <cmath>
 #include <vector>
 #include <algorithm>
-#include "frame_main.cuh"
-#include "prepass.cuh"
+#include "bin_kernel.cuh"
+#include "pair_kernel.cuh"
 
-#define THREADS_SMALL 512
+#define BIN_THREADS 256
+#define PAIR_THREADS 768
 #define SMEM_LIMIT (227 * 1024)
 
 struct chc_ctx {
@@ -18,17 +19,23 @@ struct chc_ctx {
     chc_params prm{};
     DevTopo T{};
     DevParams P{};
-    SmemLayout L{};
+    PairLayout L{};
+    BinLayout B{};
+    bool small_path = true;
+    int bin_smem = 0, bin_grid = 0, pair_grid = 0;
+    int64_t chunk_frames = 0;
+    unsigned char* binned = nullptr;
+    unsigned* gstamp = nullptr; unsigned* gstate = nullptr;
     std::vector<void*> dev_allocs;
     int32_t* counts = nullptr; bool counts_owned = false; int64_t n_pairs = 0;
     chc_contact* contacts = nullptr; unsigned long long* contact_n = nullptr;
     chc_near* near = nullptr; unsigned long long* near_n = nullptr;
     unsigned char* hpmask = nullptr; int64_t hpmask_frags = 0;
-    unsigned* gbits = nullptr;
     float* dev_stage[2] = {nullptr, nullptr}; float* pin_stage[2] = {nullptr, nullptr};
     int64_t stage_frames = 0; cudaEvent_t stage_done[2] = {nullptr, nullptr}; cudaEvent_t copied[2] = {nullptr, nullptr}; cudaStream_t copy_stream = nullptr;
     bool timing = false;
-    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_pending, ev_free;   // CUDA-event pairs around main kernels
+    struct Ev3 { cudaEvent_t a, b, c; };
+    std::vector<Ev3> ev_pending, ev_free;   // CUDA events around (bin kernel, pair kernel) of a chunk
     int64_t last_state = -1, next_index = -1;          // for fragment continuation checks
     int hp_last_slot = 0;
     chc_stats st{};
@@ -54,36 +61,53 @@ static int upload(chc_ctx* ctx, const Tp* host, size_t n, const Tp** dev) {
     return CHC_OK;
 }
 
-static int plan_small(chc_ctx* ctx) {
+static size_t al16(size_t v) { return (v + 15) & ~size_t(15); }
+
+// Decide where a frame lives while its pairs are enumerated (shared memory or in place in global memory) and lay
+// out the binned record and the pair kernel's shared memory.
+static int plan(chc_ctx* ctx) {
     const DevTopo& T = ctx->T;
-    SmemLayout& L = ctx->L;
-    const int warps = THREADS_SMALL / 32;
-    auto al = [](size_t v) { return (v + 15) & ~size_t(15); };
+    PairLayout& L = ctx->L;
+    BinLayout& B = ctx->B;
+    const int warps = PAIR_THREADS / 32;
+    if (T.n_pair > MAX_PAIR_ATOMS) return CHC_E_TOO_LARGE;
+    B.off_spos = (int)sizeof(BinHeader);
+    B.off_aux = B.off_spos + 16 * T.n_pair;
+    B.fixed_bytes = (int)al16((size_t)B.off_aux + 12 * (size_t)std::max(T.n_aux, 1));
+    B.off_cells = B.fixed_bytes;
+    const size_t queues = al16(8 * (size_t)warps * Q1_CAP) + al16(16 * (size_t)warps * Q2_CAP);
+    const size_t tables = 2 * al16(4 * (size_t)T.K * T.K) + al16(sizeof(PairMisc));
+    // ~3 cells per pair atom keeps the cells at the cutoff size for protein-like densities
+    size_t want_cells = std::min<size_t>(49152, std::max<size_t>(2048, 3 * (size_t)T.n_pair));
+    const size_t plain_bits = al16(4 * (size_t)((ctx->n_pairs + 31) / 32));
+    ctx->small_path = false;
+    for (size_t cells = std::min<size_t>(want_cells, 16384); cells >= 2048 && cells >= (size_t)T.n_pair; cells -= 1024) {
+        size_t need = 128 + (size_t)B.fixed_bytes + al16(4 * cells) + al16(4 * (size_t)T.n_pair) + plain_bits + queues + tables;
+        if (need <= SMEM_LIMIT) { ctx->small_path = true; want_cells = cells; break; }
+    }
+    if (getenv("CHACRA_FORCE_LARGE")) ctx->small_path = false;     // test hook: exercise the in-place path on small systems
+    B.max_cells = (int)want_cells;
+    B.stride = (long long)((B.off_cells + al16(4 * (size_t)B.max_cells) + 127) & ~size_t(127));
     size_t off = 0;
-    L.off_spos = (int)off; off = al(off + 16 * (size_t)T.n_pair);
-    L.off_slk = (int)off;  off = al(off + 4 * (size_t)T.n_pair);
-    L.off_tmp = (int)off;  off = al(off + 4 * (size_t)T.n_pair);
-    L.off_aux = (int)off;  off = al(off + 12 * (size_t)std::max(T.n_aux, 1));
-    L.off_q1 = (int)off;   off = al(off + 2 * (size_t)warps * LQ_CAP * 32);
-    L.off_q2 = (int)off;   off = al(off + 12 * (size_t)warps * Q2_CAP);
-    L.off_tv = (int)off;   off = al(off + 4 * (size_t)T.K * T.K);
-    L.off_th = (int)off;   off = al(off + 4 * (size_t)T.K * T.K);
-    L.off_misc = (int)off; off = al(off + sizeof(FrameMisc));
-    if (T.n_pair > MAX_PAIR_SMALL || off + 4 * 1024 > SMEM_LIMIT) return CHC_E_TOO_LARGE;
-    L.bits_words = (int)((ctx->n_pairs + 31) / 32);
-    size_t bits_bytes = al(4 * (size_t)L.bits_words);
-    size_t left = SMEM_LIMIT - off;
-    // the cell array wants ~2 cells per pair atom (plus guard cells) to keep cells at the cutoff size
-    size_t want_cells = std::min<size_t>(16384, std::max<size_t>(2048, 3 * (size_t)T.n_pair));
-    L.bits_in_smem = (bits_bytes + 4 * std::min<size_t>(want_cells, 4096) <= left) ? 1 : 0;
-    L.off_bits = (int)off;
-    if (L.bits_in_smem) { off += bits_bytes; left -= bits_bytes; }
-    L.off_cells = (int)off;
-    size_t cells = std::min<size_t>(want_cells, left / 4);
-    if (cells < 1024) return CHC_E_TOO_LARGE;
-    L.max_cells = (int)cells;
-    off = al(off + 4 * cells);
+    if (ctx->small_path) {
+        L.off_rec = (int)off;   off += al16((size_t)B.fixed_bytes); off = (off + 127) & ~size_t(127);
+        L.off_cells = (int)off; off += al16(4 * (size_t)B.max_cells);
+        L.off_lkey = (int)off;  off += al16(4 * (size_t)T.n_pair);
+        L.off_bits = (int)off;  off += plain_bits;
+        L.bits_words = (int)((ctx->n_pairs + 31) / 32);
+    } else {
+        L.off_rec = L.off_cells = L.off_lkey = L.off_bits = 0;
+        if ((ctx->n_pairs + 23) / 24 > 0x7fffffff) return CHC_E_TOO_LARGE;
+        L.bits_words = (int)((ctx->n_pairs + 23) / 24);
+    }
+    L.off_q1 = (int)off; off += al16(8 * (size_t)warps * Q1_CAP);
+    L.off_q2 = (int)off; off += al16(16 * (size_t)warps * Q2_CAP);
+    L.off_tv = (int)off; off += al16(4 * (size_t)T.K * T.K);
+    L.off_th = (int)off; off += al16(4 * (size_t)T.K * T.K);
+    L.off_misc = (int)off; off += al16(sizeof(PairMisc));
     L.total = (int)off;
+    ctx->bin_smem = (int)al16(4 * (size_t)B.max_cells);
+    if ((size_t)L.total > SMEM_LIMIT || (size_t)ctx->bin_smem + 1024 > SMEM_LIMIT) return CHC_E_TOO_LARGE;
     return CHC_OK;
 }
 
@@ -97,15 +121,15 @@ extern "C" void chc_destroy(chc_ctx* ctx) {
     for (void* p : ctx->dev_allocs) cudaFree(p);
     if (ctx->counts_owned) cudaFree(ctx->counts);
     cudaFree(ctx->contacts); cudaFree(ctx->contact_n); cudaFree(ctx->near); cudaFree(ctx->near_n);
-    cudaFree(ctx->hpmask); cudaFree(ctx->gbits);
+    cudaFree(ctx->hpmask); cudaFree(ctx->binned); cudaFree(ctx->gstamp); cudaFree(ctx->gstate);
     for (int k = 0; k < 2; ++k) {
         cudaFree(ctx->dev_stage[k]); if (ctx->pin_stage[k]) cudaFreeHost(ctx->pin_stage[k]);
         if (ctx->stage_done[k]) cudaEventDestroy(ctx->stage_done[k]);
         if (ctx->copied[k]) cudaEventDestroy(ctx->copied[k]);
     }
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
-    for (auto& e : ctx->ev_pending) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
-    for (auto& e : ctx->ev_free) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
+    for (auto& e : ctx->ev_pending) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); cudaEventDestroy(e.c); }
+    for (auto& e : ctx->ev_free) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); cudaEventDestroy(e.c); }
     delete ctx;
 }
 
@@ -161,8 +185,19 @@ extern "C" int chc_create(chc_ctx** out, const chc_topology* t, const chc_params
     if (p->itype_mask & CHC_IT_SB) cmax = std::max(cmax, p->sb_dist);
     if (p->itype_mask & CHC_IT_HB) cmax = std::max(cmax, p->hb_dist);
     P.cell = (float)(cmax * 1.0005 + 1e-3);
-    P.pre2 = (float)(cmax * cmax * (1.0 + 1e-5) + 1e-5);
+    P.pre2 = 0.f;                         // the largest exact float32 cutoff^2 among the enabled pair types
+    if (p->itype_mask & CHC_IT_VDW) P.pre2 = std::max(P.pre2, P.soft2);
+    if (p->itype_mask & CHC_IT_HP) P.pre2 = std::max(P.pre2, P.hp2);
+    if (p->itype_mask & CHC_IT_SB) P.pre2 = std::max(P.pre2, P.sb2);
+    if (p->itype_mask & CHC_IT_HB) P.pre2 = std::max(P.pre2, P.hb2);
     P.hb_angle = (float)p->hb_angle;
+    P.hb_fast = P.hb_angle < 89.0f && P.hb_angle > 1.0f;
+    if (P.hb_fast) {
+        const double t = std::tan((double)P.hb_angle / (double)57.2958f);
+        P.hb_tan_lo = (float)(t * (1.0 - 4e-4)); P.hb_tan_hi = (float)(t * (1.0 + 4e-4));
+    }
+    P.elem_ch_mask = 0;
+    for (int k = 0; k < t->n_elem; ++k) if (t->elem_class && t->elem_class[k]) P.elem_ch_mask |= 1u << k;
     double rmax = std::max(p->pc_dist, std::max(p->ps_dist, p->ts_dist)) + 0.05;
     P.ring_pre2 = (float)(rmax * rmax);
     P.pc_soft2 = sq(10.0); P.ps_soft2 = sq(10.0); P.ts_soft2 = sq(6.0);   // pi_cation.py:22, aromatics.py:26-27
@@ -172,11 +207,29 @@ extern "C" int chc_create(chc_ctx** out, const chc_topology* t, const chc_params
     P.near_d = p->near_dist_tol; P.near_a = p->near_angle_tol;
 
     ctx->n_pairs = (int64_t)T.R * (T.R + 1) / 2;
-    rc = plan_small(ctx);
-    if (rc != CHC_OK) return fail(ctx, rc, "topology with %d pair atoms / %d residues does not fit the one-CTA-per-frame path", T.n_pair, T.R);
-    CK(cudaFuncSetAttribute(frame_contacts_kernel<THREADS_SMALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->L.total));
-    if (!ctx->L.bits_in_smem) {
-        CK(cudaMalloc(&ctx->gbits, (size_t)ctx->sm_count * ctx->L.bits_words * 4));
+    rc = plan(ctx);
+    if (rc != CHC_OK) return fail(ctx, rc, "topology with %d pair atoms / %d residues does not fit any kernel path", T.n_pair, T.R);
+    if (ctx->small_path) CK(cudaFuncSetAttribute(pair_frames_kernel<PAIR_THREADS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->L.total));
+    else CK(cudaFuncSetAttribute(pair_frames_kernel<PAIR_THREADS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->L.total));
+    CK(cudaFuncSetAttribute(bin_frames_kernel<BIN_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->bin_smem));
+    ctx->pair_grid = ctx->sm_count;
+    {
+        int per_sm = 1;
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bin_frames_kernel<BIN_THREADS>, BIN_THREADS, ctx->bin_smem));
+        ctx->bin_grid = ctx->sm_count * std::max(1, per_sm);
+    }
+    // frames per (bin, pair) launch pair: the binned records of a chunk should stay in L2 (126 MB) between the two
+    {
+        int64_t by_l2 = (int64_t)((80u << 20) / (size_t)ctx->B.stride);
+        int64_t g = ctx->pair_grid;
+        ctx->chunk_frames = std::max<int64_t>(g, by_l2 / g * g);
+        if (const char* e = getenv("CHACRA_CHUNK_FRAMES")) ctx->chunk_frames = std::max<int64_t>(1, atoll(e));
+    }
+    CK(cudaMalloc(&ctx->binned, (size_t)ctx->chunk_frames * (size_t)ctx->B.stride));
+    if (!ctx->small_path) {
+        size_t words = (size_t)ctx->pair_grid * (size_t)ctx->L.bits_words;
+        CK(cudaMalloc(&ctx->gstamp, words * 4)); CK(cudaMemset(ctx->gstamp, 0, words * 4));
+        CK(cudaMalloc(&ctx->gstate, (size_t)ctx->pair_grid * 4)); CK(cudaMemset(ctx->gstate, 0, (size_t)ctx->pair_grid * 4));
     }
     CK(cudaMalloc(&ctx->counts, (size_t)p->n_states * ctx->n_pairs * sizeof(int32_t)));
     ctx->counts_owned = true;
@@ -185,8 +238,9 @@ extern "C" int chc_create(chc_ctx** out, const chc_topology* t, const chc_params
     CK(cudaMalloc(&ctx->near_n, 8)); CK(cudaMemset(ctx->near_n, 0, 8));
     CK(cudaMalloc(&ctx->contacts, std::max<int64_t>(p->contact_capacity, 1) * sizeof(chc_contact)));
     CK(cudaMalloc(&ctx->near, std::max<int64_t>(p->near_capacity, 1) * sizeof(chc_near)));
-    ctx->st.path = 1; ctx->st.smem_bytes = ctx->L.total; ctx->st.threads = THREADS_SMALL; ctx->st.staged = 0;
-    ctx->st.bitset_in_smem = ctx->L.bits_in_smem;
+    ctx->st.path = ctx->small_path ? 1 : 2; ctx->st.smem_bytes = ctx->L.total; ctx->st.threads = PAIR_THREADS;
+    ctx->st.grid = ctx->pair_grid; ctx->st.bin_smem_bytes = ctx->bin_smem; ctx->st.bin_grid = ctx->bin_grid;
+    ctx->st.chunk_frames = ctx->chunk_frames; ctx->st.record_bytes = ctx->B.stride;
     return CHC_OK;
 }
 
@@ -261,34 +315,38 @@ extern "C" int chc_submit_frames(chc_ctx* ctx, int state, const float* d_xyz, in
         // the fragment being continued was computed into slot hp_last_slot by the previous call
         CK(cudaMemcpyAsync(ctx->hpmask, ctx->hpmask + (size_t)ctx->hp_last_slot * ctx->T.n_pair, ctx->T.n_pair, cudaMemcpyDeviceToDevice, stream));
     }
-    const int first_g = continues ? 1 : 0;
-    const int n_new = (int)(frag1 - frag0 + 1) - first_g;
-    if ((ctx->P.itypes & CHC_IT_HP) && ctx->T.n_hp_base > 0 && n_new > 0) {
-        const float r = 1.7f;
-        int by = std::max(1, std::min(64, (ctx->T.n_hp_base + 7) / 8));
-        hp_prepass_kernel<<<dim3(n_new, by), 256, 0, stream>>>(ctx->T, r * r, d_xyz, frame_stride, first_index, F, frag0, first_g, ctx->hpmask);
-        CK(cudaGetLastError());
-        ctx->st.kernel_launches++;
-    }
     ctx->hp_last_slot = (int)(frag1 - frag0);
     DevOut O;
     O.counts = ctx->counts + (size_t)state * ctx->n_pairs; O.n_pairs = ctx->n_pairs;
     O.contacts = ctx->contacts; O.contact_n = ctx->contact_n; O.contact_cap = ctx->prm.contact_capacity;
     O.near = ctx->near; O.near_n = ctx->near_n; O.near_cap = ctx->prm.near_capacity;
-    int grid = (int)std::min<int64_t>(n_frames, ctx->sm_count);
-    std::pair<cudaEvent_t, cudaEvent_t> ev{nullptr, nullptr};
-    if (ctx->timing) {
-        if (!ctx->ev_free.empty()) { ev = ctx->ev_free.back(); ctx->ev_free.pop_back(); }
-        else { CK(cudaEventCreate(&ev.first)); CK(cudaEventCreate(&ev.second)); }
-        CK(cudaEventRecord(ev.first, stream));
+    // chunks of frames: the binning kernel streams the coordinates and writes the chunk's binned records, the pair
+    // kernel consumes them (from L2 when the chunk fits)
+    for (int64_t c0 = 0; c0 < n_frames; c0 += ctx->chunk_frames) {
+        const int n = (int)std::min<int64_t>(ctx->chunk_frames, n_frames - c0);
+        const float* x = d_xyz + (size_t)c0 * frame_stride;
+        chc_ctx::Ev3 ev{nullptr, nullptr, nullptr};
+        if (ctx->timing) {
+            if (!ctx->ev_free.empty()) { ev = ctx->ev_free.back(); ctx->ev_free.pop_back(); }
+            else { CK(cudaEventCreate(&ev.a)); CK(cudaEventCreate(&ev.b)); CK(cudaEventCreate(&ev.c)); }
+            CK(cudaEventRecord(ev.a, stream));
+        }
+        bin_frames_kernel<BIN_THREADS><<<std::min(n, ctx->bin_grid), BIN_THREADS, ctx->bin_smem, stream>>>(
+            ctx->T, ctx->P, ctx->B, x, frame_stride, n, first_index + c0, F, frag0, ctx->binned, ctx->hpmask);
+        CK(cudaGetLastError());
+        if (ctx->timing) CK(cudaEventRecord(ev.b, stream));
+        const int grid = std::min(n, ctx->pair_grid);
+        if (ctx->small_path)
+            pair_frames_kernel<PAIR_THREADS, true><<<grid, PAIR_THREADS, ctx->L.total, stream>>>(
+                ctx->T, ctx->P, O, ctx->L, ctx->B, ctx->binned, n, first_index + c0, F, frag0, ctx->hpmask, nullptr, nullptr);
+        else
+            pair_frames_kernel<PAIR_THREADS, false><<<grid, PAIR_THREADS, ctx->L.total, stream>>>(
+                ctx->T, ctx->P, O, ctx->L, ctx->B, ctx->binned, n, first_index + c0, F, frag0, ctx->hpmask, ctx->gstamp, ctx->gstate);
+        CK(cudaGetLastError());
+        if (ctx->timing) { CK(cudaEventRecord(ev.c, stream)); ctx->ev_pending.push_back(ev); }
+        ctx->st.kernel_launches += 2;
     }
-    frame_contacts_kernel<THREADS_SMALL><<<grid, THREADS_SMALL, ctx->L.total, stream>>>(
-        ctx->T, ctx->P, O, ctx->L, d_xyz, frame_stride, (int)n_frames, first_index, F, frag0, ctx->hpmask, ctx->gbits);
-    CK(cudaGetLastError());
-    if (ctx->timing) { CK(cudaEventRecord(ev.second, stream)); ctx->ev_pending.push_back(ev); }
-    ctx->st.kernel_launches++;
     ctx->st.frames_submitted += n_frames;
-    ctx->st.grid = grid;
     ctx->last_state = state; ctx->next_index = first_index + n_frames;
     return CHC_OK;
 }
@@ -393,7 +451,7 @@ extern "C" int chc_drain_near_cutoff(chc_ctx* ctx, chc_near* host_buf, int64_t c
 extern "C" int chc_set_timing(chc_ctx* ctx, int on) {
     if (!ctx) return CHC_E_INVALID;
     ctx->timing = on != 0;
-    if (on) { ctx->st.kernel_ms_total = 0.0; ctx->st.timed_launches = 0; }
+    if (on) { ctx->st.pair_ms_total = 0.0; ctx->st.bin_ms_total = 0.0; ctx->st.timed_chunks = 0; }
     return CHC_OK;
 }
 
@@ -402,10 +460,11 @@ extern "C" int chc_get_stats(chc_ctx* ctx, chc_stats* out) {
     if (!ctx->ev_pending.empty()) {
         CK(cudaSetDevice(ctx->device));
         for (auto& e : ctx->ev_pending) {
-            CK(cudaEventSynchronize(e.second));
+            CK(cudaEventSynchronize(e.c));
             float ms = 0.f;
-            CK(cudaEventElapsedTime(&ms, e.first, e.second));
-            ctx->st.last_kernel_ms = ms; ctx->st.kernel_ms_total += ms; ctx->st.timed_launches++;
+            CK(cudaEventElapsedTime(&ms, e.a, e.b)); ctx->st.bin_ms_total += ms;
+            CK(cudaEventElapsedTime(&ms, e.b, e.c)); ctx->st.pair_ms_total += ms;
+            ctx->st.timed_chunks++;
             ctx->ev_free.push_back(e);
         }
         ctx->ev_pending.clear();

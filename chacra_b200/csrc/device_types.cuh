@@ -15,15 +15,18 @@
 #define I_HASH   (1u << 7)
 #define I_ANION  (1u << 8)
 #define I_CATION (1u << 9)
-#define I_HP1    (1u << 10)   // static: base carbon in sele1; in shared memory: member of H1 for this fragment
-#define I_HP2    (1u << 11)   // static: base carbon in sele2; in shared memory: member of H2 for this fragment
-#define I_LIG    (1u << 12)
-#define I_BB     (1u << 13)
-#define I_CYS    (1u << 14)
-#define I_XBOND  (1u << 15)
-#define I_VDW    (1u << 16)
-#define I_PIDX_SHIFT 17        // the sorted copy keeps the pair index in the bits above the flags
-#define MAX_PAIR_SMALL (1 << 15)
+#define I_HP1    (1u << 10)   // static: base carbon in sele1; in the binned copy: member of H1 for this fragment
+#define I_HP2    (1u << 11)   // static: base carbon in sele2; in the binned copy: member of H2 for this fragment
+#define I_VDW    (1u << 12)
+#define I_SOLV   (1u << 13)
+// the bits below live only in the static table (looked up by pair index in the emit stage)
+#define I_LIG    (1u << 14)
+#define I_BB     (1u << 15)
+#define I_CYS    (1u << 16)
+#define I_XBOND  (1u << 17)
+#define I_PIDX_SHIFT 14        // the binned copy keeps the pair index in the bits above the dynamic flags
+#define I_WMASK  ((1u << I_PIDX_SHIFT) - 1u)
+#define MAX_PAIR_ATOMS (1 << 18)
 
 // pair classes handed from the exact-distance stage to the emit stage
 #define C_VDW   1u
@@ -50,12 +53,14 @@ struct DevTopo {
 
 struct DevParams {
     unsigned itypes;
+    unsigned elem_ch_mask; // bit e set when element class e is carbon or hydrogen (hydrophobics.py:24,39)
     int vdw_rd, hb_rd;
     int emit, track_near;
     float cell;            // cell edge (>= every pair cutoff, padded)
     float pre2;            // padded cmax^2 for the fused prefilter
     float sb2, hb2, hp2, soft2;   // float32(c)*float32(c)
     float hb_angle;        // float32 cutoff of measure hbonds
+    float hb_tan_lo, hb_tan_hi; int hb_fast;   // tangent bracket of the cutoff (frame_phases.cuh hb_direction)
     float ring_pre2;       // conservative centroid prefilter for pc/ps/ts
     float ps_soft2, ts_soft2, pc_soft2;
     double pc_dist, pc_angle, ps_dist, ps_angle, ps_psi, ts_dist, ts_angle, ts_psi;
@@ -68,6 +73,21 @@ struct DevOut {
     long long n_pairs;
     chc_contact* contacts; unsigned long long* contact_n; long long contact_cap;
     chc_near* near; unsigned long long* near_n; long long near_cap;
+};
+
+// ---- binned frames: what the streaming/binning kernel hands to the pair kernel -----------------------
+// One record per frame in a device buffer, every section 16-byte aligned:
+//   BinHeader | spos float4[NP] (cell-sorted x, y, z, flags|pair_index<<14) | aux float[3*NA] | cells int[ncell+1]
+// `cells` are exclusive starts over a padded (nc+2)^3 grid (one guard layer), x fastest.
+struct BinHeader {
+    float org[3]; float inv;
+    int nc[3]; int ncell;
+};
+struct BinLayout {
+    int off_spos, off_aux, off_cells;   // bytes from the start of the record
+    int fixed_bytes;                    // header + spos + aux (multiple of 16): one bulk copy
+    int max_cells;                      // capacity of the cells section (entries incl. the end sentinel)
+    long long stride;                   // bytes per record
 };
 
 __device__ __forceinline__ float dist2_exact(float ax, float ay, float az, float bx, float by, float bz) {

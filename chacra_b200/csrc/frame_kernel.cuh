@@ -1,36 +1,11 @@
-// frame_kernel.cuh -- one CTA per frame: cell list in shared memory + every interaction type.
-//
-// Phases per frame (persistent CTA, frames strided over the grid):
-//   A  bounding box of the pair atoms                      (coordinates from HBM / staging buffer)
-//   B  cell of every pair atom, per-cell counts            (shared-memory atomics = counting sort, pass 1)
-//   C  exclusive scan of the cell counts                   (block scan)
-//   D  scatter into the sorted float4 array, copy aux atoms (counting sort, pass 2), clear the bitset
-//   R  ring interactions pc / ps / ts                      (float prefilter, float64 geometry)
-//   E1 half-shell neighbour enumeration, thread per atom   (fused-multiply prefilter, survivors -> warp queue)
-//   E2 exact float32 d2 + class tests, one survivor per lane
-//   E3 bonded / disulfide / hydrogen-angle tests, residue-pair dedup (bitset), counts, records
+// frame_kernel.cuh -- helpers shared by the binning kernel (bin_kernel.cuh) and the pair kernel (pair_kernel.cuh):
+// ordered-float keys, record emission, per-frame residue-pair de-duplication, bond / disulfide lookups,
+// the float32 hydrogen-bond angle and the float64 ring geometry.
 // Reference semantics: SURVEY.md Appendix A / D; file:line citations are in include/chacra_b200.h.
 #pragma once
 #include "device_types.cuh"
 
-#define Q1_CAP 192
-#define Q2_CAP 64
 #define FULL 0xffffffffu
-
-struct SmemLayout {
-    int off_spos, off_slk, off_tmp, off_aux, off_cells, off_bits, off_q1, off_q2, off_tv, off_th, off_misc;
-    int max_cells;       // capacity of the cell array (entries), <= 16384
-    int bits_words;      // words of the residue-pair bitset
-    int bits_in_smem;
-    int total;
-};
-
-struct FrameMisc {
-    int bb_min[3], bb_max[3];
-    int chunk;            // dynamic work counter of the pair phase
-    int ring_task;
-    int scan_carry[33];
-};
 
 __device__ __forceinline__ int f2ord(float f) { int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7fffffff; }
 __device__ __forceinline__ float ord2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
@@ -59,12 +34,30 @@ __device__ __forceinline__ void emit_near(const DevOut& O, int frame, int kind, 
     }
 }
 
-// set the (ra, rb) bit of this frame's residue-pair set; first setter bumps the frequency count
-__device__ __forceinline__ void count_pair(const DevOut& O, unsigned* bits, int ra, int rb, int R) {
+// Per-frame residue-pair set.  Two encodings of the same idea (first setter of a pair bumps its count):
+//  * plain bitset (shared memory, cleared per frame):            word = idx / 32, bit = idx % 32
+//  * generation-stamped bitset (global memory, one per CTA, never cleared between frames): every word holds
+//    an 8-bit generation in its top byte and 24 pair bits; a word whose generation is stale counts as empty.
+//    The generation runs 1..255 and the table is wiped when it wraps (pair_kernel.cuh).
+__device__ __forceinline__ void count_pair(const DevOut& O, unsigned* bits, unsigned gen, int ra, int rb, int R) {
     long long idx = pair_index(ra, rb, R);
-    unsigned bit = 1u << (idx & 31);
-    unsigned old = atomicOr(&bits[idx >> 5], bit);
-    if (!(old & bit)) atomicAdd(&O.counts[idx], 1);
+    if (gen == 0u) {
+        unsigned bit = 1u << (idx & 31);
+        unsigned old = atomicOr(&bits[idx >> 5], bit);
+        if (!(old & bit)) atomicAdd(&O.counts[idx], 1);
+    } else {
+        unsigned* w = bits + idx / 24;
+        unsigned bit = 1u << (unsigned)(idx % 24);
+        unsigned old = *w;
+        for (;;) {
+            unsigned cur = (old >> 24) == gen ? old : (gen << 24);
+            if (cur & bit) return;
+            unsigned seen = atomicCAS(w, old, cur | bit);
+            if (seen == old) break;
+            old = seen;
+        }
+        atomicAdd(&O.counts[idx], 1);
+    }
 }
 
 __device__ __forceinline__ bool is_bonded(const DevTopo& T, int pi, int atom_j) {

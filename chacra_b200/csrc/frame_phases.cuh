@@ -2,12 +2,14 @@
 #pragma once
 #include "frame_kernel.cuh"
 
-struct FrameCtx {            // per-CTA view of the current frame (all pointers are shared memory)
-    const float4* spos;      // sorted pair atoms: x, y, z, (info | pair_index << 17)
-    const int* slk;          // locality key, same order
+struct FrameCtx {            // per-CTA view of the current frame (shared memory on the small path, global on the large one)
+    const float4* spos;      // cell-sorted pair atoms: x, y, z, (dynamic flags | pair_index << I_PIDX_SHIFT)
+    const int* lkey;         // locality key by pair index
     const float* aux;        // [NA][3] donor hydrogens, ring atoms, cations
-    unsigned* bits;          // residue-pair set of this frame (shared or global)
+    unsigned* bits;          // residue-pair set of this frame
+    unsigned gen;            // 0: plain bitset; 1..255: generation of the stamped bitset
     const float* tv; const float* th;
+    const unsigned char* hm; // hydrophobic membership of this frame's fragment, by pair index (bit0 H1, bit1 H2)
     int frame;               // frame id reported in records
 };
 
@@ -47,7 +49,7 @@ __device__ __forceinline__ void ring_pc_task(const DevTopo& T, const DevParams& 
     double t = fold180(angle_deg(normal3(a, b, cc), v));
     if (P.track_near && fabs(t - P.pc_angle) < P.near_a) emit_near(O, F.frame, CHC_NEAR_PC_ANGLE, catom, rep, t - P.pc_angle);
     if (t > P.pc_angle) return;
-    count_pair(O, F.bits, T.cat_res[c], T.ring_res[r], T.R);
+    count_pair(O, F.bits, F.gen, T.cat_res[c], T.ring_res[r], T.R);
     if (P.emit) {
         const float* pr = F.aux + 3 * T.ring_rep_aux[r];
         emit_contact(O, F.frame, CHC_PC, catom, rep, sqrtf(dist2_exact(xc[0], xc[1], xc[2], pr[0], pr[1], pr[2])));
@@ -108,7 +110,7 @@ __device__ __forceinline__ void ring_stack_task(const DevTopo& T, const DevParam
         if (P.track_near && fabs(psi - pcut) < P.near_a)
             emit_near(O, F.frame, which == 0 ? CHC_NEAR_PS_PSI : CHC_NEAR_TS_PSI, rep1, rep2, psi - pcut);
         if (psi > pcut) continue;
-        count_pair(O, F.bits, T.ring_res[r1], T.ring_res[r2], T.R);
+        count_pair(O, F.bits, F.gen, T.ring_res[r1], T.ring_res[r2], T.R);
         if (P.emit) {
             const float* q1 = F.aux + 3 * T.ring_rep_aux[r1]; const float* q2 = F.aux + 3 * T.ring_rep_aux[r2];
             emit_contact(O, F.frame, which == 0 ? CHC_PS : CHC_TS, rep1, rep2,
@@ -118,15 +120,14 @@ __device__ __forceinline__ void ring_stack_task(const DevTopo& T, const DevParam
 }
 
 // ---- E2: exact float32 d2 and class tests for one prefilter survivor ---------------------------------------
-__device__ __forceinline__ unsigned e2_classify(const DevTopo& T, const DevParams& P, const FrameCtx& F, float4 a, int lka,
-                                                int j, float& d2_out) {
-    float4 b = F.spos[j];
+__device__ __forceinline__ unsigned e2_classify(const DevTopo& T, const DevParams& P, const FrameCtx& F, float4 a, float4 b,
+                                                float& d2_out) {
     float d2 = dist2_exact(a.x, a.y, a.z, b.x, b.y, b.z);
     d2_out = d2;
     unsigned wi = __float_as_uint(a.w), wj = __float_as_uint(b.w);
     bool dual = ((wi & I_S1) && (wj & I_S2)) || ((wi & I_S2) && (wj & I_S1));
     if (!dual) return 0u;
-    int dl = abs(lka - F.slk[j]);
+    int dl = abs(F.lkey[wi >> I_PIDX_SHIFT] - F.lkey[wj >> I_PIDX_SHIFT]);
     int e = (wi & I_ELEM) * T.K + (wj & I_ELEM);
     unsigned cls = 0;
     if (dl >= P.vdw_rd) {
@@ -134,12 +135,19 @@ __device__ __forceinline__ unsigned e2_classify(const DevTopo& T, const DevParam
             if (d2 <= F.tv[e]) cls |= C_VDW;
             if (P.track_near && d2 <= P.soft2 && fabs((double)sqrtf(d2) - T.vcut[e]) < P.near_d) cls |= C_NEARV;
         }
-        if (P.itypes & CHC_IT_HP) {
-            bool hp = T.same ? ((wi & wj & I_HP1) != 0)
-                             : (((wi & I_HP1) && (wj & I_HP2)) || ((wj & I_HP1) && (wi & I_HP2)));
-            if (hp) {
-                if (d2 <= F.th[e]) cls |= C_HP;
-                if (P.track_near && d2 <= P.hp2 && fabs((double)sqrtf(d2) - T.vcut[e]) < P.near_d) cls |= C_NEARH;
+        if ((P.itypes & CHC_IT_HP) && d2 <= P.hp2) {
+            // static base-carbon bits first, then this fragment's membership (hydrophobics.py:8-41)
+            bool base = T.same ? ((wi & wj & I_HP1) != 0)
+                               : (((wi & I_HP1) && (wj & I_HP2)) || ((wj & I_HP1) && (wi & I_HP2)));
+            if (base) {
+                unsigned hi = F.hm[wi >> I_PIDX_SHIFT], hj = F.hm[wj >> I_PIDX_SHIFT];
+                bool hp = T.same ? ((hi & hj & 1u) != 0)
+                                 : (((wi & I_HP1) && (hi & 1u) && (wj & I_HP2) && (hj & 2u)) ||
+                                    ((wj & I_HP1) && (hj & 1u) && (wi & I_HP2) && (hi & 2u)));
+                if (hp) {
+                    if (d2 <= F.th[e]) cls |= C_HP;
+                    if (P.track_near && fabs((double)sqrtf(d2) - T.vcut[e]) < P.near_d) cls |= C_NEARH;
+                }
             }
         }
     }
@@ -149,14 +157,28 @@ __device__ __forceinline__ unsigned e2_classify(const DevTopo& T, const DevParam
     return cls;
 }
 
-// does donor (sorted slot sd) see acceptor (sorted slot sa) under the angle rule, for any of its hydrogens?
+// does donor d see acceptor a under the angle rule, for any of its hydrogens?
+// The reference value is 57.2958f * (float)atan2((double)|u x v|, (double)(u.v)) < cutoff.  atan2 is
+// monotone in |u x v| / (u.v), so away from the cutoff the decision follows from one multiply: P.hb_tan_lo / hb_tan_hi
+// bracket tan(cutoff) by a relative 4e-4 (~7e-3 degree at 70 degrees, far above every rounding step of the exact recipe
+// and above the 1e-3 degree near-cutoff band); only inside the bracket is the exact double-precision atan2 evaluated.
 __device__ __forceinline__ bool hb_direction(const DevTopo& T, const DevParams& P, const DevOut& O, const FrameCtx& F,
                                              float4 d, float4 a, int pd, int atom_d, int atom_a) {
     bool ok = false;
     int hb = T.pair_h_start[pd], he = T.pair_h_start[pd + 1];
     for (int h = hb; h < he; ++h) {
         const float* ph = F.aux + 3 * h;
-        float ang = hbond_angle(d.x, d.y, d.z, ph[0], ph[1], ph[2], a.x, a.y, a.z);
+        const float hx = ph[0], hy = ph[1], hz = ph[2];
+        float ux = hx - d.x, uy = hy - d.y, uz = hz - d.z;
+        float vx = a.x - hx, vy = a.y - hy, vz = a.z - hz;
+        float cx = uy * vz - uz * vy, cy = uz * vx - ux * vz, cz = ux * vy - uy * vx;
+        float psin = sqrtf((cx * cx + cy * cy) + cz * cz);
+        float pcos = (ux * vx + uy * vy) + uz * vz;
+        if (P.hb_fast) {
+            if (pcos > 0.f && psin < pcos * P.hb_tan_lo) { ok = true; continue; }      // surely below the cutoff
+            if (pcos <= 0.f || psin > pcos * P.hb_tan_hi) continue;                    // surely above it
+        }
+        float ang = 57.2958f * (float)atan2((double)psin, (double)pcos);
         if (P.track_near && fabs((double)ang - (double)P.hb_angle) < P.near_a)
             emit_near(O, F.frame, CHC_NEAR_HB_ANGLE, atom_d, atom_a, (double)ang - (double)P.hb_angle);
         ok |= ang < P.hb_angle;
@@ -171,23 +193,24 @@ __device__ __forceinline__ void e3_finish(const DevTopo& T, const DevParams& P, 
     unsigned wi = __float_as_uint(a.w), wj = __float_as_uint(b.w);
     int pi = wi >> I_PIDX_SHIFT, pj = wj >> I_PIDX_SHIFT;
     int ai = T.pair_atom[pi], aj = T.pair_atom[pj];
+    const unsigned si = T.pair_info[pi], sj = T.pair_info[pj];       // static-only bits: ligand, backbone, CYS, xbond
     // directly bonded pairs are excluded by measure contacts / measure hbonds (Appendix A.4, A.5)
-    bool need_bond = (cls & (C_SB | C_HB)) || ((wi & I_XBOND) && (wj & I_XBOND));
+    bool need_bond = (cls & (C_SB | C_HB)) || ((si & I_XBOND) && (sj & I_XBOND));
     if (need_bond && is_bonded(T, pi, aj)) return;
     int ri = T.pair_res[pi], rj = T.pair_res[pj];
     float dist = sqrtf(d2);
     if (cls & (C_VDW | C_HP | C_NEARV | C_NEARH)) {
-        bool ss = (wi & I_CYS) && (wj & I_CYS) && is_disulfide(T, T.pair_resid[pi], T.pair_resid[pj]);
+        bool ss = (si & I_CYS) && (sj & I_CYS) && is_disulfide(T, T.pair_resid[pi], T.pair_resid[pj]);
         if (!ss) {
             int e = (wi & I_ELEM) * T.K + (wj & I_ELEM);
             if (cls & C_NEARV) emit_near(O, F.frame, CHC_NEAR_VDW_DIST, ai, aj, (double)dist - T.vcut[e]);
             if (cls & C_NEARH) emit_near(O, F.frame, CHC_NEAR_HP_DIST, ai, aj, (double)dist - T.vcut[e]);
             if (cls & C_VDW) {
-                count_pair(O, F.bits, ri, rj, T.R);
+                count_pair(O, F.bits, F.gen, ri, rj, T.R);
                 if (P.emit) emit_contact(O, F.frame, CHC_VDW, ai, aj, dist);
             }
             if ((cls & C_HP) && P.emit) {     // hp is not a counted type (get_contact_frequencies.py:107-109)
-                bool li = wi & I_LIG, lj = wj & I_LIG;
+                bool li = si & I_LIG, lj = sj & I_LIG;
                 emit_contact(O, F.frame, (li || lj) ? ((li != lj) ? CHC_HPLP : CHC_HPLL) : CHC_HP, ai, aj, dist);
             }
         }
@@ -195,10 +218,10 @@ __device__ __forceinline__ void e3_finish(const DevTopo& T, const DevParams& P, 
     if (cls & C_SB) {
         // orient as (anion, cation); salt_bridges.py:90-97 appends a plain sb line unless both are ligand atoms
         bool ij = (wi & I_ANION) && (wj & I_CATION);
-        unsigned wa = ij ? wi : wj, wc = ij ? wj : wi;
+        unsigned wa = ij ? si : sj, wc = ij ? sj : si;
         int aa = ij ? ai : aj, ac = ij ? aj : ai;
         bool al = wa & I_LIG, cl = wc & I_LIG;
-        if (!(al && cl)) count_pair(O, F.bits, ri, rj, T.R);
+        if (!(al && cl)) count_pair(O, F.bits, F.gen, ri, rj, T.R);
         if (P.emit) emit_contact(O, F.frame, al ? (cl ? CHC_SBLL : CHC_SBLP) : (cl ? CHC_SBPL : CHC_SB), aa, ac, dist);
     }
     if (cls & C_HB) {
@@ -211,7 +234,7 @@ __device__ __forceinline__ void e3_finish(const DevTopo& T, const DevParams& P, 
             ok |= hb_direction(T, P, O, F, xd, xa, dir ? pj : pi, dir ? aj : ai, dir ? ai : aj);
         }
         if (ok) {
-            bool li = wi & I_LIG, lj = wj & I_LIG, bi = wi & I_BB, bj = wj & I_BB;
+            bool li = si & I_LIG, lj = sj & I_LIG, bi = si & I_BB, bj = sj & I_BB;
             int t;
             if (li && lj) t = CHC_HBLL;
             else if (li) t = bj ? CHC_HBLB : CHC_HBLS;
@@ -219,7 +242,7 @@ __device__ __forceinline__ void e3_finish(const DevTopo& T, const DevParams& P, 
             else if (bi && bj) t = CHC_HBBB;
             else if (!bi && !bj) t = CHC_HBSS;
             else t = CHC_HBSB;
-            if (t != CHC_HBLL) count_pair(O, F.bits, ri, rj, T.R);
+            if (t != CHC_HBLL) count_pair(O, F.bits, F.gen, ri, rj, T.R);
             if (P.emit) emit_contact(O, F.frame, t, ai, aj, dist);
         }
     }

@@ -94,6 +94,7 @@ class ContactEngine:
         t.vdw_cut = _ptr(arr("cut", cut, np.float64), C.c_double)
         t.hp_base = _ptr(arr("hp_base", topo.hp_base_atoms, np.int32), C.c_int32)
         t.atom_class = _ptr(arr("atom_class", topo.elem_is_c, np.uint8), C.c_uint8)
+        t.elem_class = _ptr(arr("elem_class", topo.elem_class, np.uint8), C.c_uint8)
 
         p = _lib.ChcParams()
         p.itype_mask = sum(ITYPE_BITS[x] for x in self.itypes)

@@ -281,11 +281,12 @@ INFO_ANION = 1 << 8
 INFO_CATION = 1 << 9
 INFO_HPB1 = 1 << 10      # hydrophobic base carbon in sele1 (hydrophobics.py:9-11)
 INFO_HPB2 = 1 << 11      # ... in sele2
-INFO_LIGAND = 1 << 12
-INFO_BB = 1 << 13        # atom.py:37-38 is_bb
-INFO_CYS = 1 << 14
-INFO_XBOND = 1 << 15     # has a bond that the residue-distance filters do not already exclude
-INFO_VDW = 1 << 16       # takes part in the vdW search (heavy, in sele1|sele2)
+INFO_VDW = 1 << 12       # takes part in the vdW search (heavy, in sele1|sele2)
+INFO_SOLV = 1 << 13      # solvent heavy atom (water-bridge partner, hbonds.py:64-82)
+INFO_LIGAND = 1 << 14
+INFO_BB = 1 << 15        # atom.py:37-38 is_bb
+INFO_CYS = 1 << 16
+INFO_XBOND = 1 << 17     # has a bond that the residue-distance filters do not already exclude
 
 
 @dataclass
@@ -327,6 +328,7 @@ class CompiledTopology:
     atom_res: np.ndarray = None         # int32 [N] residue-label rank of every atom
     hp_base_atoms: np.ndarray = None    # int32 [NHB] pair-atom indices (into pair_atom) of hydrophobic base carbons
     elem_is_c: np.ndarray = None        # uint8 [N] 1 = element C, 2 = element H, 0 = other (for the 1.7 A rule)
+    elem_class: np.ndarray = None       # uint8 [K] the same code per element class
 
     @property
     def n_atoms(self):
@@ -365,11 +367,13 @@ def compile_topology(atoms: AtomTable, xyz0: np.ndarray | None = None, sele1: st
     nm, rn = atoms.name, atoms.resname
 
     # --- residue-label ranks: frequency keys are the label strings, ordered as Python strings ----------
+    # (only residues that own a selected atom can appear in a contact line; solvent outside the selection would
+    # otherwise blow the pair table up)
     rlab = atoms.residue_labels()
-    uniq = sorted(set(rlab.tolist()))
+    uniq = sorted(set(rlab[either].tolist()))
     rank = {s: k for k, s in enumerate(uniq)}
     ct.residue_label = np.array(uniq, dtype=object)
-    ct.atom_res = np.array([rank[s] for s in rlab], np.int32)
+    ct.atom_res = np.array([rank.get(s, -1) for s in rlab], np.int32)
 
     # --- ion classes (salt_bridges.py:25-30) + ligand ions (contact_utils.py:605-665) -------------------
     anion = ((rn == "ASP") & np.isin(nm, ["OD1", "OD2"])) | ((rn == "GLU") & np.isin(nm, ["OE1", "OE2"])) | \
@@ -402,7 +406,10 @@ def compile_topology(atoms: AtomTable, xyz0: np.ndarray | None = None, sele1: st
 
     # --- element classes & thresholds ------------------------------------------------------------
     vdw_atoms = either & heavy
-    pmask = vdw_atoms | hbu | ((anion | cation) & either & heavy) | (hp_base & either)
+    # atoms that are neither carbon nor hydrogen by ELEMENT decide the 1.7 A hydrophobic-carbon rule whether or
+    # not they are selected, so they join the grid too (they carry no selection bit and never form a contact)
+    not_ch = ~np.isin(atoms.element, ["C", "H"])
+    pmask = vdw_atoms | hbu | ((anion | cation) & either & heavy) | (hp_base & either) | not_ch
     pidx = np.nonzero(pmask)[0]
     symbols = sorted(set(atoms.element[pidx].tolist())) or ["C"]
     if len(symbols) > 15:
@@ -447,6 +454,7 @@ def compile_topology(atoms: AtomTable, xyz0: np.ndarray | None = None, sele1: st
     ct.hp_base_atoms = np.nonzero((ct.pair_info & (INFO_HPB1 | INFO_HPB2)) != 0)[0].astype(np.int32)
     el = atoms.element
     ct.elem_is_c = np.where(el == "C", 1, np.where(el == "H", 2, 0)).astype(np.uint8)
+    ct.elem_class = np.array([1 if s == "C" else (2 if s == "H" else 0) for s in symbols], np.uint8)
 
     # --- aux atoms: polar hydrogens, ring atoms, pi-cation cations -------------------------------------
     # slots [0, NH) hold the donor hydrogens in CSR order (pair_h_start), the rest are handed out on demand

@@ -129,6 +129,7 @@ typedef struct chc_topology {
     const double*   vdw_cut;          /* [K][K] r1+r2+eps */
     const int32_t*  hp_base;          /* [n_hp_base] pair indices of hydrophobic base carbons */
     const uint8_t*  atom_class;       /* [n_atoms] 1 = element C, 2 = element H, 0 = other */
+    const uint8_t*  elem_class;       /* [K] the same code per element class of the pair atoms */
 } chc_topology;
 
 typedef struct chc_params {
@@ -152,19 +153,21 @@ typedef struct chc_params {
 
 typedef struct chc_stats {
     int64_t frames_submitted;
-    int64_t kernel_launches;      /* contact kernels + prepass kernels launched so far */
+    int64_t kernel_launches;      /* binning + pair kernels launched so far */
     int64_t contacts_emitted;     /* including dropped ones */
     int64_t contacts_dropped;     /* beyond contact_capacity */
     int64_t near_total;
-    int32_t path;                 /* 1 = one CTA per frame (shared-memory cell list) */
-    int32_t smem_bytes;
-    int32_t threads;
-    int32_t grid;
-    int32_t staged;               /* 1: frames are staged through shared memory with bulk async copies */
-    int32_t bitset_in_smem;
-    double  last_kernel_ms;       /* main contact kernel of the last timed chc_submit_frames */
-    double  kernel_ms_total;      /* sum over all timed main-kernel launches since chc_set_timing(1) */
-    int64_t timed_launches;
+    int32_t path;                 /* 1 = frame staged in shared memory by bulk async copy, 2 = read in place (large systems) */
+    int32_t smem_bytes;           /* pair kernel, dynamic shared memory per CTA */
+    int32_t threads;              /* pair kernel */
+    int32_t grid;                 /* pair kernel */
+    int32_t bin_smem_bytes;       /* binning kernel */
+    int32_t bin_grid;
+    int64_t chunk_frames;         /* frames per (binning, pair) launch pair */
+    int64_t record_bytes;         /* binned record per frame */
+    double  pair_ms_total;        /* CUDA-event time of the pair kernels since chc_set_timing(1) */
+    double  bin_ms_total;         /* ... of the binning kernels */
+    int64_t timed_chunks;
 } chc_stats;
 
 typedef struct chc_ctx chc_ctx;

@@ -30,10 +30,13 @@ def main():
         eng.submit(x, 0, 0)
     eng.synchronize()
     st = eng.stats()
-    ms = st["kernel_ms_total"] / st["timed_launches"]
-    print("frames %d atoms %d: %.3f ms/launch, %.0f frames/s, %.2f us/frame/SM, smem %d, pairs/frame %.1f" % (
-        a.frames, atoms.n, ms, a.frames / ms * 1e3, ms * 1e3 / (a.frames / 148.0), st["smem_bytes"],
-        float(eng.counts(0).sum()) / a.frames / a.launches))
+    pair_ms, bin_ms = st["pair_ms_total"] / a.launches, st["bin_ms_total"] / a.launches
+    ms = pair_ms + bin_ms
+    print("frames %d atoms %d path %d: pair %.3f ms + bin %.3f ms per pass, %.0f frames/s, pair %.2f us/frame/SM, "
+          "bin %.0f GB/s, smem %d, chunk %d, record %d B, pairs/frame %.1f" % (
+              a.frames, atoms.n, st["path"], pair_ms, bin_ms, a.frames / ms * 1e3, pair_ms * 1e3 / (a.frames / 148.0),
+              12.0 * atoms.n * a.frames / (bin_ms * 1e-3) / 1e9, st["smem_bytes"], st["chunk_frames"], st["record_bytes"],
+              float(eng.counts(0).sum()) / a.frames / a.launches))
 
 
 if __name__ == "__main__":
