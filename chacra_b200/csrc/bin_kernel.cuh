@@ -8,8 +8,8 @@
 //   2  per-cell counts                            (shared-memory atomics)
 //   3  exclusive scan                             (block scan)
 //   4  scatter to the sorted float4 array in HBM/L2, aux atoms, cell starts, header
-//   5  only on the first frame of a 100-frame fragment: hydrophobic carbon membership (hydrophobics.py:8-41),
-//      a 1.7 A radius query on the freshly built grid.
+// hp_mask_kernel (below) then runs a 1.7 A radius query on the grid of every frame that opens a 100-frame
+// fragment: the hydrophobic carbon membership of that fragment (hydrophobics.py:8-41).
 // Algorithmic HBM traffic: 12 B x n_atoms read per frame (every 32-byte sector of the frame is touched once:
 // heavy atoms and hydrogens interleave), plus the binned record written once.
 #pragma once
@@ -25,8 +25,11 @@ struct BinShared {
     int scan_carry[33];
 };
 
-template <int THREADS>
-__global__ void __launch_bounds__(THREADS)
+// APT > 0: every thread keeps its (at most APT) pair atoms' coordinates in registers, so a frame is read from HBM
+// exactly once with 3*APT independent loads in flight per thread; APT == 0: three gather passes (large systems; the
+// second and third pass hit L2).
+template <int THREADS, int APT, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB)
 bin_frames_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__ xyz, long long frame_stride, int n_frames,
                   long long first_index, int frag_frames, long long frag0, unsigned char* __restrict__ binned,
                   unsigned char* __restrict__ hpmask) {
@@ -34,6 +37,16 @@ bin_frames_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__
     __shared__ BinShared M;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int NP = T.n_pair;
+    constexpr int NR = APT > 0 ? APT : 1;
+    int r_atom[NR];
+    float rx[NR], ry[NR], rz[NR];
+    if (APT > 0) {
+#pragma unroll
+        for (int k = 0; k < NR; ++k) {
+            const int p = tid + k * THREADS;
+            r_atom[k] = p < NP ? T.pair_atom[p] : -1;
+        }
+    }
     for (int f = blockIdx.x; f < n_frames; f += gridDim.x) {
         const float* __restrict__ X = xyz + (size_t)f * frame_stride;
         unsigned char* rec = binned + (size_t)f * B.stride;
@@ -45,10 +58,26 @@ bin_frames_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__
         // ---- 1: bounding box --------------------------------------------------------------------------
         {
             float lo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, hi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
-            for (int p = tid; p < NP; p += THREADS) {
-                const float* q = X + 3 * (size_t)T.pair_atom[p];
+            if (APT > 0) {
 #pragma unroll
-                for (int d = 0; d < 3; ++d) { float v = q[d]; lo[d] = fminf(lo[d], v); hi[d] = fmaxf(hi[d], v); }
+                for (int k = 0; k < NR; ++k)
+                    if (r_atom[k] >= 0) {
+                        const float* q = X + 3 * (size_t)r_atom[k];
+                        rx[k] = q[0]; ry[k] = q[1]; rz[k] = q[2];
+                    }
+#pragma unroll
+                for (int k = 0; k < NR; ++k)
+                    if (r_atom[k] >= 0) {
+                        lo[0] = fminf(lo[0], rx[k]); hi[0] = fmaxf(hi[0], rx[k]);
+                        lo[1] = fminf(lo[1], ry[k]); hi[1] = fmaxf(hi[1], ry[k]);
+                        lo[2] = fminf(lo[2], rz[k]); hi[2] = fmaxf(hi[2], rz[k]);
+                    }
+            } else {
+                for (int p = tid; p < NP; p += THREADS) {
+                    const float* q = X + 3 * (size_t)T.pair_atom[p];
+#pragma unroll
+                    for (int d = 0; d < 3; ++d) { float v = q[d]; lo[d] = fminf(lo[d], v); hi[d] = fmaxf(hi[d], v); }
+                }
             }
 #pragma unroll
             for (int d = 0; d < 3; ++d) {
@@ -75,11 +104,22 @@ bin_frames_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__
         for (int c = tid; c < ncell; c += THREADS) cells[c] = 0;
         __syncthreads();
         // ---- 2: count ---------------------------------------------------------------------------------
-        for (int p = tid; p < NP; p += THREADS) {
-            const float* q = X + 3 * (size_t)T.pair_atom[p];
-            int c = (cell_of(q[2], org[2], inv, nc[2]) + 1) * pxy + (cell_of(q[1], org[1], inv, nc[1]) + 1) * px +
-                    cell_of(q[0], org[0], inv, nc[0]) + 1;
-            atomicAdd(&cells[c], 1);
+        int r_cell[NR];
+        if (APT > 0) {
+#pragma unroll
+            for (int k = 0; k < NR; ++k)
+                if (r_atom[k] >= 0) {
+                    r_cell[k] = (cell_of(rz[k], org[2], inv, nc[2]) + 1) * pxy + (cell_of(ry[k], org[1], inv, nc[1]) + 1) * px +
+                                cell_of(rx[k], org[0], inv, nc[0]) + 1;
+                    atomicAdd(&cells[r_cell[k]], 1);
+                }
+        } else {
+            for (int p = tid; p < NP; p += THREADS) {
+                const float* q = X + 3 * (size_t)T.pair_atom[p];
+                int c = (cell_of(q[2], org[2], inv, nc[2]) + 1) * pxy + (cell_of(q[1], org[1], inv, nc[1]) + 1) * px +
+                        cell_of(q[0], org[0], inv, nc[0]) + 1;
+                atomicAdd(&cells[c], 1);
+            }
         }
         __syncthreads();
         // ---- 3: exclusive scan over the cells --------------------------------------------------------------
@@ -105,13 +145,23 @@ bin_frames_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__
         }
         __syncthreads();
         // ---- 4: scatter (cells[c] becomes the END of cell c), aux atoms, header ----------------------------------
-        for (int p = tid; p < NP; p += THREADS) {
-            const float* q = X + 3 * (size_t)T.pair_atom[p];
-            const float x = q[0], y = q[1], z = q[2];
-            int c = (cell_of(z, org[2], inv, nc[2]) + 1) * pxy + (cell_of(y, org[1], inv, nc[1]) + 1) * px +
-                    cell_of(x, org[0], inv, nc[0]) + 1;
-            int dst = atomicAdd(&cells[c], 1);
-            spos[dst] = make_float4(x, y, z, __uint_as_float((T.pair_info[p] & I_WMASK) | ((unsigned)p << I_PIDX_SHIFT)));
+        if (APT > 0) {
+#pragma unroll
+            for (int k = 0; k < NR; ++k)
+                if (r_atom[k] >= 0) {
+                    const int p = tid + k * THREADS;
+                    const int dst = atomicAdd(&cells[r_cell[k]], 1);
+                    spos[dst] = make_float4(rx[k], ry[k], rz[k], __uint_as_float((T.pair_info[p] & I_WMASK) | ((unsigned)p << I_PIDX_SHIFT)));
+                }
+        } else {
+            for (int p = tid; p < NP; p += THREADS) {
+                const float* q = X + 3 * (size_t)T.pair_atom[p];
+                const float x = q[0], y = q[1], z = q[2];
+                int c = (cell_of(z, org[2], inv, nc[2]) + 1) * pxy + (cell_of(y, org[1], inv, nc[1]) + 1) * px +
+                        cell_of(x, org[0], inv, nc[0]) + 1;
+                int dst = atomicAdd(&cells[c], 1);
+                spos[dst] = make_float4(x, y, z, __uint_as_float((T.pair_info[p] & I_WMASK) | ((unsigned)p << I_PIDX_SHIFT)));
+            }
         }
         for (int s = tid; s < T.n_aux; s += THREADS) {
             const float* q = X + 3 * (size_t)T.aux_atom[s];
@@ -126,44 +176,67 @@ bin_frames_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__
         }
         __syncthreads();
         for (int c = tid; c < ncell; c += THREADS) cells_out[c + 1] = cells[c];
-        // ---- 5: hydrophobic carbon sets of the fragment this frame opens ------------------------------------------
-        const long long gidx = first_index + f;
-        if ((P.itypes & CHC_IT_HP) && gidx % frag_frames == 0) {
-            unsigned char* hm = hpmask + (size_t)(gidx / frag_frames - frag0) * NP;
-            const float r2 = 1.7f * 1.7f;
-            for (int b = tid; b < T.n_hp_base; b += THREADS) {
-                const int p = T.hp_base[b];
-                const float* q = X + 3 * (size_t)T.pair_atom[p];
-                const float x = q[0], y = q[1], z = q[2];
-                const int c0 = (cell_of(z, org[2], inv, nc[2]) + 1) * pxy + (cell_of(y, org[1], inv, nc[1]) + 1) * px +
-                               cell_of(x, org[0], inv, nc[0]) + 1;
-                bool other = false;       // an atom that is neither carbon nor hydrogen within 1.7 A
-                for (int dz = -1; dz <= 1; ++dz)
-                    for (int dy = -1; dy <= 1; ++dy) {
-                        const int base = c0 + dy * px + dz * pxy;
-                        const int jb = base >= 2 ? cells[base - 2] : 0, je = cells[base + 1];   // cells[] holds ENDS: start of base-1 .. end of base+1
-                        for (int j = jb; j < je; ++j) {
-                            const float4 o = __ldcg(spos + j);
-                            if (dist2_exact(o.x, o.y, o.z, x, y, z) <= r2 && !((P.elem_ch_mask >> (__float_as_uint(o.w) & I_ELEM)) & 1u))
-                                other = true;
-                        }
-                    }
-                unsigned sub = other ? 0u : 1u;
-                unsigned eq = 0u;
-                if (!T.same && sub) {
-                    // sele2 wants the element set to EQUAL {C, H} (hydrophobics.py:39): a hydrogen must be in range too.
-                    // Hydrogens are not in the grid; rare path (ChACRA always passes equal selections): linear scan.
-                    bool hyd = false;
-                    for (int a = 0; a < T.n_atoms && !hyd; ++a)
-                        if (T.atom_class[a] == 2) {
-                            const float* h = X + 3 * (size_t)a;
-                            hyd = dist2_exact(h[0], h[1], h[2], x, y, z) <= r2;
-                        }
-                    eq = hyd ? 2u : 0u;
-                }
-                hm[p] = (unsigned char)(sub | eq);
-            }
-        }
         __syncthreads();
+    }
+}
+
+// ---- hydrophobic carbon sets -------------------------------------------------------------------------------
+// The reference recomputes, for every 100-frame fragment, which carbons of ALA PHE GLY ILE LEU PRO VAL TRP (or ligand)
+// have only C/H atoms within 1.7 A in that fragment's FIRST frame (hydrophobics.py:8-41); sele1 uses a
+// subset test, sele2 an equality test against {C, H}.  Every atom that is neither C nor H by element is a pair atom
+// (topology.py), so the subset test is a radius query on the frame's grid: one warp per base carbon, lanes over the
+// nine 3-cell rows around it.  blockIdx.x = k-th fragment-opening frame of the chunk.
+__global__ void __launch_bounds__(256)
+hp_mask_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__ xyz, long long frame_stride, int n_frames,
+               long long first_index, int frag_frames, long long frag0, const unsigned char* __restrict__ binned,
+               unsigned char* __restrict__ hpmask) {
+    const int f0 = (int)((frag_frames - first_index % frag_frames) % frag_frames);
+    const long long f = f0 + (long long)blockIdx.x * frag_frames;
+    if (f >= n_frames) return;
+    const long long gidx = first_index + f;
+    const float* __restrict__ X = xyz + (size_t)f * frame_stride;
+    const unsigned char* rec = binned + (size_t)f * B.stride;
+    const BinHeader h = *reinterpret_cast<const BinHeader*>(rec);
+    const float4* spos = reinterpret_cast<const float4*>(rec + B.off_spos);
+    const int* cells = reinterpret_cast<const int*>(rec + B.off_cells);
+    unsigned char* hm = hpmask + (size_t)(gidx / frag_frames - frag0) * T.n_pair;
+    const int px = h.nc[0] + 2, pxy = px * (h.nc[1] + 2);
+    const int lane = threadIdx.x & 31, warps = blockDim.x >> 5;
+    const float r2 = 1.7f * 1.7f;
+    for (int b = blockIdx.y * warps + (threadIdx.x >> 5); b < T.n_hp_base; b += gridDim.y * warps) {
+        const int p = T.hp_base[b];
+        const float* q = X + 3 * (size_t)T.pair_atom[p];
+        const float x = q[0], y = q[1], z = q[2];
+        const int c0 = (cell_of(z, h.org[2], h.inv, h.nc[2]) + 1) * pxy + (cell_of(y, h.org[1], h.inv, h.nc[1]) + 1) * px +
+                       cell_of(x, h.org[0], h.inv, h.nc[0]) + 1;
+        unsigned other = 0u;          // an atom that is neither carbon nor hydrogen within 1.7 A
+        int jb[9], je[9];
+#pragma unroll
+        for (int r = 0; r < 9; ++r) {               // all eighteen bounds first: independent loads
+            const int base = c0 + (r % 3 - 1) * px + (r / 3 - 1) * pxy;
+            jb[r] = cells[base - 1]; je[r] = cells[base + 2];
+        }
+#pragma unroll
+        for (int r = 0; r < 9; ++r)
+            for (int j = jb[r] + lane; j < je[r]; j += 32) {
+                const float4 o = spos[j];
+                if (dist2_exact(o.x, o.y, o.z, x, y, z) <= r2 && !((P.elem_ch_mask >> (__float_as_uint(o.w) & I_ELEM)) & 1u))
+                    other = 1u;
+            }
+        other = __reduce_or_sync(FULL, other);
+        const unsigned sub = other ? 0u : 1u;
+        unsigned eq = 0u;
+        if (!T.same && sub) {
+            // sele2 wants the element set to EQUAL {C, H} (hydrophobics.py:39): a hydrogen must be in range too.
+            // Hydrogens are not in the grid; ChACRA always passes equal selections, so this scan is the rare path.
+            unsigned hyd = 0u;
+            for (int a = lane; a < T.n_atoms; a += 32)
+                if (T.atom_class[a] == 2) {
+                    const float* hq = X + 3 * (size_t)a;
+                    if (dist2_exact(hq[0], hq[1], hq[2], x, y, z) <= r2) hyd = 1u;
+                }
+            eq = __reduce_or_sync(FULL, hyd) ? 2u : 0u;
+        }
+        if (lane == 0) hm[p] = (unsigned char)(sub | eq);
     }
 }

@@ -9,7 +9,6 @@
 #include "bin_kernel.cuh"
 #include "pair_kernel.cuh"
 
-#define BIN_THREADS 256
 #define PAIR_THREADS 768
 #define SMEM_LIMIT (227 * 1024)
 
@@ -22,7 +21,7 @@ struct chc_ctx {
     PairLayout L{};
     BinLayout B{};
     bool small_path = true;
-    int bin_smem = 0, bin_grid = 0, pair_grid = 0;
+    int bin_smem = 0, bin_grid = 0, pair_grid = 0, bin_threads = 256, bin_variant = 0;
     int64_t chunk_frames = 0;
     unsigned char* binned = nullptr;
     unsigned* gstamp = nullptr; unsigned* gstate = nullptr;
@@ -59,6 +58,14 @@ static int upload(chc_ctx* ctx, const Tp* host, size_t n, const Tp** dev) {
     else CK(cudaMemset(d, 0, bytes));
     *dev = static_cast<const Tp*>(d);
     return CHC_OK;
+}
+
+static const void* bin_kernel_fn(int variant, int* threads) {
+    switch (variant) {
+        case 1: if (threads) *threads = 512; return (const void*)bin_frames_kernel<512, 8, 2>;
+        case 2: if (threads) *threads = 1024; return (const void*)bin_frames_kernel<1024, 8, 1>;
+        default: if (threads) *threads = 256; return (const void*)bin_frames_kernel<256, 0, 1>;
+    }
 }
 
 static size_t al16(size_t v) { return (v + 15) & ~size_t(15); }
@@ -211,11 +218,15 @@ extern "C" int chc_create(chc_ctx** out, const chc_topology* t, const chc_params
     if (rc != CHC_OK) return fail(ctx, rc, "topology with %d pair atoms / %d residues does not fit any kernel path", T.n_pair, T.R);
     if (ctx->small_path) CK(cudaFuncSetAttribute(pair_frames_kernel<PAIR_THREADS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->L.total));
     else CK(cudaFuncSetAttribute(pair_frames_kernel<PAIR_THREADS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->L.total));
-    CK(cudaFuncSetAttribute(bin_frames_kernel<BIN_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->bin_smem));
+    // binning kernel variant: registers hold the frame's pair atoms when they fit (one HBM pass), else three gather passes
+    ctx->bin_variant = T.n_pair <= 512 * 8 ? 1 : (T.n_pair <= 1024 * 8 ? 2 : 0);
+    if (getenv("CHACRA_BIN_VARIANT")) ctx->bin_variant = atoi(getenv("CHACRA_BIN_VARIANT"));
+    const void* bin_fn = bin_kernel_fn(ctx->bin_variant, &ctx->bin_threads);
+    CK(cudaFuncSetAttribute(bin_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->bin_smem));
     ctx->pair_grid = ctx->sm_count;
     {
         int per_sm = 1;
-        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bin_frames_kernel<BIN_THREADS>, BIN_THREADS, ctx->bin_smem));
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bin_fn, ctx->bin_threads, ctx->bin_smem));
         ctx->bin_grid = ctx->sm_count * std::max(1, per_sm);
     }
     // frames per (bin, pair) launch pair: the binned records of a chunk should stay in L2 (126 MB) between the two
@@ -331,9 +342,25 @@ extern "C" int chc_submit_frames(chc_ctx* ctx, int state, const float* d_xyz, in
             else { CK(cudaEventCreate(&ev.a)); CK(cudaEventCreate(&ev.b)); CK(cudaEventCreate(&ev.c)); }
             CK(cudaEventRecord(ev.a, stream));
         }
-        bin_frames_kernel<BIN_THREADS><<<std::min(n, ctx->bin_grid), BIN_THREADS, ctx->bin_smem, stream>>>(
-            ctx->T, ctx->P, ctx->B, x, frame_stride, n, first_index + c0, F, frag0, ctx->binned, ctx->hpmask);
+        {
+            int nn = n; long long fi = first_index + c0, fs = frame_stride, fr0 = frag0; int ff = F;
+            void* args[] = {&ctx->T, &ctx->P, &ctx->B, &x, &fs, &nn, &fi, &ff, &fr0, &ctx->binned, &ctx->hpmask};
+            CK(cudaLaunchKernel(bin_kernel_fn(ctx->bin_variant, nullptr), dim3(std::min(n, ctx->bin_grid)), dim3(ctx->bin_threads),
+                                args, ctx->bin_smem, stream));
+        }
         CK(cudaGetLastError());
+        if ((ctx->P.itypes & CHC_IT_HP) && ctx->T.n_hp_base > 0) {
+            const int64_t fi = first_index + c0;
+            const int64_t f0 = (F - fi % F) % F;                  // first fragment-opening frame of the chunk
+            if (f0 < n) {
+                const int n_open = (int)((n - f0 + F - 1) / F);
+                const int by = std::max(1, std::min(1024, (ctx->T.n_hp_base + 7) / 8));     // one base carbon per warp
+                hp_mask_kernel<<<dim3(n_open, by), 256, 0, stream>>>(ctx->T, ctx->P, ctx->B, x, frame_stride, n, fi, F, frag0,
+                                                                     ctx->binned, ctx->hpmask);
+                CK(cudaGetLastError());
+                ctx->st.kernel_launches++;
+            }
+        }
         if (ctx->timing) CK(cudaEventRecord(ev.b, stream));
         const int grid = std::min(n, ctx->pair_grid);
         if (ctx->small_path)

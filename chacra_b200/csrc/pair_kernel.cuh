@@ -17,6 +17,7 @@
 
 #define Q1_CAP 64           // (i, j) survivors per warp
 #define Q2_CAP 64           // classified pairs per warp
+#define CELL_BLK 8          // cells a warp claims at a time (small blocks keep the end-of-frame tail short)
 
 struct PairLayout {         // shared-memory plan of the pair kernel (bytes)
     int off_rec;            // SMALL: header | spos | aux  (B.fixed_bytes)
@@ -30,7 +31,7 @@ struct PairLayout {         // shared-memory plan of the pair kernel (bytes)
 
 struct PairMisc {
     unsigned long long bar;     // mbarrier of the bulk copies
-    int cursor;                 // next block of 32 cells
+    int cursor;                 // next block of CELL_BLK cells
     int pad;
 };
 
@@ -149,13 +150,14 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                     if (jj >= J) {                     // next non-empty cell
                         while (blk_mask == 0u) {
                             int base = 0;
-                            if (lane == 0) base = atomicAdd(&M->cursor, 32);
+                            if (lane == 0) base = atomicAdd(&M->cursor, CELL_BLK);
                             base = __shfl_sync(FULL, base, 0);
                             if (base >= ncell) { exhausted = true; break; }
                             blk_base = base;
                             const int c = base + lane;
-                            my_cs = c < ncell ? cells[c] : 0;
-                            my_ce = c < ncell ? cells[c + 1] : 0;
+                            const bool mine = lane < CELL_BLK && c < ncell;
+                            my_cs = mine ? cells[c] : 0;
+                            my_ce = mine ? cells[c + 1] : 0;
                             blk_mask = __ballot_sync(FULL, my_ce > my_cs);
                         }
                         if (exhausted) break;
