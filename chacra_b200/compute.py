@@ -1,0 +1,86 @@
+"""``compute_contacts``: the reference's Python entry point for the path, same signature and file output
+(``external/getcontacts/contact_calc/compute_contacts.py:187-293``), with the frames processed by the CUDA
+kernels behind ``libchacra_b200.so`` instead of VMD worker processes.
+
+What stays on the host: argument handling, the one-off topology compilation (the reference's setup block
+:226-238), reading trajectory fragments, and turning device records into text (:306-359).
+"""
+from __future__ import annotations
+
+import math
+import sys
+
+import numpy as np
+
+from .engine import ContactEngine, ChacraError, COMPUTE_ORDER, TRAJ_FRAG_SIZE
+from .topology import read_pdb, compile_topology
+from .trajectory import open_trajectory
+from .tsv import ContactWriter, header_lines
+
+# frames handed to the device per round trip: whole fragments, bounded by the record buffer
+_RECORD_CAPACITY = 1 << 23
+
+
+def compute_contacts(top, traj, output, itypes, geom_criterion_values, cores, beg, end, stride, distout,
+                     ligand_sele, solv_sele, lipid_sele, sele1, sele2, device=0, frequency_output=None):
+    """Compute the contact list of ``traj`` and write it to ``output`` (contact-list TSV).
+
+    ``cores`` is accepted for interface compatibility (the reference uses it as the number of VMD worker
+    processes, :267); one GPU replaces them.  ``frequency_output`` (extension): also write the residue-pair
+    frequency table straight from the device count table (intended counts, SURVEY A.12 level L2).
+    """
+    geom = dict(geom_criterion_values or {})
+    itypes = list(itypes)
+    sele2 = sele1 if sele2 is None else sele2
+    atoms = read_pdb(top)
+    trj = open_trajectory(traj)
+    if trj.n_atoms != atoms.n:
+        raise ChacraError("topology has %d atoms but the trajectory has %d" % (atoms.n, trj.n_atoms))
+    sim_length = trj.n_frames
+    xyz0 = trj.read(0, 0)[0]
+    topo = compile_topology(atoms, xyz0, sele1, sele2, solv_sele or "", lipid_sele or "", ligand_sele or "",
+                            vdw_res_diff=int(geom.get("VDW_RES_DIFF", 2)), hbond_res_diff=int(geom.get("HBOND_RES_DIFF", 1)))
+    if not topo.sele1.any():                              # compute_contacts.py:240-245
+        print("The --sele selection is empty!")
+        sys.exit(1)
+    if not topo.sele2.any():
+        print("The --sele2 selection is empty!")
+        sys.exit(1)
+    end = sys.maxsize if end is None else end
+    beg = max(min(beg, sim_length - 1), 0)                # :247-249
+    end = min(max(end, beg), sim_length - 1)
+    stride = max(1, stride)
+    total_frames = math.ceil((end - beg + 1) / stride)
+    num_fragments = math.ceil((end - beg + 1) / (TRAJ_FRAG_SIZE * stride))
+    print("Processing %s (frame %d to %d with stride of %d) as %d fragments\n" % (traj, beg, end, stride, num_fragments))
+
+    kernel_itypes = [t for t in COMPUTE_ORDER if t in itypes]
+    eng = ContactEngine(topo, kernel_itypes, geom, n_states=1, emit_contacts=True, contact_capacity=_RECORD_CAPACITY,
+                        device=device)
+    labels = atoms.atom_labels()
+    with open(output, "w") as fd:
+        fd.write(header_lines(total_frames, beg, end, stride, itypes, distout))
+        writer = ContactWriter(fd, labels, beg, stride, distout, TRAJ_FRAG_SIZE)
+        done = 0                                         # selected frames processed so far
+        per_frame = None                                 # measured records per frame
+        while done < total_frames:
+            if per_frame is None:
+                n = min(TRAJ_FRAG_SIZE, total_frames - done)
+            else:
+                room = int(0.5 * _RECORD_CAPACITY / max(per_frame, 1.0))
+                n = min(max(TRAJ_FRAG_SIZE, room // TRAJ_FRAG_SIZE * TRAJ_FRAG_SIZE), total_frames - done)
+            first = beg + done * stride
+            frames = trj.read(first, min(first + (n - 1) * stride, end), stride)
+            eng.submit(frames, 0, done)
+            eng.synchronize()
+            rec = eng.drain_contacts()
+            writer.write(rec)
+            per_frame = max(per_frame or 0.0, len(rec) / float(len(frames)))
+            done += len(frames)
+    if frequency_output:
+        from .frequencies import ALL_FREQ_ITYPES, counts_to_table, write_frequency_table
+        table = counts_to_table(topo.residue_label, eng.counts(0))
+        with open(frequency_output, "w") as fd:
+            write_frequency_table(fd, total_frames, ALL_FREQ_ITYPES,
+                                  {k: (c, float(c) / total_frames) for k, c in table.items()})
+    eng.close()

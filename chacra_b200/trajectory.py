@@ -63,3 +63,47 @@ class DCDFile:
 
 def read_dcd(path: str) -> np.ndarray:
     return DCDFile(path).read()
+
+
+class PDBFrames:
+    """A PDB file used as a trajectory: one frame per MODEL (a file without MODEL records is one frame).
+    VMD's pdb plugin behaves the same way (``contact_utils.py:106-114`` loads it with ``molecule.read``)."""
+
+    def __init__(self, path: str):
+        frames, cur = [], []
+        with open(path) as fh:
+            for line in fh:
+                rec = line[:6]
+                if rec in ("ATOM  ", "HETATM"):
+                    cur.append((float(line[30:38]), float(line[38:46]), float(line[46:54])))
+                elif rec.strip() == "ENDMDL":
+                    if cur:
+                        frames.append(cur)
+                    cur = []
+        if cur:
+            frames.append(cur)
+        if not frames:
+            raise ValueError("%s: no ATOM/HETATM records" % path)
+        n = len(frames[0])
+        frames = [f for f in frames if len(f) == n]
+        self.xyz = np.array(frames, np.float64).astype(np.float32)
+        self.n_frames, self.n_atoms = self.xyz.shape[0], n
+
+    def read(self, beg: int = 0, end: int | None = None, stride: int = 1) -> np.ndarray:
+        end = self.n_frames - 1 if end is None else min(end, self.n_frames - 1)
+        return np.ascontiguousarray(self.xyz[beg:end + 1:max(1, stride)])
+
+
+def open_trajectory(path: str):
+    """Trajectory reader by file suffix (the reference maps suffixes to VMD molfile plugins,
+    ``contact_utils.py:40-66``).  Every reader offers ``n_frames``, ``n_atoms`` and
+    ``read(beg, end, stride)`` -> float32 [F][N][3] Angstrom with ``end`` inclusive."""
+    low = path.lower()
+    if low.endswith(".dcd"):
+        return DCDFile(path)
+    if low.endswith(".pdb") or low.endswith(".ent"):
+        return PDBFrames(path)
+    if low.endswith(".xtc"):
+        from .xtc import XTCFile
+        return XTCFile(path)
+    raise ValueError("unsupported trajectory format: %s (dcd, xtc and pdb are read)" % path)

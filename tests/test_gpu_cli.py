@@ -1,0 +1,102 @@
+"""The drop-in scripts end to end on the GPU: same assertions as the reference's own integration tests
+(external/getcontacts/tests/test_get_dynamic_contacts.py:11-76) plus equality with its golden contact list."""
+import os
+import sys
+from collections import Counter
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, ROOT, read_golden_tsv
+
+pytestmark = pytest.mark.gpu
+GC = os.path.join(ROOT, "chacra_b200", "getcontacts")
+TOP = os.path.join(GOLDEN, "5xnd_topology.pdb")
+TRJ = os.path.join(GOLDEN, "5xnd_trajectory.dcd")
+
+
+def _cli():
+    if GC not in sys.path:
+        sys.path.insert(0, GC)
+    import get_dynamic_contacts
+    import get_contact_frequencies
+    return get_dynamic_contacts, get_contact_frequencies
+
+
+def _lines(path):
+    return [ln.rstrip("\n") for ln in open(path)]
+
+
+def test_dynamic_contacts_all_itypes(tmp_path):
+    dyn, freq = _cli()
+    out = tmp_path / "cont.tsv"
+    dyn.main(["--topology", TOP, "--trajectory", TRJ, "--output", str(out), "--itypes", "all"])
+    lines = _lines(out)
+    assert len(lines) == 22589                                   # test_get_dynamic_contacts.py:22
+    assert lines[0] == "# total_frames:20 beg:0 end:19 stride:1 interaction_types:hp,sb,pc,ps,ts,vdw,hb"
+    assert lines[1] == "# Columns: frame, interaction_type, atom_1, atom_2[, atom_3[, atom_4]]"
+    body = [ln.split("\t") for ln in lines[2:]]
+    assert {int(t[0]) for t in body} == set(range(20))           # :31
+    seen = set()
+    for t in body:                                               # :34-45 no duplicate, even with swapped atoms
+        assert (t[0], t[1], t[2], t[3]) not in seen and (t[0], t[1], t[3], t[2]) not in seen
+        seen.add((t[0], t[1], t[2], t[3]))
+    gold = read_golden_tsv(os.path.join(GOLDEN, "test_5xnd_expected.tsv.gz"))
+    assert Counter(tuple(t) for t in body) == Counter(tuple(t) for t in gold)
+    assert [int(t[0]) for t in body] == sorted(int(t[0]) for t in body)     # frames ascending
+    # the frequency step on OUR contact list, shipped semantics: the pair set and every count that does not depend on
+    # which line happens to be first in a frame equal the reference table; the rest differ by the documented bound
+    f_out = tmp_path / "freqs.tsv"
+    freq.main(["--input_files", str(out), "--output_file", str(f_out)])
+    mine = {(a, b): round(float(f) * 20) for a, b, f in (ln.split("\t") for ln in _lines(f_out)[2:])}
+    ref = {(a, b): round(float(f) * 20) for a, b, f in read_golden_tsv(os.path.join(GOLDEN, "freq_5xnd_reference.tsv"))}
+    assert set(mine) == set(ref)
+    diff = {k: mine[k] - ref[k] for k in ref if mine[k] != ref[k]}
+    assert sum(abs(v) for v in diff.values()) <= 2 * 19         # at most one first-line drop per frame on either side
+    # intended semantics = the device count table
+    f_int = tmp_path / "freqs_intended.tsv"
+    freq.main(["--input_files", str(out), "--output_file", str(f_int), "--semantics", "intended"])
+    inten = {(a, b): round(float(f) * 20) for a, b, f in (ln.split("\t") for ln in _lines(f_int)[2:])}
+    assert len(inten) == 398 and sum(inten.values()) == 5831
+
+
+def test_dynamic_contacts_distout_and_device_frequencies(tmp_path):
+    dyn, _ = _cli()
+    out, fout = tmp_path / "cont.tsv", tmp_path / "freqs_dev.tsv"
+    dyn.main(["--topology", TOP, "--trajectory", TRJ, "--output", str(out), "--itypes", "all", "--distout",
+              "--sele", "protein", "--sele2", "protein", "--cores", "4", "--frequency_output", str(fout)])     # ChACRA's call
+    lines = _lines(out)
+    assert lines[1].endswith(", distance_1-2") and len(lines) == 22589
+    import getcontacts_oracle as o
+    xyz = o.read_dcd(TRJ)
+    top = o.Topology(TOP)
+    lab = {top.label(i): i for i in range(top.n)}
+    for t in [ln.split("\t") for ln in lines[2:400]]:
+        a, b, f = xyz[int(t[0])][lab[t[2]]], xyz[int(t[0])][lab[t[3]]], t[-1]
+        assert f == "%.3f" % float(np.sqrt(o._d2(a, b), dtype=np.float32))
+    rows = [ln.split("\t") for ln in _lines(fout)[2:]]
+    assert len(rows) == 398 and sum(round(float(r[2]) * 20) for r in rows) == 5831
+
+
+def test_dynamic_contacts_salt_bridges_asp_lys(tmp_path):
+    dyn, _ = _cli()
+    out = tmp_path / "sb.tsv"
+    dyn.main(["--topology", TOP, "--trajectory", TRJ, "--output", str(out), "--itypes", "sb", "--sele", "resname ASP LYS"])
+    lines = _lines(out)
+    assert len(lines) == 22                                      # test_get_dynamic_contacts.py:65
+    assert {int(ln.split("\t")[0]) for ln in lines[2:]} == {1, 2, 3, 4, 5, 8, 12, 13, 15, 16, 18, 19}    # :74
+
+
+def test_beg_end_stride_and_empty_selection(tmp_path):
+    dyn, _ = _cli()
+    out = tmp_path / "sub.tsv"
+    dyn.main(["--topology", TOP, "--trajectory", TRJ, "--output", str(out), "--itypes", "vdw", "--beg", "3", "--end", "15",
+              "--stride", "4"])
+    lines = _lines(out)
+    assert lines[0].startswith("# total_frames:4 beg:3 end:15 stride:4 ")
+    assert {int(ln.split("\t")[0]) for ln in lines[2:]} == {3, 7, 11, 15}
+    gold = [t for t in read_golden_tsv(os.path.join(GOLDEN, "test_5xnd_expected.tsv.gz")) if t[1] == "vdw" and int(t[0]) in (3, 7, 11, 15)]
+    assert Counter(tuple(ln.split("\t")) for ln in lines[2:]) == Counter(tuple(t) for t in gold)
+    with pytest.raises(SystemExit) as e:                         # compute_contacts.py:240-245
+        dyn.main(["--topology", TOP, "--trajectory", TRJ, "--output", str(out), "--itypes", "sb", "--sele", "resname XYZ"])
+    assert e.value.code == 1
