@@ -224,6 +224,7 @@ extern "C" int chc_create(chc_ctx** out, const chc_topology* t, const chc_params
     const void* bin_fn = bin_kernel_fn(ctx->bin_variant, &ctx->bin_threads);
     CK(cudaFuncSetAttribute(bin_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->bin_smem));
     ctx->pair_grid = ctx->sm_count;
+    if (const char* e = getenv("CHACRA_PAIR_GRID")) ctx->pair_grid = std::max(1, std::min(ctx->sm_count, atoi(e)));   // test hook
     {
         int per_sm = 1;
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bin_fn, ctx->bin_threads, ctx->bin_smem));
