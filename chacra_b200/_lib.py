@@ -47,14 +47,14 @@ f32p, f64p = C.POINTER(C.c_float), C.POINTER(C.c_double)
 class ChcTopology(C.Structure):
     _fields_ = [(n, C.c_int32) for n in (
         "n_atoms", "n_pair", "n_aux", "n_h_slots", "n_rings", "n_cations", "n_disulfide", "n_elem", "n_residues",
-        "n_hp_base", "n_bond_adj", "same_selection")] + [
+        "n_hp_base", "n_bond_adj", "same_selection", "n_pair_a", "n_solvent")] + [
         ("pair_atom", i32p), ("pair_info", u32p), ("pair_lkey", i32p), ("pair_res", i32p), ("pair_resid", i32p),
         ("pair_h_start", i32p), ("pair_bond_start", i32p), ("pair_bond_adj", i32p), ("aux_atom", i32p),
         ("ring_aux", i32p), ("ring_pc_aux", i32p), ("ring_sel_aux", i32p), ("ring_sel_flags", u8p),
         ("ring_atoms", i32p), ("ring_res", i32p), ("ring_rep", i32p), ("ring_rep_aux", i32p),
         ("cation_aux", i32p), ("cation_atom", i32p), ("cation_flags", u8p), ("cation_res", i32p),
         ("cation_excl_ring", i32p), ("disulfide", i32p), ("vdw_d2max", f32p), ("vdw_cut", f64p), ("hp_base", i32p),
-        ("atom_class", u8p), ("elem_class", u8p)]
+        ("atom_class", u8p), ("elem_class", u8p), ("pair_solv_ord", i32p)]
 
 
 class ChcParams(C.Structure):

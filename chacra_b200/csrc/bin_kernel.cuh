@@ -37,6 +37,8 @@ bin_frames_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__
     __shared__ BinShared M;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int NP = T.n_pair;
+    // grid B: pair atoms [n_pair_a, NP) (unselected solvent) are sorted into a second set of cells, keys ncell..2*ncell-1
+    const bool gridb = T.n_pair_a < NP;
     constexpr int NR = APT > 0 ? APT : 1;
     int r_atom[NR];
     float rx[NR], ry[NR], rz[NR];
@@ -73,6 +75,7 @@ bin_frames_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__
                         lo[2] = fminf(lo[2], rz[k]); hi[2] = fmaxf(hi[2], rz[k]);
                     }
             } else {
+#pragma unroll 4
                 for (int p = tid; p < NP; p += THREADS) {
                     const float* q = X + 3 * (size_t)T.pair_atom[p];
 #pragma unroll
@@ -96,12 +99,13 @@ bin_frames_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__
                 inv = 1.0f / cell;
 #pragma unroll
                 for (int d = 0; d < 3; ++d) nc[d] = (int)(ext[d] * inv) + 1;
-                if ((long long)(nc[0] + 2) * (nc[1] + 2) * (nc[2] + 2) + 1 <= B.max_cells) break;
+                if ((long long)(nc[0] + 2) * (nc[1] + 2) * (nc[2] + 2) * (gridb ? 2 : 1) + 1 <= B.max_cells) break;
                 cell *= 1.25f;
             }
         }
         const int px = nc[0] + 2, pxy = px * (nc[1] + 2), ncell = pxy * (nc[2] + 2);
-        for (int c = tid; c < ncell; c += THREADS) cells[c] = 0;
+        const int nkey = gridb ? 2 * ncell : ncell;
+        for (int c = tid; c < nkey; c += THREADS) cells[c] = 0;
         __syncthreads();
         // ---- 2: count ---------------------------------------------------------------------------------
         int r_cell[NR];
@@ -110,22 +114,23 @@ bin_frames_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__
             for (int k = 0; k < NR; ++k)
                 if (r_atom[k] >= 0) {
                     r_cell[k] = (cell_of(rz[k], org[2], inv, nc[2]) + 1) * pxy + (cell_of(ry[k], org[1], inv, nc[1]) + 1) * px +
-                                cell_of(rx[k], org[0], inv, nc[0]) + 1;
+                                cell_of(rx[k], org[0], inv, nc[0]) + 1 + (tid + k * THREADS >= T.n_pair_a ? ncell : 0);
                     atomicAdd(&cells[r_cell[k]], 1);
                 }
         } else {
+#pragma unroll 4
             for (int p = tid; p < NP; p += THREADS) {
                 const float* q = X + 3 * (size_t)T.pair_atom[p];
                 int c = (cell_of(q[2], org[2], inv, nc[2]) + 1) * pxy + (cell_of(q[1], org[1], inv, nc[1]) + 1) * px +
-                        cell_of(q[0], org[0], inv, nc[0]) + 1;
+                        cell_of(q[0], org[0], inv, nc[0]) + 1 + (p >= T.n_pair_a ? ncell : 0);
                 atomicAdd(&cells[c], 1);
             }
         }
         __syncthreads();
         // ---- 3: exclusive scan over the cells --------------------------------------------------------------
         {
-            const int per = (ncell + THREADS - 1) / THREADS;
-            const int b = min(tid * per, ncell), e = min(b + per, ncell);
+            const int per = (nkey + THREADS - 1) / THREADS;
+            const int b = min(tid * per, nkey), e = min(b + per, nkey);
             int s = 0;
             for (int c = b; c < e; ++c) s += cells[c];
             int incl = s;
@@ -154,15 +159,17 @@ bin_frames_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__
                     spos[dst] = make_float4(rx[k], ry[k], rz[k], __uint_as_float((T.pair_info[p] & I_WMASK) | ((unsigned)p << I_PIDX_SHIFT)));
                 }
         } else {
+#pragma unroll 4
             for (int p = tid; p < NP; p += THREADS) {
                 const float* q = X + 3 * (size_t)T.pair_atom[p];
                 const float x = q[0], y = q[1], z = q[2];
                 int c = (cell_of(z, org[2], inv, nc[2]) + 1) * pxy + (cell_of(y, org[1], inv, nc[1]) + 1) * px +
-                        cell_of(x, org[0], inv, nc[0]) + 1;
+                        cell_of(x, org[0], inv, nc[0]) + 1 + (p >= T.n_pair_a ? ncell : 0);
                 int dst = atomicAdd(&cells[c], 1);
                 spos[dst] = make_float4(x, y, z, __uint_as_float((T.pair_info[p] & I_WMASK) | ((unsigned)p << I_PIDX_SHIFT)));
             }
         }
+#pragma unroll 4
         for (int s = tid; s < T.n_aux; s += THREADS) {
             const float* q = X + 3 * (size_t)T.aux_atom[s];
             aux[3 * s] = q[0]; aux[3 * s + 1] = q[1]; aux[3 * s + 2] = q[2];
@@ -175,7 +182,7 @@ bin_frames_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__
             cells_out[0] = 0;
         }
         __syncthreads();
-        for (int c = tid; c < ncell; c += THREADS) cells_out[c + 1] = cells[c];
+        for (int c = tid; c < nkey; c += THREADS) cells_out[c + 1] = cells[c];
         __syncthreads();
     }
 }
@@ -210,19 +217,22 @@ hp_mask_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__ xy
         const int c0 = (cell_of(z, h.org[2], h.inv, h.nc[2]) + 1) * pxy + (cell_of(y, h.org[1], h.inv, h.nc[1]) + 1) * px +
                        cell_of(x, h.org[0], h.inv, h.nc[0]) + 1;
         unsigned other = 0u;          // an atom that is neither carbon nor hydrogen within 1.7 A
-        int jb[9], je[9];
+        const int ngrid = T.n_pair_a < T.n_pair ? 2 : 1;          // unselected solvent lives in the second set of cells
+        for (int g = 0; g < ngrid; ++g) {
+            int jb[9], je[9];
 #pragma unroll
-        for (int r = 0; r < 9; ++r) {               // all eighteen bounds first: independent loads
-            const int base = c0 + (r % 3 - 1) * px + (r / 3 - 1) * pxy;
-            jb[r] = cells[base - 1]; je[r] = cells[base + 2];
-        }
-#pragma unroll
-        for (int r = 0; r < 9; ++r)
-            for (int j = jb[r] + lane; j < je[r]; j += 32) {
-                const float4 o = spos[j];
-                if (dist2_exact(o.x, o.y, o.z, x, y, z) <= r2 && !((P.elem_ch_mask >> (__float_as_uint(o.w) & I_ELEM)) & 1u))
-                    other = 1u;
+            for (int r = 0; r < 9; ++r) {               // all eighteen bounds first: independent loads
+                const int base = c0 + g * h.ncell + (r % 3 - 1) * px + (r / 3 - 1) * pxy;
+                jb[r] = cells[base - 1]; je[r] = cells[base + 2];
             }
+#pragma unroll
+            for (int r = 0; r < 9; ++r)
+                for (int j = jb[r] + lane; j < je[r]; j += 32) {
+                    const float4 o = spos[j];
+                    if (dist2_exact(o.x, o.y, o.z, x, y, z) <= r2 && !((P.elem_ch_mask >> (__float_as_uint(o.w) & I_ELEM)) & 1u))
+                        other = 1u;
+                }
+        }
         other = __reduce_or_sync(FULL, other);
         const unsigned sub = other ? 0u : 1u;
         unsigned eq = 0u;

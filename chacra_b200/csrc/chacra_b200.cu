@@ -25,6 +25,7 @@ struct chc_ctx {
     int64_t chunk_frames = 0;
     unsigned char* binned = nullptr;
     unsigned* gstamp = nullptr; unsigned* gstate = nullptr;
+    int* wscratch = nullptr; unsigned* status = nullptr;
     std::vector<void*> dev_allocs;
     int32_t* counts = nullptr; bool counts_owned = false; int64_t n_pairs = 0;
     chc_contact* contacts = nullptr; unsigned long long* contact_n = nullptr;
@@ -64,7 +65,7 @@ static const void* bin_kernel_fn(int variant, int* threads) {
     switch (variant) {
         case 1: if (threads) *threads = 512; return (const void*)bin_frames_kernel<512, 8, 2>;
         case 2: if (threads) *threads = 1024; return (const void*)bin_frames_kernel<1024, 8, 1>;
-        default: if (threads) *threads = 256; return (const void*)bin_frames_kernel<256, 0, 1>;
+        default: if (threads) *threads = 1024; return (const void*)bin_frames_kernel<1024, 0, 1>;
     }
 }
 
@@ -129,6 +130,7 @@ extern "C" void chc_destroy(chc_ctx* ctx) {
     if (ctx->counts_owned) cudaFree(ctx->counts);
     cudaFree(ctx->contacts); cudaFree(ctx->contact_n); cudaFree(ctx->near); cudaFree(ctx->near_n);
     cudaFree(ctx->hpmask); cudaFree(ctx->binned); cudaFree(ctx->gstamp); cudaFree(ctx->gstate);
+    cudaFree(ctx->wscratch); cudaFree(ctx->status);
     for (int k = 0; k < 2; ++k) {
         cudaFree(ctx->dev_stage[k]); if (ctx->pin_stage[k]) cudaFreeHost(ctx->pin_stage[k]);
         if (ctx->stage_done[k]) cudaEventDestroy(ctx->stage_done[k]);
@@ -162,13 +164,15 @@ extern "C" int chc_create(chc_ctx** out, const chc_topology* t, const chc_params
     T.n_atoms = t->n_atoms; T.n_pair = t->n_pair; T.n_aux = t->n_aux; T.n_h = t->n_h_slots; T.n_rings = t->n_rings;
     T.n_cat = t->n_cations; T.n_dis = t->n_disulfide; T.K = t->n_elem; T.R = t->n_residues; T.n_hp_base = t->n_hp_base;
     T.same = t->same_selection;
+    T.n_pair_a = t->n_pair_a; T.n_solv = t->n_solvent;
+    if (T.n_pair_a < 0 || T.n_pair_a > T.n_pair) return fail(ctx, CHC_E_INVALID, "bad n_pair_a %d", T.n_pair_a);
     int rc;
     const size_t NP = t->n_pair, NR = t->n_rings, NC = t->n_cations, K2 = (size_t)t->n_elem * t->n_elem;
 #define UP(field, src, n) if ((rc = upload(ctx, src, (size_t)(n), &T.field)) != CHC_OK) return rc
     UP(pair_atom, t->pair_atom, NP); UP(pair_info, t->pair_info, NP); UP(pair_lkey, t->pair_lkey, NP);
     UP(pair_res, t->pair_res, NP); UP(pair_resid, t->pair_resid, NP); UP(pair_h_start, t->pair_h_start, NP + 1);
     UP(pair_bond_start, t->pair_bond_start, NP + 1); UP(pair_bond_adj, t->pair_bond_adj, t->n_bond_adj);
-    UP(aux_atom, t->aux_atom, t->n_aux);
+    UP(aux_atom, t->aux_atom, t->n_aux); UP(pair_solv_ord, t->pair_solv_ord, NP);
     UP(ring_aux, t->ring_aux, 3 * NR); UP(ring_pc_aux, t->ring_pc_aux, 3 * NR); UP(ring_sel_aux, t->ring_sel_aux, 3 * NR);
     UP(ring_sel_flags, t->ring_sel_flags, 3 * NR); UP(ring_atoms, t->ring_atoms, 3 * NR); UP(ring_res, t->ring_res, NR);
     UP(ring_rep, t->ring_rep, NR); UP(ring_rep_aux, t->ring_rep_aux, NR);
@@ -238,6 +242,14 @@ extern "C" int chc_create(chc_ctx** out, const chc_topology* t, const chc_params
         if (const char* e = getenv("CHACRA_CHUNK_FRAMES")) ctx->chunk_frames = std::max<int64_t>(1, atoll(e));
     }
     CK(cudaMalloc(&ctx->binned, (size_t)ctx->chunk_frames * (size_t)ctx->B.stride));
+    CK(cudaMalloc(&ctx->status, 4)); CK(cudaMemset(ctx->status, 0, 4));
+    if (T.n_solv > 0) {
+        // the solvent shell of the reference (3.5 A, hbonds.py:24) is implied by the hydrogen-bond cutoff only up to 3.5 A
+        if ((p->itype_mask & CHC_IT_HB) && p->hb_dist > 3.5)
+            return fail(ctx, CHC_E_INVALID, "hbond cutoff %.3f A above the 3.5 A water-shell radius is not supported with solvent", p->hb_dist);
+        size_t ints = (size_t)ctx->pair_grid * (size_t)T.n_solv * (3 + WADJ);
+        CK(cudaMalloc(&ctx->wscratch, ints * 4)); CK(cudaMemset(ctx->wscratch, 0, ints * 4));
+    }
     if (!ctx->small_path) {
         size_t words = (size_t)ctx->pair_grid * (size_t)ctx->L.bits_words;
         CK(cudaMalloc(&ctx->gstamp, words * 4)); CK(cudaMemset(ctx->gstamp, 0, words * 4));
@@ -332,6 +344,7 @@ extern "C" int chc_submit_frames(chc_ctx* ctx, int state, const float* d_xyz, in
     O.counts = ctx->counts + (size_t)state * ctx->n_pairs; O.n_pairs = ctx->n_pairs;
     O.contacts = ctx->contacts; O.contact_n = ctx->contact_n; O.contact_cap = ctx->prm.contact_capacity;
     O.near = ctx->near; O.near_n = ctx->near_n; O.near_cap = ctx->prm.near_capacity;
+    O.status = ctx->status;
     // chunks of frames: the binning kernel streams the coordinates and writes the chunk's binned records, the pair
     // kernel consumes them (from L2 when the chunk fits)
     for (int64_t c0 = 0; c0 < n_frames; c0 += ctx->chunk_frames) {
@@ -366,10 +379,10 @@ extern "C" int chc_submit_frames(chc_ctx* ctx, int state, const float* d_xyz, in
         const int grid = std::min(n, ctx->pair_grid);
         if (ctx->small_path)
             pair_frames_kernel<PAIR_THREADS, true><<<grid, PAIR_THREADS, ctx->L.total, stream>>>(
-                ctx->T, ctx->P, O, ctx->L, ctx->B, ctx->binned, n, first_index + c0, F, frag0, ctx->hpmask, nullptr, nullptr);
+                ctx->T, ctx->P, O, ctx->L, ctx->B, ctx->binned, n, first_index + c0, F, frag0, ctx->hpmask, nullptr, nullptr, ctx->wscratch);
         else
             pair_frames_kernel<PAIR_THREADS, false><<<grid, PAIR_THREADS, ctx->L.total, stream>>>(
-                ctx->T, ctx->P, O, ctx->L, ctx->B, ctx->binned, n, first_index + c0, F, frag0, ctx->hpmask, ctx->gstamp, ctx->gstate);
+                ctx->T, ctx->P, O, ctx->L, ctx->B, ctx->binned, n, first_index + c0, F, frag0, ctx->hpmask, ctx->gstamp, ctx->gstate, ctx->wscratch);
         CK(cudaGetLastError());
         if (ctx->timing) { CK(cudaEventRecord(ev.c, stream)); ctx->ev_pending.push_back(ev); }
         ctx->st.kernel_launches += 2;
@@ -435,6 +448,10 @@ extern "C" int chc_synchronize(chc_ctx* ctx, void* stream) {
     if (!ctx) return CHC_E_INVALID;
     CK(cudaSetDevice(ctx->device));
     CK(cudaStreamSynchronize((cudaStream_t)stream));
+    unsigned st = 0;
+    CK(cudaMemcpy(&st, ctx->status, 4, cudaMemcpyDeviceToHost));
+    if (st & ST_WATER_DEGREE)
+        return fail(ctx, CHC_E_TOO_LARGE, "a solvent atom is hydrogen bonded to more than %d non-solvent atoms in one frame; water bridges would be incomplete", WADJ);
     return CHC_OK;
 }
 

@@ -35,9 +35,12 @@
 #define C_HB    8u
 #define C_NEARV 16u   // within near_dist_tol of the vdW cutoff
 #define C_NEARH 32u   // ... of the hydrophobic (same) cutoff
+#define C_HBW   64u   // hydrogen-bond candidate between a non-solvent atom and a solvent atom (water-bridge edge)
 
 struct DevTopo {
     int n_atoms, n_pair, n_aux, n_h, n_rings, n_cat, n_dis, K, R, n_hp_base, same;
+    int n_pair_a, n_solv;  // grid A pair atoms; solvent heavy atoms among all pair atoms
+    const int* pair_solv_ord;
     const int* pair_atom; const unsigned* pair_info; const int* pair_lkey; const int* pair_res; const int* pair_resid;
     const int* pair_h_start; const int* pair_bond_start; const int* pair_bond_adj;
     const int* aux_atom;
@@ -73,7 +76,9 @@ struct DevOut {
     long long n_pairs;
     chc_contact* contacts; unsigned long long* contact_n; long long contact_cap;
     chc_near* near; unsigned long long* near_n; long long near_cap;
+    unsigned* status;            // sticky error bits (ST_*), checked by the host
 };
+#define ST_WATER_DEGREE 1u       // a solvent atom had more than WADJ hydrogen-bonded non-solvent neighbours
 
 // ---- binned frames: what the streaming/binning kernel hands to the pair kernel -----------------------
 // One record per frame in a device buffer, every section 16-byte aligned:

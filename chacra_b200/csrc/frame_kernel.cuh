@@ -26,6 +26,30 @@ __device__ __forceinline__ void emit_contact(const DevOut& O, int frame, int ity
     }
 }
 
+// water-bridge record: atom1, atom2 and the one or two mediating solvent atoms (hbonds.py:168-204)
+__device__ __forceinline__ void emit_bridge(const DevOut& O, int frame, int itype, int a1, int a2, int w1, int w2, float dist) {
+    unsigned long long pos = atomicAdd(O.contact_n, 1ull);
+    if (pos < (unsigned long long)O.contact_cap) {
+        int4* dst = reinterpret_cast<int4*>(O.contacts + pos);
+        dst[0] = make_int4(frame, itype, a1, a2);
+        dst[1] = make_int4(w1, w2, __float_as_int(dist), 0);
+    }
+}
+
+// Per-CTA scratch of the water-bridge phase (global memory): for every solvent pair atom (by solvent ordinal) the
+// number of hydrogen-bonded non-solvent neighbours found in this frame, their sorted slots, the solvent atom's own
+// sorted slot, and the list of solvent ordinals that have at least one neighbour.  `cnt` is all zero between frames.
+#define WADJ 8
+struct WaterScratch { int* cnt; int* adj; int* slot; int* list; };
+__device__ __forceinline__ WaterScratch water_scratch(int* base, int cta, int n_solv) {
+    WaterScratch W{nullptr, nullptr, nullptr, nullptr};
+    if (base && n_solv > 0) {
+        int* p = base + (size_t)cta * n_solv * (3 + WADJ);
+        W.cnt = p; W.adj = p + n_solv; W.slot = p + (size_t)n_solv * (1 + WADJ); W.list = p + (size_t)n_solv * (2 + WADJ);
+    }
+    return W;
+}
+
 __device__ __forceinline__ void emit_near(const DevOut& O, int frame, int kind, int a1, int a2, double delta) {
     unsigned long long pos = atomicAdd(O.near_n, 1ull);
     if (pos < (unsigned long long)O.near_cap) {

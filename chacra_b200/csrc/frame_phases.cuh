@@ -11,6 +11,8 @@ struct FrameCtx {            // per-CTA view of the current frame (shared memory
     const float* tv; const float* th;
     const unsigned char* hm; // hydrophobic membership of this frame's fragment, by pair index (bit0 H1, bit1 H2)
     int frame;               // frame id reported in records
+    WaterScratch W;          // water-bridge scratch of this CTA (null pointers without solvent)
+    int* nmark;              // shared counter: entries of W.list
 };
 
 // ---- R: pi-cation ----------------------------------------------------------------------------------
@@ -126,8 +128,13 @@ __device__ __forceinline__ unsigned e2_classify(const DevTopo& T, const DevParam
     d2_out = d2;
     unsigned wi = __float_as_uint(a.w), wj = __float_as_uint(b.w);
     bool dual = ((wi & I_S1) && (wj & I_S2)) || ((wi & I_S2) && (wj & I_S1));
-    if (!dual) return 0u;
+    // water-bridge edge: exactly one solvent atom, the other in the hydrogen-bond selection U; needs no dual selection
+    // (hbonds.py:78-80) and is dropped only inside one residue (:131)
+    const bool edge = (P.itypes & CHC_IT_HB) && ((wi ^ wj) & I_SOLV) && (((wi & I_SOLV) ? wj : wi) & I_HBU) &&
+                      ((wi | wj) & I_HASH) && d2 <= P.hb2;
+    if (!dual && !edge) return 0u;
     int dl = abs(F.lkey[wi >> I_PIDX_SHIFT] - F.lkey[wj >> I_PIDX_SHIFT]);
+    if (!dual) return (edge && dl != 0) ? C_HBW : 0u;
     int e = (wi & I_ELEM) * T.K + (wj & I_ELEM);
     unsigned cls = 0;
     if (dl >= P.vdw_rd) {
@@ -154,6 +161,7 @@ __device__ __forceinline__ unsigned e2_classify(const DevTopo& T, const DevParam
     if ((P.itypes & CHC_IT_SB) && d2 <= P.sb2 &&
         (((wi & I_ANION) && (wj & I_CATION)) || ((wj & I_ANION) && (wi & I_CATION)))) cls |= C_SB;
     if ((P.itypes & CHC_IT_HB) && d2 <= P.hb2 && (wi & wj & I_HBU) && ((wi | wj) & I_HASH) && dl >= P.hb_rd) cls |= C_HB;
+    if (edge && dl != 0) cls |= C_HBW;
     return cls;
 }
 
@@ -163,7 +171,7 @@ __device__ __forceinline__ unsigned e2_classify(const DevTopo& T, const DevParam
 // bracket tan(cutoff) by a relative 4e-4 (~7e-3 degree at 70 degrees, far above every rounding step of the exact recipe
 // and above the 1e-3 degree near-cutoff band); only inside the bracket is the exact double-precision atan2 evaluated.
 __device__ __forceinline__ bool hb_direction(const DevTopo& T, const DevParams& P, const DevOut& O, const FrameCtx& F,
-                                             float4 d, float4 a, int pd, int atom_d, int atom_a) {
+                                             float4 d, float4 a, int pd, int atom_d, int atom_a, bool report = true) {
     bool ok = false;
     int hb = T.pair_h_start[pd], he = T.pair_h_start[pd + 1];
     for (int h = hb; h < he; ++h) {
@@ -179,7 +187,7 @@ __device__ __forceinline__ bool hb_direction(const DevTopo& T, const DevParams& 
             if (pcos <= 0.f || psin > pcos * P.hb_tan_hi) continue;                    // surely above it
         }
         float ang = 57.2958f * (float)atan2((double)psin, (double)pcos);
-        if (P.track_near && fabs((double)ang - (double)P.hb_angle) < P.near_a)
+        if (report && P.track_near && fabs((double)ang - (double)P.hb_angle) < P.near_a)
             emit_near(O, F.frame, CHC_NEAR_HB_ANGLE, atom_d, atom_a, (double)ang - (double)P.hb_angle);
         ok |= ang < P.hb_angle;
     }
@@ -195,7 +203,7 @@ __device__ __forceinline__ void e3_finish(const DevTopo& T, const DevParams& P, 
     int ai = T.pair_atom[pi], aj = T.pair_atom[pj];
     const unsigned si = T.pair_info[pi], sj = T.pair_info[pj];       // static-only bits: ligand, backbone, CYS, xbond
     // directly bonded pairs are excluded by measure contacts / measure hbonds (Appendix A.4, A.5)
-    bool need_bond = (cls & (C_SB | C_HB)) || ((si & I_XBOND) && (sj & I_XBOND));
+    bool need_bond = (cls & (C_SB | C_HB | C_HBW)) || ((si & I_XBOND) && (sj & I_XBOND));
     if (need_bond && is_bonded(T, pi, aj)) return;
     int ri = T.pair_res[pi], rj = T.pair_res[pj];
     float dist = sqrtf(d2);
@@ -224,16 +232,25 @@ __device__ __forceinline__ void e3_finish(const DevTopo& T, const DevParams& P, 
         if (!(al && cl)) count_pair(O, F.bits, F.gen, ri, rj, T.R);
         if (P.emit) emit_contact(O, F.frame, al ? (cl ? CHC_SBLL : CHC_SBLP) : (cl ? CHC_SBPL : CHC_SB), aa, ac, dist);
     }
-    if (cls & C_HB) {
+    if (cls & (C_HB | C_HBW)) {
         bool ok = false;
 #pragma unroll 1
-        for (int dir = 0; dir < 2; ++dir) {            // both atoms are tried as donor (one-selection measure hbonds)
+        for (int dir = 0; dir < 2; ++dir) {            // both atoms are tried as donor (measure hbonds, both argument orders)
             const unsigned wd = dir ? wj : wi;
             if (!(wd & I_HASH)) continue;
             const float4 xd = dir ? b : a, xa = dir ? a : b;
-            ok |= hb_direction(T, P, O, F, xd, xa, dir ? pj : pi, dir ? aj : ai, dir ? ai : aj);
+            ok |= hb_direction(T, P, O, F, xd, xa, dir ? pj : pi, dir ? aj : ai, dir ? ai : aj, (cls & C_HB) != 0);
         }
-        if (ok) {
+        if (ok && (cls & C_HBW)) {
+            // record the edge with the solvent atom: neighbour = sorted slot of the non-solvent atom (hbonds.py:126-142)
+            const bool wi_solv = (wi & I_SOLV) != 0;
+            const int ord = T.pair_solv_ord[wi_solv ? pi : pj];
+            const int n = atomicAdd(&F.W.cnt[ord], 1);
+            if (n < WADJ) F.W.adj[ord * WADJ + n] = wi_solv ? j : i;
+            else atomicOr(O.status, ST_WATER_DEGREE);
+            if (n == 0) { F.W.slot[ord] = wi_solv ? i : j; F.W.list[atomicAdd(F.nmark, 1)] = ord; }
+        }
+        if (ok && (cls & C_HB)) {
             bool li = si & I_LIG, lj = sj & I_LIG, bi = si & I_BB, bj = sj & I_BB;
             int t;
             if (li && lj) t = CHC_HBLL;

@@ -14,6 +14,7 @@
 // version inlined them at ~45 sites and stalled on instruction fetch, profiles/r01_v1_*).
 #pragma once
 #include "frame_phases.cuh"
+#include "water_phase.cuh"
 
 #define Q1_CAP 64           // (i, j) survivors per warp
 #define Q2_CAP 64           // classified pairs per warp
@@ -32,7 +33,7 @@ struct PairLayout {         // shared-memory plan of the pair kernel (bytes)
 struct PairMisc {
     unsigned long long bar;     // mbarrier of the bulk copies
     int cursor;                 // next block of CELL_BLK cells
-    int pad;
+    int nmark;                  // waters with at least one hydrogen bond to a non-solvent atom (this frame)
 };
 
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -58,7 +59,8 @@ template <int THREADS, bool SMALL>
 __global__ void __launch_bounds__(THREADS, 1)
 pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, const unsigned char* __restrict__ binned,
                    int n_frames, long long first_index, int frag_frames, long long frag0,
-                   const unsigned char* __restrict__ hpmask, unsigned* __restrict__ gstamp, unsigned* __restrict__ gstate) {
+                   const unsigned char* __restrict__ hpmask, unsigned* __restrict__ gstamp, unsigned* __restrict__ gstate,
+                   int* __restrict__ wscratch) {
     extern __shared__ __align__(128) unsigned char smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     float* tv = reinterpret_cast<float*>(smem + L.off_tv);
@@ -88,13 +90,13 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
         if (SMALL) {
             if (tid == 0) {
                 const int ncell = __ldcg(&reinterpret_cast<const BinHeader*>(rec)->ncell);
-                const unsigned cbytes = (unsigned)((4 * (ncell + 1) + 15) & ~15);
+                const unsigned cbytes = (unsigned)((4 * ((T.n_pair_a < T.n_pair ? 2 : 1) * ncell + 1) + 15) & ~15);
                 // the previous frame's generic-proxy reads of these buffers are ordered before the async-proxy writes
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 mbar_expect_tx(&M->bar, (unsigned)B.fixed_bytes + cbytes);
                 bulk_g2s(smem + L.off_rec, rec, (unsigned)B.fixed_bytes, &M->bar);
                 bulk_g2s(smem + L.off_cells, rec + B.off_cells, cbytes, &M->bar);
-                M->cursor = 0;
+                M->cursor = 0; M->nmark = 0;
             }
             for (int w = tid; w < L.bits_words; w += THREADS) bits[w] = 0u;
             mbar_wait(&M->bar, phase);
@@ -104,7 +106,7 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
             aux = reinterpret_cast<const float*>(smem + L.off_rec + B.off_aux);
             cells = reinterpret_cast<const int*>(smem + L.off_cells);
         } else {
-            if (tid == 0) M->cursor = 0;
+            if (tid == 0) { M->cursor = 0; M->nmark = 0; }
             gen = gen + 1u;
             if (gen > 255u) {               // generations wrapped: wipe the table once per 255 frames
                 for (int w = tid; w < L.bits_words; w += THREADS) bits[w] = 0u;
@@ -118,7 +120,8 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
         __syncthreads();
         const int px = hdr->nc[0] + 2, pxy = px * (hdr->nc[1] + 2), ncell = hdr->ncell;
         FrameCtx F{spos, SMALL ? s_lkey : T.pair_lkey, aux, bits, gen, tv, th,
-                   hpmask + (size_t)(gidx / frag_frames - frag0) * T.n_pair, (int)gidx};
+                   hpmask + (size_t)(gidx / frag_frames - frag0) * T.n_pair, (int)gidx,
+                   water_scratch(wscratch, blockIdx.x, T.n_solv), &M->nmark};
         // ---- R: ring interactions (small lists; float prefilter, float64 geometry) ------------------------------
         if (P.itypes & CHC_IT_PC) {
             const int n = T.n_cat * T.n_rings;
@@ -139,7 +142,9 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
         // E1 iteration state (warp-uniform): current cell [i, ce), its j ranges, the j block
         int blk_base = 0; unsigned blk_mask = 0u; int my_cs = 0, my_ce = 0;
         int i = 0, ce = 0, cs = 0, J = 0, jj = 0;
-        int rb = 0, rlen = 0;                 // lanes 0..4: begin / length of half-shell range `lane`
+        int rb = 0, rlen = 0;                 // lanes 0..nr-1: begin / length of neighbour range `lane`
+        // ranges 0..4: half shell of grid A; ranges 5..13 (only with unselected solvent): the full 3x3 rows of grid B
+        const int nr = T.n_pair_a < T.n_pair ? 14 : 5;
         int j = -1; float4 pj = make_float4(0.f, 0.f, 0.f, 0.f);
         bool exhausted = false;
         for (;;) {
@@ -173,17 +178,20 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                             const int base = c + dy * px + dz * pxy;
                             rb = lane == 0 ? cs : cells[base - 1];
                             rlen = cells[base + 2] - rb;
+                        } else if (lane < nr) {
+                            const int r = lane - 5;
+                            const int base = c + ncell + (r % 3 - 1) * px + (r / 3 - 1) * pxy;
+                            rb = cells[base - 1];
+                            rlen = cells[base + 2] - rb;
                         }
                         J = 0;
-#pragma unroll
-                        for (int r = 0; r < 5; ++r) J += __shfl_sync(FULL, rlen, r);
+                        for (int r = 0; r < nr; ++r) J += __shfl_sync(FULL, rlen, r);
                         jj = 0;
                     }
                     // this lane's j of the block
                     int k = jj + lane;
                     j = -1;
-#pragma unroll
-                    for (int r = 0; r < 5; ++r) {
+                    for (int r = 0; r < nr; ++r) {
                         const int len = __shfl_sync(FULL, rlen, r), beg = __shfl_sync(FULL, rb, r);
                         if (j < 0 && k >= 0 && k < len) j = beg + k;
                         k -= len;
@@ -232,6 +240,12 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
             }
         }
         __syncthreads();
+        // ---- W: water bridges from the (non-solvent, solvent) hydrogen bonds the pair phase recorded ----------------
+        if (T.n_solv > 0 && (P.itypes & CHC_IT_HB)) {
+            WaterScratch W = water_scratch(wscratch, blockIdx.x, T.n_solv);
+            water_bridges(T, P, O, F, W, cells, px, pxy, ncell, hdr, &M->nmark, tid, THREADS);
+            __syncthreads();
+        }
     }
     if (!SMALL && tid == 0) gstate[blockIdx.x] = gen;
 }

@@ -79,13 +79,14 @@ class ContactEngine:
         t.n_rings, t.n_cations, t.n_disulfide = len(topo.ring_res), len(topo.cation_atom), len(topo.disulfide)
         t.n_elem, t.n_residues, t.n_hp_base = len(topo.elem_symbols), topo.n_residues, len(topo.hp_base_atoms)
         t.n_bond_adj, t.same_selection = len(topo.pair_bond_adj), int(topo.same_selection)
+        t.n_pair_a, t.n_solvent = int(topo.n_pair_a), int(topo.n_solvent_pair)
         for name, ct in (("pair_atom", C.c_int32), ("pair_lkey", C.c_int32), ("pair_res", C.c_int32),
                          ("pair_resid", C.c_int32), ("pair_h_start", C.c_int32), ("pair_bond_start", C.c_int32),
                          ("pair_bond_adj", C.c_int32), ("aux_atom", C.c_int32), ("ring_aux", C.c_int32),
                          ("ring_pc_aux", C.c_int32), ("ring_sel_aux", C.c_int32), ("ring_atoms", C.c_int32),
                          ("ring_res", C.c_int32), ("ring_rep", C.c_int32), ("ring_rep_aux", C.c_int32),
                          ("cation_aux", C.c_int32), ("cation_atom", C.c_int32), ("cation_res", C.c_int32),
-                         ("cation_excl_ring", C.c_int32), ("disulfide", C.c_int32)):
+                         ("cation_excl_ring", C.c_int32), ("disulfide", C.c_int32), ("pair_solv_ord", C.c_int32)):
             setattr(t, name, _ptr(arr(name, getattr(topo, name), np.int32), ct))
         t.pair_info = _ptr(arr("pair_info", topo.pair_info, np.uint32), C.c_uint32)
         t.ring_sel_flags = _ptr(arr("ring_sel_flags", topo.ring_sel_flags, np.uint8), C.c_uint8)

@@ -329,6 +329,9 @@ class CompiledTopology:
     hp_base_atoms: np.ndarray = None    # int32 [NHB] pair-atom indices (into pair_atom) of hydrophobic base carbons
     elem_is_c: np.ndarray = None        # uint8 [N] 1 = element C, 2 = element H, 0 = other (for the 1.7 A rule)
     elem_class: np.ndarray = None       # uint8 [K] the same code per element class
+    pair_solv_ord: np.ndarray = None    # int32 [NP] ordinal among solvent pair atoms or -1
+    n_solvent_pair: int = 0
+    n_pair_a: int = 0                   # pair atoms [0, n_pair_a) live in grid A, the rest (unselected solvent) in grid B
 
     @property
     def n_atoms(self):
@@ -395,7 +398,7 @@ def compile_topology(atoms: AtomTable, xyz0: np.ndarray | None = None, sele1: st
     hbu = either & ~(sel("carbon") | sel("sulfur") | solvent) & heavy
     start, adj = atoms.neighbours
     nh = np.zeros(n, np.int64)
-    for i in np.nonzero(hbu)[0]:
+    for i in np.nonzero(hbu | (solvent & heavy))[0]:
         nh[i] = int(atoms.is_hydrogen[adj[start[i]:start[i + 1]]].sum())
 
     # --- hydrophobic base carbons (hydrophobics.py:8-41) ---------------------------------------------
@@ -409,8 +412,14 @@ def compile_topology(atoms: AtomTable, xyz0: np.ndarray | None = None, sele1: st
     # atoms that are neither carbon nor hydrogen by ELEMENT decide the 1.7 A hydrophobic-carbon rule whether or
     # not they are selected, so they join the grid too (they carry no selection bit and never form a contact)
     not_ch = ~np.isin(atoms.element, ["C", "H"])
-    pmask = vdw_atoms | hbu | ((anion | cation) & either & heavy) | (hp_base & either) | not_ch
-    pidx = np.nonzero(pmask)[0]
+    # solvent heavy atoms can mediate water bridges (hbonds.py:64-82) whether or not they are selected
+    solv_heavy = solvent & heavy
+    pmask = vdw_atoms | hbu | ((anion | cation) & either & heavy) | (hp_base & either) | not_ch | solv_heavy
+    # grid B = solvent atoms outside both selections: they only ever pair with non-solvent atoms (as bridge waters),
+    # so the kernels keep them in a second cell list that is searched from the other side only.  They go last.
+    gridb = solv_heavy & ~either
+    pidx = np.concatenate([np.nonzero(pmask & ~gridb)[0], np.nonzero(gridb)[0]])
+    ct.n_pair_a = int((pmask & ~gridb).sum())
     symbols = sorted(set(atoms.element[pidx].tolist())) or ["C"]
     if len(symbols) > 15:
         raise ValueError("more than 15 distinct elements among selected heavy atoms (%d)" % len(symbols))
@@ -441,10 +450,10 @@ def compile_topology(atoms: AtomTable, xyz0: np.ndarray | None = None, sele1: st
 
     info = np.zeros(n, np.uint32)
     info[pidx] = np.array([sym_id[e] for e in atoms.element[pidx]], np.uint32)
-    for bit, mask in ((INFO_S1, m1), (INFO_S2, m2), (INFO_HBU, hbu), (INFO_HAS_H, hbu & (nh > 0)),
+    for bit, mask in ((INFO_S1, m1), (INFO_S2, m2), (INFO_HBU, hbu), (INFO_HAS_H, (hbu | solv_heavy) & (nh > 0)),
                       (INFO_ANION, anion & either), (INFO_CATION, cation & either), (INFO_HPB1, hp_base & m1),
                       (INFO_HPB2, hp_base & m2), (INFO_LIGAND, ligand), (INFO_BB, np.isin(nm, BACKBONE_NAMES)),
-                      (INFO_CYS, rn == "CYS"), (INFO_XBOND, xbond), (INFO_VDW, vdw_atoms)):
+                      (INFO_CYS, rn == "CYS"), (INFO_XBOND, xbond), (INFO_VDW, vdw_atoms), (INFO_SOLV, solv_heavy)):
         info[mask] |= np.uint32(bit)
     ct.pair_atom = pidx.astype(np.int32)
     ct.pair_info = info[pidx]
@@ -452,6 +461,9 @@ def compile_topology(atoms: AtomTable, xyz0: np.ndarray | None = None, sele1: st
     ct.pair_res = ct.atom_res[pidx]
     ct.pair_resid = atoms.resid[pidx].astype(np.int32)
     ct.hp_base_atoms = np.nonzero((ct.pair_info & (INFO_HPB1 | INFO_HPB2)) != 0)[0].astype(np.int32)
+    is_sv = (ct.pair_info & INFO_SOLV) != 0
+    ct.pair_solv_ord = np.where(is_sv, np.cumsum(is_sv) - 1, -1).astype(np.int32)
+    ct.n_solvent_pair = int(is_sv.sum())
     el = atoms.element
     ct.elem_is_c = np.where(el == "C", 1, np.where(el == "H", 2, 0)).astype(np.uint8)
     ct.elem_class = np.array([1 if s == "C" else (2 if s == "H" else 0) for s in symbols], np.uint8)
@@ -461,7 +473,7 @@ def compile_topology(atoms: AtomTable, xyz0: np.ndarray | None = None, sele1: st
     aux, slot = [], {}
     h_start = np.zeros(len(pidx) + 1, np.int32)
     for k, a in enumerate(pidx):
-        if hbu[a]:
+        if hbu[a] or solv_heavy[a]:
             aux.extend(int(h) for h in adj[start[a]:start[a + 1]] if atoms.is_hydrogen[h])
         h_start[k + 1] = len(aux)
     ct.pair_h_start = h_start

@@ -102,6 +102,9 @@ typedef struct chc_topology {
     int32_t n_hp_base;
     int32_t n_bond_adj;
     int32_t same_selection;   /* 1 when the --sele and --sele2 strings are equal */
+    int32_t n_pair_a;         /* pair atoms [0, n_pair_a) are searched against each other (grid A); the rest are
+                                 unselected solvent heavy atoms, searched from the non-solvent side only (grid B) */
+    int32_t n_solvent;        /* solvent heavy atoms among the pair atoms (water-bridge candidates) */
     const int32_t*  pair_atom;        /* [NP] atom index */
     const uint32_t* pair_info;        /* [NP] element class | flag bits (topology.py INFO_*) */
     const int32_t*  pair_lkey;        /* [NP] locality key: same chain & |dresid|<k <=> |dlkey|<k */
@@ -130,6 +133,7 @@ typedef struct chc_topology {
     const int32_t*  hp_base;          /* [n_hp_base] pair indices of hydrophobic base carbons */
     const uint8_t*  atom_class;       /* [n_atoms] 1 = element C, 2 = element H, 0 = other */
     const uint8_t*  elem_class;       /* [K] the same code per element class of the pair atoms */
+    const int32_t*  pair_solv_ord;    /* [NP] ordinal among the solvent pair atoms, -1 for the others */
 } chc_topology;
 
 typedef struct chc_params {
