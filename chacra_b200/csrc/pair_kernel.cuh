@@ -185,13 +185,21 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                             rlen = cells[base + 2] - rb;
                         }
                         J = 0;
-                        for (int r = 0; r < nr; ++r) J += __shfl_sync(FULL, rlen, r);
+#pragma unroll
+                        for (int r = 0; r < 5; ++r) J += __shfl_sync(FULL, rlen, r);
+                        for (int r = 5; r < nr; ++r) J += __shfl_sync(FULL, rlen, r);
                         jj = 0;
                     }
                     // this lane's j of the block
                     int k = jj + lane;
                     j = -1;
-                    for (int r = 0; r < nr; ++r) {
+#pragma unroll
+                    for (int r = 0; r < 5; ++r) {
+                        const int len = __shfl_sync(FULL, rlen, r), beg = __shfl_sync(FULL, rb, r);
+                        if (j < 0 && k >= 0 && k < len) j = beg + k;
+                        k -= len;
+                    }
+                    for (int r = 5; r < nr; ++r) {          // grid B rows (only with unselected solvent)
                         const int len = __shfl_sync(FULL, rlen, r), beg = __shfl_sync(FULL, rb, r);
                         if (j < 0 && k >= 0 && k < len) j = beg + k;
                         k -= len;

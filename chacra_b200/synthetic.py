@@ -79,3 +79,49 @@ class FrameGenerator:
         if self.quantize:
             x = torch.round(x / self.quantize) * self.quantize
         return x.to(torch.float32).contiguous()
+
+
+def solvate_pdb(src: str, dst: str, target_atoms: int, spacing: float = 3.1, clash: float = 2.4, pad: float = 6.0,
+                seed: int = 5) -> int:
+    """Append TIP3 waters (resname TIP3, names OH2 H1 H2, O-H 0.9572 A, H-O-H 104.52 deg) on a jittered lattice around
+    the atoms of `src` until the file holds about `target_atoms` atoms.  Waters whose oxygen
+    lies within `clash` A of a solute heavy atom are left out.  Waters get chain W and resids 1..9999 recycled with
+    segment names W000, W001, ... so that residues stay distinct.  Returns the atom count."""
+    from scipy.spatial import cKDTree
+    atoms = [ln.rstrip("\n") for ln in open(src) if ln[:6] in ("ATOM  ", "HETATM")]
+    xyz = np.array([[float(ln[30:38]), float(ln[38:46]), float(ln[46:54])] for ln in atoms])
+    heavy = np.array([not (ln[12:16].strip()[:1] == "H" or (ln[12:16].strip()[:1].isdigit() and ln[12:16].strip()[1:2] == "H"))
+                      for ln in atoms])
+    n_w = max(0, (target_atoms - len(atoms)) // 3)
+    rng = np.random.Generator(np.random.PCG64(seed))
+    lo, hi = xyz.min(0) - pad, xyz.max(0) + pad
+    # grow the box isotropically until the lattice holds enough sites
+    while True:
+        n_axis = np.maximum(1, np.floor((hi - lo) / spacing).astype(int))
+        if int(np.prod(n_axis)) >= int(1.25 * n_w) + 8:
+            break
+        lo, hi = lo - 1.0, hi + 1.0
+    g = np.stack(np.meshgrid(*[np.arange(k) for k in n_axis], indexing="ij"), -1).reshape(-1, 3)
+    sites = lo + (g + 0.5) * spacing + rng.uniform(-0.35, 0.35, (len(g), 3))
+    near = cKDTree(xyz[heavy]).query(sites, distance_upper_bound=clash)[0]
+    sites = sites[~np.isfinite(near)]
+    # keep the sites closest to the solute first (a droplet), so that small targets still wet the surface
+    d = cKDTree(xyz[heavy]).query(sites)[0]
+    sites = sites[np.argsort(d, kind="stable")[:n_w]]
+    half = np.deg2rad(104.52) / 2
+    out = list(atoms)
+    serial = len(atoms)
+    for k, o in enumerate(sites):
+        # random orientation: orthonormal frame (u, v), hydrogens at +-half angle around u in the (u, v) plane
+        u = rng.normal(size=3); u /= np.linalg.norm(u)
+        t = rng.normal(size=3); v = t - u * (t @ u); v /= np.linalg.norm(v)
+        h1 = o + 0.9572 * (np.cos(half) * u + np.sin(half) * v)
+        h2 = o + 0.9572 * (np.cos(half) * u - np.sin(half) * v)
+        resid, seg = k % 9999 + 1, "W%03d" % (k // 9999)
+        for name, p, el in (("OH2", o, "O"), ("H1", h1, "H"), ("H2", h2, "H")):
+            serial += 1
+            out.append("ATOM  %5d %-4s TIP3W%4d    %8.3f%8.3f%8.3f  1.00  0.00      %-4s%2s" % (
+                serial % 100000, " " + name if len(name) < 4 else name, resid, p[0], p[1], p[2], seg, el))
+    with open(dst, "w") as fh:
+        fh.write("\n".join(out) + "\nEND\n")
+    return len(out)

@@ -64,3 +64,41 @@ def test_static_5y0t_whole_structure_vs_oracle(pdb_5y0t):
     ref = o.intended_counts(res)
     counts = eng.counts(0)
     assert int(counts.sum()) == sum(ref.values()) and int((counts > 0).sum()) == len(ref)
+
+
+@pytest.mark.parametrize("n_atoms,force_large", [(6000, False), (6000, True), (30000, False)])
+def test_solvated_synthetic_vs_oracle(tmp_path, monkeypatch, n_atoms, force_large):
+    """5xnd in a TIP3 droplet (BASELINE.json config-5 recipe, small): every interaction type incl. water bridges,
+    through the shared-memory path (second cell list in shared memory) and the in-place path."""
+    import torch
+    import getcontacts_oracle as o
+    from chacra_b200 import read_pdb, compile_topology
+    from chacra_b200.engine import ContactEngine, ITYPE_NAMES
+    from chacra_b200.synthetic import FrameGenerator, solvate_pdb
+    if force_large:
+        monkeypatch.setenv("CHACRA_FORCE_LARGE", "1")
+    pdb = str(tmp_path / "solv.pdb")
+    solvate_pdb(os.path.join(GOLDEN, "5xnd_topology.pdb"), pdb, n_atoms)
+    atoms = read_pdb(pdb)
+    frames = FrameGenerator(atoms.xyz, 5000, amplitude=0.3, device="cpu").frames(3).numpy()
+    its = ["sb", "pc", "ps", "ts", "vdw", "hb", "hp"]
+    res = o.run(pdb, pdb, its, frames=frames)
+    topo = compile_topology(atoms, frames[0])
+    eng = ContactEngine(topo, its, emit_contacts=True)
+    assert eng.stats()["path"] == (2 if (force_large or n_atoms > 20000) else 1)
+    eng.submit(torch.from_numpy(frames).cuda(), 0, 0)
+    eng.synchronize()
+    rec = eng.drain_contacts()
+
+    def key(f, it, a, b, ws):
+        if b < a:
+            a, b, ws = b, a, ws[::-1] if len(ws) == 2 else ws
+        return (f, it, a, b) + tuple(ws)
+    got = Counter(key(int(r["frame"]), ITYPE_NAMES[r["itype"]], int(r["atom1"]), int(r["atom2"]),
+                      [int(w) for w in (r["water1"], r["water2"]) if w >= 0]) for r in rec)
+    want = Counter(key(c[0], c[1], c[2], c[3], list(c[4:])) for c in res["contacts"])
+    assert any(k[1] == "wb" for k in want) and any(k[1] == "wb2" for k in want)
+    assert got == want
+    ref = o.intended_counts(res)
+    counts = eng.counts(0)
+    assert int(counts.sum()) == sum(ref.values()) and int((counts > 0).sum()) == len(ref)
