@@ -148,6 +148,7 @@ def main():
     import torch.distributed as dist
     from chacra_b200 import compile_topology
     from chacra_b200.engine import ContactEngine
+    from chacra_b200.sharding import merge_count_tables
     from chacra_b200.synthetic import FrameGenerator
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -179,8 +180,7 @@ def main():
         eng.reset_counts()
         for s in range(S):
             eng.submit(traj[s], s, 0)
-        if world > 1:
-            dist.all_reduce(eng.counts_tensor)          # the path's one exchange step (int32 sum, order-free)
+        merge_count_tables(eng.counts_tensor)           # the path's one exchange step (int32 sum, order-free; no-op at N=1)
 
     def barrier():
         if world > 1:
@@ -222,8 +222,7 @@ def main():
         eng.reset_counts()
         for s in range(S):
             eng.submit(host, s, 0)
-        if world > 1:
-            dist.all_reduce(eng.counts_tensor)
+        merge_count_tables(eng.counts_tensor)
         return eng.counts_tensor.cpu()
 
     e2e_step()
