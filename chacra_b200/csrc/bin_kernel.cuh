@@ -15,11 +15,6 @@
 #pragma once
 #include "frame_kernel.cuh"
 
-__device__ __forceinline__ int cell_of(float x, float origin, float inv, int n) {
-    int c = (int)((x - origin) * inv);
-    return min(max(c, 0), n - 1);
-}
-
 struct BinShared {
     int bb_min[3], bb_max[3];
     int scan_carry[33];

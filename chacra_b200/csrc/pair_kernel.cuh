@@ -5,9 +5,10 @@
 // set is a plain shared-memory bitset.  !SMALL = everything is read in place from global memory / L2 and the
 // residue-pair set is a generation-stamped bitset private to the CTA (frame_kernel.cuh count_pair).
 //
-// Pair phase, per warp (cells are handed out 32 at a time through a shared counter):
-//   E1  one cell's atoms (i) against the concatenated half-shell ranges (j): lane-per-j, loop over i, exact float32
-//       d2 against the largest cutoff; survivors are compacted into the warp's queue with ballot/popc
+// Pair phase, per warp (tiles of 32 cell-sorted atoms are handed out through a shared counter):
+//   E1  lane = atom i of the tile; every lane walks its own half-shell ranges (five runs of three x-adjacent cells,
+//       contiguous in the sorted array) 32 slots at a time, exact float32 d2 against the largest cutoff, hits kept as a
+//       per-lane bit mask (no warp votes in the inner loop); the masks are expanded into the warp's queue afterwards
 //   E2  32 survivors at a time: class tests (selection, locality, vdW/hp thresholds, ion and hbond classes)
 //   E3  32 classified pairs at a time: bonded / disulfide / hydrogen-angle tests, residue-pair set, counts, records
 // The three stages form one resumable loop so that E2 and E3 are emitted exactly once in the SASS (the first
@@ -16,9 +17,8 @@
 #include "frame_phases.cuh"
 #include "water_phase.cuh"
 
-#define Q1_CAP 64           // (i, j) survivors per warp
+#define Q1_CAP 96           // (i, j) survivors per warp (>= 64: see the flush in E1)
 #define Q2_CAP 64           // classified pairs per warp
-#define CELL_BLK 8          // cells a warp claims at a time (small blocks keep the end-of-frame tail short)
 
 struct PairLayout {         // shared-memory plan of the pair kernel (bytes)
     int off_rec;            // SMALL: header | spos | aux  (B.fixed_bytes)
@@ -32,28 +32,9 @@ struct PairLayout {         // shared-memory plan of the pair kernel (bytes)
 
 struct PairMisc {
     unsigned long long bar;     // mbarrier of the bulk copies
-    int cursor;                 // next block of CELL_BLK cells
+    int cursor;                 // next tile of 32 sorted atoms
     int nmark;                  // waters with at least one hydrogen bond to a non-solvent atom (this frame)
 };
-
-__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
-    asm volatile(
-        "{\n .reg .pred p;\n"
-        "WAIT_%=:\n mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n @p bra DONE_%=;\n bra WAIT_%=;\n"
-        "DONE_%=:\n}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
-}
-// 1-D bulk async copy global -> shared, completion counted in bytes on the mbarrier (TMA engine, no tensor map)
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
-}
 
 template <int THREADS, bool SMALL>
 __global__ void __launch_bounds__(THREADS, 1)
@@ -139,84 +120,86 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
         // ---- E: pair interactions ------------------------------------------------------------------------------
         const float cut2 = P.pre2;            // largest exact float32 cutoff^2 of the enabled pair types
         int q1n = 0, q2n = 0;
-        // E1 iteration state (warp-uniform): current cell [i, ce), its j ranges, the j block
-        int blk_base = 0; unsigned blk_mask = 0u; int my_cs = 0, my_ce = 0;
-        int i = 0, ce = 0, cs = 0, J = 0, jj = 0;
-        int rb = 0, rlen = 0;                 // lanes 0..nr-1: begin / length of neighbour range `lane`
-        // ranges 0..4: half shell of grid A; ranges 5..13 (only with unselected solvent): the full 3x3 rows of grid B
+        // E1 state.  A tile = 32 consecutive cell-sorted atoms of grid A, one per lane (atom i).  Lane ranges:
+        // 0..4 = half shell of grid A (own row from the slot after i to the end of cell x+1, then rows (y+1,z) (y-1,z+1)
+        // (y,z+1) (y+1,z+1) from x-1 to x+1); 5..13 (only with unselected solvent) = the full 3x3 rows of grid B.
+        const int nA = T.n_pair_a, last = T.n_pair - 1;
         const int nr = T.n_pair_a < T.n_pair ? 14 : 5;
-        int j = -1; float4 pj = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int ntiles = (nA + 31) >> 5;
+        int r = nr, k0 = 0, maxlen = 0;                // warp-uniform: current range, chunk offset, longest lane range
+        int my_i = -1, my_c = 0, beg = 0, len = 0;     // this lane's atom, its cell, its current range
+        float ix = 0.f, iy = 0.f, iz = 0.f;
+        unsigned mask = 0u; int mbase = 0;             // this lane's hits of the last chunk not yet queued: j = mbase + bit
         bool exhausted = false;
         for (;;) {
             // ---- E1 ----
             while (q1n < 32 && !exhausted) {
-                if (i >= ce) {
-                    jj += 32;
-                    if (jj >= J) {                     // next non-empty cell
-                        while (blk_mask == 0u) {
-                            int base = 0;
-                            if (lane == 0) base = atomicAdd(&M->cursor, CELL_BLK);
-                            base = __shfl_sync(FULL, base, 0);
-                            if (base >= ncell) { exhausted = true; break; }
-                            blk_base = base;
-                            const int c = base + lane;
-                            const bool mine = lane < CELL_BLK && c < ncell;
-                            my_cs = mine ? cells[c] : 0;
-                            my_ce = mine ? cells[c + 1] : 0;
-                            blk_mask = __ballot_sync(FULL, my_ce > my_cs);
-                        }
-                        if (exhausted) break;
-                        const int b = __ffs(blk_mask) - 1;
-                        blk_mask &= blk_mask - 1u;
-                        cs = __shfl_sync(FULL, my_cs, b);
-                        ce = __shfl_sync(FULL, my_ce, b);
-                        const int c = blk_base + b;
-                        // half shell: own row from the cell itself to the end of cell x+1, then rows
-                        // (y+1,z) (y-1,z+1) (y,z+1) (y+1,z+1) from x-1 to x+1
-                        if (lane < 5) {
-                            const int dy = (lane == 1 || lane == 4) - (lane == 2), dz = lane >= 2;
-                            const int base = c + dy * px + dz * pxy;
-                            rb = lane == 0 ? cs : cells[base - 1];
-                            rlen = cells[base + 2] - rb;
-                        } else if (lane < nr) {
-                            const int r = lane - 5;
-                            const int base = c + ncell + (r % 3 - 1) * px + (r / 3 - 1) * pxy;
-                            rb = cells[base - 1];
-                            rlen = cells[base + 2] - rb;
-                        }
-                        J = 0;
+                if (__any_sync(FULL, mask != 0u)) {
+                    // queue the pending hits, whole lanes at a time, as far as the queue has room (q1n < 32 here and a
+                    // lane holds at most 32 hits, so the first pending lane always fits: Q1_CAP - 32 >= 32)
+                    const int cnt = __popc(mask);
+                    int incl = cnt;
 #pragma unroll
-                        for (int r = 0; r < 5; ++r) J += __shfl_sync(FULL, rlen, r);
-                        for (int r = 5; r < nr; ++r) J += __shfl_sync(FULL, rlen, r);
-                        jj = 0;
+                    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += t; }
+                    const bool ok = incl <= Q1_CAP - q1n;
+                    if (ok) {
+                        int at = q1n + incl - cnt;
+                        unsigned m = mask;
+                        while (m) {
+                            const int k = __ffs(m) - 1;
+                            m &= m - 1u;
+                            q1[at] = (unsigned)my_i; q1[Q1_CAP + at] = (unsigned)(mbase + k);
+                            ++at;
+                        }
+                        mask = 0u;
                     }
-                    // this lane's j of the block
-                    int k = jj + lane;
-                    j = -1;
-#pragma unroll
-                    for (int r = 0; r < 5; ++r) {
-                        const int len = __shfl_sync(FULL, rlen, r), beg = __shfl_sync(FULL, rb, r);
-                        if (j < 0 && k >= 0 && k < len) j = beg + k;
-                        k -= len;
-                    }
-                    for (int r = 5; r < nr; ++r) {          // grid B rows (only with unselected solvent)
-                        const int len = __shfl_sync(FULL, rlen, r), beg = __shfl_sync(FULL, rb, r);
-                        if (j < 0 && k >= 0 && k < len) j = beg + k;
-                        k -= len;
-                    }
-                    if (j >= 0) pj = spos[j];
-                    i = cs;
+                    q1n += __reduce_max_sync(FULL, ok ? incl : 0);
+                    continue;
                 }
-                const float4 pi = spos[i];
-                const float d2 = dist2_exact(pi.x, pi.y, pi.z, pj.x, pj.y, pj.z);
-                const bool hit = j > i && d2 <= cut2;
-                const unsigned bal = __ballot_sync(FULL, hit);
-                if (hit) {
-                    const int at = q1n + __popc(bal & ((1u << lane) - 1u));
-                    q1[at] = (unsigned)i; q1[Q1_CAP + at] = (unsigned)j;
+                k0 += 32;
+                if (k0 >= maxlen) {                    // next range, or next tile
+                    if (++r >= nr) {
+                        int t = 0;
+                        if (lane == 0) t = atomicAdd(&M->cursor, 1);
+                        t = __shfl_sync(FULL, t, 0);
+                        if (t >= ntiles) { exhausted = true; break; }
+                        my_i = t * 32 + lane;
+                        if (my_i < nA) {
+                            const float4 p = spos[my_i];
+                            ix = p.x; iy = p.y; iz = p.z;
+                            my_c = (cell_of(iz, hdr->org[2], hdr->inv, hdr->nc[2]) + 1) * pxy +
+                                   (cell_of(iy, hdr->org[1], hdr->inv, hdr->nc[1]) + 1) * px +
+                                   cell_of(ix, hdr->org[0], hdr->inv, hdr->nc[0]) + 1;
+                        } else my_i = -1;
+                        r = 0;
+                    }
+                    len = 0;
+                    if (my_i >= 0) {
+                        if (r == 0) { beg = my_i + 1; len = cells[my_c + 2] - beg; }
+                        else {
+                            int base;
+                            if (r < 5) base = my_c + ((r == 1 || r == 4) - (r == 2)) * px + (r >= 2 ? pxy : 0);
+                            else { const int q = r - 5; base = my_c + ncell + (q % 3 - 1) * px + (q / 3 - 1) * pxy; }
+                            beg = cells[base - 1];
+                            len = cells[base + 2] - beg;
+                        }
+                    }
+                    maxlen = __reduce_max_sync(FULL, len);
+                    k0 = 0;
+                    if (maxlen == 0) continue;
                 }
-                q1n += __popc(bal);
-                ++i;
+                // 32 candidate slots of every lane's range: exact float32 d2 against the largest cutoff
+                const int n = min(32, maxlen - k0);
+                const int lim = len - k0;
+                mbase = beg + k0;
+                unsigned m = 0u;
+#pragma unroll 4
+                for (int k = 0; k < n; ++k) {
+                    const float4 pj = spos[min(mbase + k, last)];
+                    const float d2 = dist2_exact(ix, iy, iz, pj.x, pj.y, pj.z);
+                    if (k < lim && d2 <= cut2) m |= 1u << k;
+                }
+                mask = m;
             }
             if (q1n == 0 && q2n == 0) break;           // only reachable when exhausted
             __syncwarp();
