@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(CSRC, "libchacra_b200.so")
 SOURCES = ["chacra_b200.cu"]
-HEADERS = ["device_types.cuh", "frame_kernel.cuh", "frame_phases.cuh", "bin_kernel.cuh", "pair_kernel.cuh", "water_phase.cuh",
+HEADERS = ["device_types.cuh", "bin_tma_kernel.cuh", "frame_kernel.cuh", "frame_phases.cuh", "bin_kernel.cuh", "pair_kernel.cuh", "water_phase.cuh",
            os.path.join("..", "..", "include", "chacra_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-fmad=false", "-std=c++17",
               "-shared", "-Xcompiler", "-fPIC"]

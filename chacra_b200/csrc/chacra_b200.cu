@@ -7,6 +7,7 @@
 #include <vector>
 #include <algorithm>
 #include "bin_kernel.cuh"
+#include "bin_tma_kernel.cuh"
 #include "pair_kernel.cuh"
 
 #define PAIR_THREADS 768
@@ -20,7 +21,8 @@ struct chc_ctx {
     DevParams P{};
     PairLayout L{};
     BinLayout B{};
-    bool small_path = true;
+    BinTmaLayout Y{};
+    bool small_path = true, bin_tma = false;
     int bin_smem = 0, bin_grid = 0, pair_grid = 0, bin_threads = 256, bin_variant = 0;
     int64_t chunk_frames = 0;
     unsigned char* binned = nullptr;
@@ -63,6 +65,10 @@ static int upload(chc_ctx* ctx, const Tp* host, size_t n, const Tp** dev) {
 
 static const void* bin_kernel_fn(int variant, int* threads) {
     switch (variant) {
+        case 3: if (threads) *threads = 512; return (const void*)bin_frames_tma_kernel<512, 8, true>;
+        case 4: if (threads) *threads = 512; return (const void*)bin_frames_tma_kernel<512, 16, true>;
+        case 5: if (threads) *threads = 512; return (const void*)bin_frames_tma_kernel<512, 8, false>;
+        case 6: if (threads) *threads = 512; return (const void*)bin_frames_tma_kernel<512, 16, false>;
         case 1: if (threads) *threads = 512; return (const void*)bin_frames_kernel<512, 8, 2>;
         case 2: if (threads) *threads = 1024; return (const void*)bin_frames_kernel<1024, 8, 1>;
         default: if (threads) *threads = 1024; return (const void*)bin_frames_kernel<1024, 0, 1>;
@@ -224,7 +230,20 @@ extern "C" int chc_create(chc_ctx** out, const chc_topology* t, const chc_params
     else CK(cudaFuncSetAttribute(pair_frames_kernel<PAIR_THREADS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->L.total));
     // binning kernel variant: registers hold the frame's pair atoms when they fit (one HBM pass), else three gather passes
     ctx->bin_variant = T.n_pair <= 512 * 8 ? 1 : (T.n_pair <= 1024 * 8 ? 2 : 0);
+    // frames that fit twice in shared memory stream through bulk async copies (bin_tma_kernel.cuh)
+    {
+        BinTmaLayout& Y = ctx->Y;
+        Y.cap_groups = (ctx->B.max_cells + 2047) / 2048;
+        Y.buf_bytes = (int)al16(std::max<size_t>(12 * (size_t)T.n_atoms + 28, (size_t)ctx->B.off_aux + 8 * (size_t)std::max(T.n_hp_base, 0)));
+        Y.off_auxtab = (int)(16 * (size_t)Y.cap_groups * 512);
+        Y.off_buf0 = (int)(((size_t)Y.off_auxtab + 6 * (size_t)std::max(T.n_aux, 0) + 127) & ~size_t(127));
+        Y.off_buf1 = (int)(((size_t)Y.off_buf0 + Y.buf_bytes + 127) & ~size_t(127));
+        Y.total = Y.off_buf1 + Y.buf_bytes;
+        if (Y.cap_groups <= BT_MAXG && T.n_pair <= 8192 && 3 * (size_t)T.n_atoms < 65536 && (size_t)Y.total + 1024 <= SMEM_LIMIT) ctx->bin_variant = T.n_pair <= 4096 ? 3 : 4;
+    }
     if (getenv("CHACRA_BIN_VARIANT")) ctx->bin_variant = atoi(getenv("CHACRA_BIN_VARIANT"));
+    ctx->bin_tma = ctx->bin_variant >= 3;
+    if (ctx->bin_tma) ctx->bin_smem = ctx->Y.total;
     const void* bin_fn = bin_kernel_fn(ctx->bin_variant, &ctx->bin_threads);
     CK(cudaFuncSetAttribute(bin_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->bin_smem));
     ctx->pair_grid = ctx->sm_count;
@@ -356,14 +375,21 @@ extern "C" int chc_submit_frames(chc_ctx* ctx, int state, const float* d_xyz, in
             else { CK(cudaEventCreate(&ev.a)); CK(cudaEventCreate(&ev.b)); CK(cudaEventCreate(&ev.c)); }
             CK(cudaEventRecord(ev.a, stream));
         }
+        const bool hp_on = (ctx->P.itypes & CHC_IT_HP) && ctx->T.n_hp_base > 0;
+        const bool fuse_hp = hp_on && ctx->bin_tma && ctx->T.same;      // the binning CTA answers the 1.7 A query itself
         {
-            int nn = n; long long fi = first_index + c0, fs = frame_stride, fr0 = frag0; int ff = F;
-            void* args[] = {&ctx->T, &ctx->P, &ctx->B, &x, &fs, &nn, &fi, &ff, &fr0, &ctx->binned, &ctx->hpmask};
+            int nn = n; long long fi = first_index + c0, fs = frame_stride, fr0 = frag0; int ff = F, fuse = fuse_hp ? 1 : 0;
+            BinTmaLayout Y = ctx->Y;
+            Y.open_phase = (int)(fi % F);
+            long long slot0 = fi / F - frag0;
+            void* args_reg[] = {&ctx->T, &ctx->P, &ctx->B, &x, &fs, &nn, &fi, &ff, &fr0, &ctx->binned, &ctx->hpmask};
+            void* args_tma[] = {&ctx->T, &ctx->P, &ctx->B, &Y, &x, &fs, &nn, &ff, &slot0, &ctx->binned, &ctx->hpmask, &fuse};
             CK(cudaLaunchKernel(bin_kernel_fn(ctx->bin_variant, nullptr), dim3(std::min(n, ctx->bin_grid)), dim3(ctx->bin_threads),
-                                args, ctx->bin_smem, stream));
+                                ctx->bin_tma ? args_tma : args_reg, ctx->bin_smem, stream));
         }
         CK(cudaGetLastError());
-        if ((ctx->P.itypes & CHC_IT_HP) && ctx->T.n_hp_base > 0) {
+        if (ctx->timing) CK(cudaEventRecord(ev.b, stream));        // the hydrophobic query kernel (below) is timed with the pair kernel
+        if (hp_on && !fuse_hp) {
             const int64_t fi = first_index + c0;
             const int64_t f0 = (F - fi % F) % F;                  // first fragment-opening frame of the chunk
             if (f0 < n) {
@@ -375,7 +401,6 @@ extern "C" int chc_submit_frames(chc_ctx* ctx, int state, const float* d_xyz, in
                 ctx->st.kernel_launches++;
             }
         }
-        if (ctx->timing) CK(cudaEventRecord(ev.b, stream));
         const int grid = std::min(n, ctx->pair_grid);
         if (ctx->small_path)
             pair_frames_kernel<PAIR_THREADS, true><<<grid, PAIR_THREADS, ctx->L.total, stream>>>(

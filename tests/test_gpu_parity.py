@@ -112,3 +112,23 @@ def test_fragment_boundaries_and_chunking(oracle_5xnd):
     run = _engine_run(top, frames, ["hp", "vdw", "hb"], host=True)
     assert run["contacts"] == _oracle_sets(res)[0]
     _check_counts(run, res)
+
+
+def test_binning_kernel_variants_agree(oracle_5xnd, monkeypatch):
+    """Every binning kernel (bulk-copy double-buffered 3/4 staged, 5/6 direct stores; register 1/2; gather 0) must hand the pair kernel the same
+    frame: identical contacts and counts over 3 fragments (the fused and the stand-alone hydrophobic query included),
+    with device chunks that start on unaligned frame addresses (1 629 atoms: 12 N is not a multiple of 16)."""
+    base = oracle_5xnd["frames"]
+    frames = np.ascontiguousarray(base[np.arange(250) % 20])
+    frames[100:200] = base[(np.arange(100) + 7) % 20]
+    top = os.path.join(GOLDEN, "5xnd_topology.pdb")
+    runs = {}
+    for variant in ("3", "0", "1", "2", "4", "5", "6"):
+        monkeypatch.setenv("CHACRA_BIN_VARIANT", variant)
+        runs[variant] = _engine_run(top, frames, ALL)
+        assert runs[variant]["contacts"] == runs["3"]["contacts"], variant
+        assert np.array_equal(runs[variant]["counts"], runs["3"]["counts"]), variant
+        assert runs[variant]["near"] == runs["3"]["near"], variant
+    # the first 20 frames are the fixture itself
+    want, _ = _oracle_sets(oracle_5xnd)
+    assert {c for c in runs["3"]["contacts"] if c[0] < 20} == want
