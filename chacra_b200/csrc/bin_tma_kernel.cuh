@@ -1,34 +1,34 @@
-// bin_tma_kernel.cuh -- the coordinate-streaming kernel for frames that fit twice in shared memory.
+// bin_tma_kernel.cuh -- the coordinate-streaming kernel for frames that fit in shared memory.
 //
 // Same job and same output record as bin_frames_kernel (bin_kernel.cuh), organised around the HBM pipe instead of
-// around the sort: one persistent CTA per SM owns two frame buffers in shared memory; whole frames arrive through
-// 1-D bulk async copies (cp.async.bulk -> SASS UBLKCP, completion counted on an mbarrier), so the coordinate
-// stream is perfectly coalesced, costs no registers and no issue slots, and the copy of frame k+2 is in flight
-// while frames k and k+1 are sorted.  Per frame (THREADS threads, <= APT pair atoms per thread):
+// around the sort.  Whole frames arrive through 1-D bulk async copies (cp.async.bulk -> SASS UBLKCP, completion counted
+// on an mbarrier): the coordinate stream is perfectly coalesced and costs no registers and no issue slots.  Two
+// shapes of the same code (template NBUF):
+//   NBUF = 1  two 256-thread CTAs per SM, one frame buffer each.  A CTA copies its frame to registers (P1), releases
+//             the buffer and has the NEXT frame's bulk copy in flight while it sorts the current one; the two CTAs of
+//             an SM are independent instruction streams, so the barrier-separated phases of one hide behind the other.
+//   NBUF = 2  one 512-thread CTA per SM, two frame buffers, the sorted record leaves through a bulk async store.
+// Per frame (<= APT pair atoms per thread):
 //   P1  gather this thread's pair atoms from the shared-memory frame into registers, bounding box (warp redux +
-//       shared atomics), aux atoms straight to the record, zero the cell counters      -> barrier; buffer released,
-//       next bulk copy issued
-//   P2  cell of every atom; shared atomicAdd returns the atom's rank inside its cell    -> barrier
-//   P3  exclusive scan of the counters in use (int4 groups per thread), starts to shared memory and to the record
-//   P4  scatter x, y, z, flags|index to start[cell] + rank of a shared-memory image of the record (the released frame
-//       buffer), which one bulk async store then writes out; the buffer is refilled once that store has read it
+//       shared atomics), aux atoms straight to the record (one float per thread, coalesced)          -> barrier
+//   P2  cell of every atom; shared atomicAdd returns the atom's rank inside its cell                -> barrier
+//   P3  exclusive scan of the counters in use (int4 groups per thread)                              -> barrier
+//   P4  scatter x, y, z, flags|index to start[cell] + rank; cell starts to the record (coalesced)
 //   P5  (frames that open a 100-frame fragment, equal selections) hydrophobic carbon membership: 1.7 A query on the
-//       grid just built (hydrophobics.py:8-41): the sorted atoms and a work list of base carbons are staged in the
-//       released frame buffer, one warp per base carbon, lane = (row of three cells, slot stride)
+//       grid just built (hydrophobics.py:8-41), thread = base carbon, sorted atoms staged in the frame buffer
 // Everything that is the same for all threads of a frame (grid origin, cell edge, grid dimensions) costs issue slots in
-// every warp, so the CTA is 16 fat warps (8..16 atoms per thread) rather than 32 thin ones.
+// every warp, so the CTAs are few fat warps (up to 16 atoms per thread) rather than many thin ones.
 // Algorithmic HBM traffic: 12 B x n_atoms read per frame; the record (written once) is consumed from L2.
 #pragma once
 #include "frame_kernel.cuh"
 
-
-#define BT_MAXG 8               // int4 groups of cell counters per thread in the scan (512 threads: 16 384 counters)
+#define BT_MAXG 8               // int4 groups of cell counters per thread in the scan
 
 struct BinTmaLayout {
-    int off_buf0, off_buf1;     // bytes from the start of dynamic shared memory (cell counters come first)
-    int buf_bytes;              // one frame buffer: >= 12 n_atoms + 28 and >= 32 + 16 n_pair + 8 n_hp_base (record image + P5 list)
+    int off_buf0, off_buf1;     // frame buffers, bytes from the start of dynamic shared memory (cell counters come first)
+    int buf_bytes;              // one frame buffer: >= 12 n_atoms + 28 and >= 32 + 16 n_pair + 4 n_hp_base (P5 / record image)
     int cap_groups;             // capacity of the counter array in int4 groups per thread
-    int off_auxtab;             // uint16 [3 n_aux]: float offset inside the frame of every aux coordinate
+    int max_cells;              // cells the grid may use (<= BinLayout::max_cells and < 4 cap_groups THREADS)
     int open_phase;             // first_index % fragment_frames of the launch (set per launch)
     int total;
 };
@@ -44,20 +44,20 @@ struct BinTmaShared {
 // is already in [0, n - 1]; same value as cell_of
 __device__ __forceinline__ int cell_in(float x, float origin, float inv) { return (int)((x - origin) * inv); }
 
-// STAGE: the sorted atoms go to a shared-memory image of the record and leave through one bulk async store (the
-// buffer is refilled when the store has read it); !STAGE: scattered 16-byte global stores, buffer refilled right after P1.
-template <int THREADS, int APT, bool STAGE>
-__global__ void __launch_bounds__(THREADS, 1)
+template <int THREADS, int APT, int NBUF>
+__global__ void __launch_bounds__(THREADS, NBUF == 1 ? 2 : 1)
 bin_frames_tma_kernel(DevTopo T, DevParams P, BinLayout B, BinTmaLayout Y, const float* __restrict__ xyz, long long frame_stride,
                       int n_frames, int frag_frames, long long frag_slot0, unsigned char* __restrict__ binned,
                       unsigned char* __restrict__ hpmask, int fuse_hp) {
-    extern __shared__ __align__(128) unsigned char bsm[];      // counters int[4 cap_groups THREADS] | frame buffer 0 | frame buffer 1
+    constexpr bool STAGE = NBUF == 2;     // record image in shared memory + bulk store, or direct global stores
+    extern __shared__ __align__(128) unsigned char bsm[];      // counters int[4 cap_groups THREADS] | frame buffer(s)
     __shared__ BinTmaShared M;
     int* cells = reinterpret_cast<int*>(bsm);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int NP = T.n_pair;
     const bool gridb = T.n_pair_a < NP;
     const unsigned frame_bytes = 12u * (unsigned)T.n_atoms;
+    const int dummy = 4 * Y.cap_groups * THREADS - 1;          // counter nobody reads: padding slots count there
     // bulk copy of frame f into buffer b: source rounded down / size rounded up to 16 bytes (the consumer skips the
     // leading floats); the rounding never leaves the 16-byte granule the caller's allocation ends in
     auto issue = [&](int f, int b) {
@@ -68,89 +68,91 @@ bin_frames_tma_kernel(DevTopo T, DevParams P, BinLayout B, BinTmaLayout Y, const
         mbar_expect_tx(&M.full[b], bytes);
         bulk_g2s(bsm + (b ? Y.off_buf1 : Y.off_buf0), reinterpret_cast<const void*>(a0), bytes, &M.full[b]);
     };
-    if (tid == 0) {                       // the first two frames are on their way before anything else happens
+    if (tid == 0) {                       // the first frame(s) are on their way before anything else happens
         mbar_init(&M.full[0], 1); mbar_init(&M.full[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        if (blockIdx.x < n_frames) issue(blockIdx.x, 0);
-        if (blockIdx.x + gridDim.x < n_frames) issue(blockIdx.x + gridDim.x, 1);
+#pragma unroll
+        for (int k = 0; k < NBUF; ++k)
+            if (blockIdx.x + k * gridDim.x < n_frames) issue(blockIdx.x + k * gridDim.x, k);
         M.nlist = 0;
     }
     if (tid < 3) {
         M.bb_min[0][tid] = M.bb_min[1][tid] = 0x7fffffff;
         M.bb_max[0][tid] = M.bb_max[1][tid] = (int)0x80000000;
     }
-    int r_atom[APT]; unsigned r_info[APT];
+    // this thread's pair atoms p = tid + k THREADS (float offset inside the frame); padding slots repeat the thread's
+    // first atom (or atom 0), so that P1 and P2 run without branches: they change neither the box nor any real counter
+    int r_atom[APT];
 #pragma unroll
     for (int k = 0; k < APT; ++k) {
         const int p = tid + k * THREADS;
-        r_atom[k] = p < NP ? 3 * T.pair_atom[p] : -1;                 // float offset inside the frame
-        r_info[k] = p < NP ? ((T.pair_info[p] & I_WMASK) | ((unsigned)p << I_PIDX_SHIFT)) : 0u;
+        r_atom[k] = 3 * T.pair_atom[p < NP ? p : min(tid, NP - 1)];
     }
-    unsigned short* auxtab = reinterpret_cast<unsigned short*>(bsm + Y.off_auxtab);
+    const unsigned short* __restrict__ auxtab = T.aux_off16;      // 6 n_aux bytes, read every frame: stays in L1
     const int n_aux3 = 3 * T.n_aux;
-    for (int e = tid; e < n_aux3; e += THREADS) { const int s = e / 3; auxtab[e] = (unsigned short)(3 * T.aux_atom[s] + (e - 3 * s)); }
     for (int g = 0; g < Y.cap_groups; ++g) reinterpret_cast<int4*>(cells)[g * THREADS + tid] = make_int4(0, 0, 0, 0);
     __syncthreads();
     int it = 0, used_groups = 0;          // int4 groups per thread the previous frame dirtied
+    int fphase = (Y.open_phase + (int)blockIdx.x) % frag_frames;      // (open_phase + f) % frag_frames, kept incrementally
     int refill_f = -1, refill_b = 0;      // buffer whose record image is being stored: refill it once the store has read it
     for (int f = blockIdx.x; f < n_frames; f += gridDim.x, ++it) {
-        const int b = it & 1;
+        const int b = NBUF == 2 ? (it & 1) : 0, bi = it & 1;
         unsigned char* rec = binned + (size_t)f * B.stride;
         unsigned char* fbuf = bsm + (b ? Y.off_buf1 : Y.off_buf0);
         const float* Xs = reinterpret_cast<const float*>(fbuf) +
                           (int)((reinterpret_cast<unsigned long long>(xyz + (size_t)f * frame_stride) & 15ull) >> 2);
         const int fidx = Y.open_phase + f;                      // position inside the fragment sequence of this launch
-        const bool opens = fuse_hp && (fidx % frag_frames) == 0;
+        if (it > 0) { fphase += (int)gridDim.x; while (fphase >= frag_frames) fphase -= frag_frames; }
+        const bool opens = fuse_hp && fphase == 0;
         // counters the previous frame used go back to zero (nobody reads them any more: S6)
         for (int g = 0; g < used_groups; ++g) reinterpret_cast<int4*>(cells)[tid * used_groups + g] = make_int4(0, 0, 0, 0);
         if (tid == 0 && refill_f >= 0) {
             asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
             if (refill_f < n_frames) issue(refill_f, refill_b);
         }
-        mbar_wait(&M.full[b], (unsigned)(it >> 1) & 1u);
+        refill_f = -1;
+        mbar_wait(&M.full[b], (unsigned)(NBUF == 2 ? (it >> 1) : it) & 1u);
         // ---- P1: registers <- shared frame, bounding box, aux atoms -----------------------------------------------------
         float rx[APT], ry[APT], rz[APT];
         {
             float lo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, hi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
 #pragma unroll
-            for (int k = 0; k < APT; ++k)
-                if (r_atom[k] >= 0) {
-                    const float* q = Xs + r_atom[k];
-                    rx[k] = q[0]; ry[k] = q[1]; rz[k] = q[2];
-                } else { rx[k] = ry[k] = rz[k] = 0.f; }
+            for (int k = 0; k < APT; ++k) {
+                const float* q = Xs + r_atom[k];
+                rx[k] = q[0]; ry[k] = q[1]; rz[k] = q[2];
+            }
 #pragma unroll
-            for (int k = 0; k < APT; ++k)
-                if (r_atom[k] >= 0) {
-                    lo[0] = fminf(lo[0], rx[k]); hi[0] = fmaxf(hi[0], rx[k]);
-                    lo[1] = fminf(lo[1], ry[k]); hi[1] = fmaxf(hi[1], ry[k]);
-                    lo[2] = fminf(lo[2], rz[k]); hi[2] = fmaxf(hi[2], rz[k]);
-                }
+            for (int k = 0; k < APT; ++k) {
+                lo[0] = fminf(lo[0], rx[k]); hi[0] = fmaxf(hi[0], rx[k]);
+                lo[1] = fminf(lo[1], ry[k]); hi[1] = fmaxf(hi[1], ry[k]);
+                lo[2] = fminf(lo[2], rz[k]); hi[2] = fmaxf(hi[2], rz[k]);
+            }
 #pragma unroll
             for (int d = 0; d < 3; ++d) {
                 const int a = __reduce_min_sync(FULL, f2ord(lo[d])), c = __reduce_max_sync(FULL, f2ord(hi[d]));
-                if (lane == 0) { atomicMin(&M.bb_min[b][d], a); atomicMax(&M.bb_max[b][d], c); }
+                if (lane == 0) { atomicMin(&M.bb_min[bi][d], a); atomicMax(&M.bb_max[bi][d], c); }
             }
             // aux atoms (donor hydrogens, ring atoms, cations) straight to the record, one float per thread: coalesced
             float* aux = reinterpret_cast<float*>(rec + B.off_aux);
 #pragma unroll 4
-            for (int e = tid; e < n_aux3; e += THREADS) aux[e] = Xs[auxtab[e]];
+            for (int e = tid; e < n_aux3; e += THREADS) aux[e] = Xs[__ldg(&auxtab[e])];
         }
         __syncthreads();                                                                    // S1: the frame lives in registers
-        if (!STAGE && tid == 0 && !opens && f + 2 * (int)gridDim.x < n_frames) issue(f + 2 * gridDim.x, b);
+        if (!STAGE && tid == 0 && !opens && f + NBUF * (int)gridDim.x < n_frames) issue(f + NBUF * gridDim.x, b);
         if (tid >= 32 && tid < 35) {      // bounding box of the next frame starts empty (read again only after later barriers)
-            M.bb_min[b ^ 1][tid - 32] = 0x7fffffff; M.bb_max[b ^ 1][tid - 32] = (int)0x80000000;
+            M.bb_min[bi ^ 1][tid - 32] = 0x7fffffff; M.bb_max[bi ^ 1][tid - 32] = (int)0x80000000;
         }
         float org[3], inv; int nc[3];
         {
             float ext[3];
 #pragma unroll
-            for (int d = 0; d < 3; ++d) { org[d] = ord2f(M.bb_min[b][d]); ext[d] = ord2f(M.bb_max[b][d]) - org[d]; }
+            for (int d = 0; d < 3; ++d) { org[d] = ord2f(M.bb_min[bi][d]); ext[d] = ord2f(M.bb_max[bi][d]) - org[d]; }
             float cell = P.cell;
             for (;;) {                    // the cell edge only ever grows: every pair within the cutoff stays in adjacent cells
                 inv = 1.0f / cell;
 #pragma unroll
                 for (int d = 0; d < 3; ++d) nc[d] = (int)(ext[d] * inv) + 1;
-                if ((long long)(nc[0] + 2) * (nc[1] + 2) * (nc[2] + 2) * (gridb ? 2 : 1) + 1 <= B.max_cells) break;
+                if ((long long)(nc[0] + 2) * (nc[1] + 2) * (nc[2] + 2) * (gridb ? 2 : 1) + 1 <= Y.max_cells) break;
                 cell *= 1.25f;
             }
         }
@@ -159,15 +161,22 @@ bin_frames_tma_kernel(DevTopo T, DevParams P, BinLayout B, BinTmaLayout Y, const
         const int groups = (nkey + 4 * THREADS) / (4 * THREADS);        // covers counters 0..nkey
         used_groups = groups;
         // ---- P2: cell of every atom; the shared atomic returns the atom's rank inside its cell -----------------------
-        int r_c[APT], r_rank[APT];
+        unsigned r_cr[APT];               // cell | rank << 16   (max_cells <= 16 384, n_pair <= 8 192 on this path)
 #pragma unroll
         for (int k = 0; k < APT; ++k) {
-            r_c[k] = (cell_in(rz[k], org[2], inv) + 1) * pxy + (cell_in(ry[k], org[1], inv) + 1) * px + cell_in(rx[k], org[0], inv) + 1;
-            if (gridb && tid + k * THREADS >= T.n_pair_a) r_c[k] += ncell;
+            const int p = tid + k * THREADS;
+            int c = (cell_in(rz[k], org[2], inv) + 1) * pxy + (cell_in(ry[k], org[1], inv) + 1) * px + cell_in(rx[k], org[0], inv) + 1;
+            r_cr[k] = (unsigned)(p < NP ? c : dummy);
+        }
+        if (gridb) {                      // unselected solvent sorts into the second set of cells
+#pragma unroll
+            for (int k = 0; k < APT; ++k) {
+                const int p = tid + k * THREADS;
+                if (p >= T.n_pair_a && p < NP) r_cr[k] += (unsigned)ncell;
+            }
         }
 #pragma unroll
-        for (int k = 0; k < APT; ++k)
-            if (r_atom[k] >= 0) r_rank[k] = atomicAdd(&cells[r_c[k]], 1);
+        for (int k = 0; k < APT; ++k) r_cr[k] |= (unsigned)atomicAdd(&cells[r_cr[k]], 1) << 16;
         __syncthreads();                                                                    // S2
         // ---- P3: exclusive scan; thread t owns counters [4 groups t, 4 groups (t + 1)) ---------------------------------
         {
@@ -188,7 +197,7 @@ bin_frames_tma_kernel(DevTopo T, DevParams P, BinLayout B, BinTmaLayout Y, const
             const int w0 = lane < (THREADS >> 5) ? M.carry[lane] : 0;
             int w = w0;
 #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULL, w, o); if (lane >= o) w += t; }
+            for (int o = 1; o < (THREADS >> 5); o <<= 1) { const int t = __shfl_up_sync(FULL, w, o); if (lane >= o) w += t; }
             int run = __shfl_sync(FULL, w - w0, warp) + incl - s;
 #pragma unroll
             for (int g = 0; g < BT_MAXG; ++g)
@@ -199,22 +208,26 @@ bin_frames_tma_kernel(DevTopo T, DevParams P, BinLayout B, BinTmaLayout Y, const
                 }
         }
         __syncthreads();                                                                    // S5
-        // ---- P4: scatter (into the record image in the released frame buffer, or straight to the record) ----------------
+        // ---- P4: scatter (into the record image in the frame buffer, or straight to the record) -----------------------
         unsigned char* img = (STAGE || opens) ? fbuf : rec;
         float4* stage = reinterpret_cast<float4*>(fbuf + B.off_spos);
         int* list = reinterpret_cast<int*>(fbuf + B.off_aux);           // P5 work list: sorted slots of the base carbons
         {
-            int dst[APT];
+            int dst[APT]; unsigned info[APT];
 #pragma unroll
-            for (int k = 0; k < APT; ++k) dst[k] = r_atom[k] >= 0 ? cells[r_c[k]] + r_rank[k] : 0;
+            for (int k = 0; k < APT; ++k) {
+                const int p = tid + k * THREADS;
+                dst[k] = cells[r_cr[k] & 0xffffu] + (int)(r_cr[k] >> 16);
+                info[k] = p < NP ? ((__ldg(&T.pair_info[p]) & I_WMASK) | ((unsigned)p << I_PIDX_SHIFT)) : 0u;
+            }
             float4* out = reinterpret_cast<float4*>(img + B.off_spos);
 #pragma unroll
             for (int k = 0; k < APT; ++k)
-                if (r_atom[k] >= 0) out[dst[k]] = make_float4(rx[k], ry[k], rz[k], __uint_as_float(r_info[k]));
+                if (tid + k * THREADS < NP) out[dst[k]] = make_float4(rx[k], ry[k], rz[k], __uint_as_float(info[k]));
             if (opens) {
 #pragma unroll
                 for (int k = 0; k < APT; ++k)
-                    if (r_atom[k] >= 0 && (r_info[k] & (I_HP1 | I_HP2))) list[atomicAdd(&M.nlist, 1)] = dst[k];
+                    if (tid + k * THREADS < NP && (info[k] & (I_HP1 | I_HP2))) list[atomicAdd(&M.nlist, 1)] = dst[k];
             }
             // cell starts 0..nkey (the last one = total) to the record, coalesced
             int4* cells_out = reinterpret_cast<int4*>(rec + B.off_cells);
@@ -234,9 +247,7 @@ bin_frames_tma_kernel(DevTopo T, DevParams P, BinLayout B, BinTmaLayout Y, const
                              ::"l"(rec), "r"(smem_u32(fbuf)), "r"((unsigned)B.off_aux) : "memory");
                 asm volatile("cp.async.bulk.commit_group;" ::: "memory");
             }
-            refill_f = f + 2 * (int)gridDim.x; refill_b = b;
-        } else {
-            refill_f = -1;                // refilled right after S1
+            refill_f = f + NBUF * (int)gridDim.x; refill_b = b;
         }
         // ---- P5: hydrophobic carbon membership of the fragment this frame opens (equal selections) ---------------------
         // thread = base carbon; the 1.7 A ball touches at most 2 x 2 x 2 cells (cell edge >= 3.5 A)

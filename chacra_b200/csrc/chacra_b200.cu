@@ -22,7 +22,7 @@ struct chc_ctx {
     PairLayout L{};
     BinLayout B{};
     BinTmaLayout Y{};
-    bool small_path = true, bin_tma = false;
+    bool small_path = true, bin_tma = false; int tma_apt = 8;
     int bin_smem = 0, bin_grid = 0, pair_grid = 0, bin_threads = 256, bin_variant = 0;
     int64_t chunk_frames = 0;
     unsigned char* binned = nullptr;
@@ -63,12 +63,25 @@ static int upload(chc_ctx* ctx, const Tp* host, size_t n, const Tp** dev) {
     return CHC_OK;
 }
 
-static const void* bin_kernel_fn(int variant, int* threads) {
+// apt: atoms per thread of the bulk-copy binning kernels (chosen by plan_bin_tma in chc_create)
+static const void* bin_kernel_fn(int variant, int apt, int* threads) {
     switch (variant) {
-        case 3: if (threads) *threads = 512; return (const void*)bin_frames_tma_kernel<512, 8, true>;
-        case 4: if (threads) *threads = 512; return (const void*)bin_frames_tma_kernel<512, 16, true>;
-        case 5: if (threads) *threads = 512; return (const void*)bin_frames_tma_kernel<512, 8, false>;
-        case 6: if (threads) *threads = 512; return (const void*)bin_frames_tma_kernel<512, 16, false>;
+        case 3:               // two 256-thread CTAs per SM, one frame buffer each
+            if (threads) *threads = 256;
+            switch (apt) {
+                case 2: return (const void*)bin_frames_tma_kernel<256, 2, 1>;
+                case 4: return (const void*)bin_frames_tma_kernel<256, 4, 1>;
+                case 6: return (const void*)bin_frames_tma_kernel<256, 6, 1>;
+                case 8: return (const void*)bin_frames_tma_kernel<256, 8, 1>;
+                case 10: return (const void*)bin_frames_tma_kernel<256, 10, 1>;
+                case 12: return (const void*)bin_frames_tma_kernel<256, 12, 1>;
+                case 13: return (const void*)bin_frames_tma_kernel<256, 13, 1>;
+                case 14: return (const void*)bin_frames_tma_kernel<256, 14, 1>;
+                default: return (const void*)bin_frames_tma_kernel<256, 16, 1>;
+            }
+        case 4:               // one 512-thread CTA per SM, two frame buffers, bulk store of the record image
+            if (threads) *threads = 512;
+            return apt <= 8 ? (const void*)bin_frames_tma_kernel<512, 8, 2> : (const void*)bin_frames_tma_kernel<512, 16, 2>;
         case 1: if (threads) *threads = 512; return (const void*)bin_frames_kernel<512, 8, 2>;
         case 2: if (threads) *threads = 1024; return (const void*)bin_frames_kernel<1024, 8, 1>;
         default: if (threads) *threads = 1024; return (const void*)bin_frames_kernel<1024, 0, 1>;
@@ -89,7 +102,7 @@ static int plan(chc_ctx* ctx) {
     B.off_aux = B.off_spos + 16 * T.n_pair;
     B.fixed_bytes = (int)al16((size_t)B.off_aux + 12 * (size_t)std::max(T.n_aux, 1));
     B.off_cells = B.fixed_bytes;
-    const size_t queues = al16(8 * (size_t)warps * Q1_CAP) + al16(16 * (size_t)warps * Q2_CAP);
+    const size_t queues = al16(8 * (size_t)warps * Q1_CAP) + al16(32 * (size_t)warps * Q2_CAP);
     const size_t tables = 2 * al16(4 * (size_t)T.K * T.K) + al16(sizeof(PairMisc));
     // ~3 cells per pair atom keeps the cells at the cutoff size for protein-like densities
     size_t want_cells = std::min<size_t>(49152, std::max<size_t>(2048, 3 * (size_t)T.n_pair));
@@ -115,7 +128,7 @@ static int plan(chc_ctx* ctx) {
         L.bits_words = (int)((ctx->n_pairs + 23) / 24);
     }
     L.off_q1 = (int)off; off += al16(8 * (size_t)warps * Q1_CAP);
-    L.off_q2 = (int)off; off += al16(16 * (size_t)warps * Q2_CAP);
+    L.off_q2 = (int)off; off += al16(32 * (size_t)warps * Q2_CAP);
     L.off_tv = (int)off; off += al16(4 * (size_t)T.K * T.K);
     L.off_th = (int)off; off += al16(4 * (size_t)T.K * T.K);
     L.off_misc = (int)off; off += al16(sizeof(PairMisc));
@@ -184,6 +197,12 @@ extern "C" int chc_create(chc_ctx** out, const chc_topology* t, const chc_params
     UP(ring_rep, t->ring_rep, NR); UP(ring_rep_aux, t->ring_rep_aux, NR);
     UP(cat_aux, t->cation_aux, NC); UP(cat_atom, t->cation_atom, NC); UP(cat_flags, t->cation_flags, NC); UP(cat_res, t->cation_res, NC); UP(cat_excl, t->cation_excl_ring, NC);
     UP(disulfide, t->disulfide, 2 * (size_t)t->n_disulfide);
+    {
+        std::vector<unsigned short> off((3 * (size_t)std::max(t->n_aux, 0) + 7) / 8 * 8 + 8, 0);
+        for (int k = 0; k < t->n_aux; ++k)
+            for (int d = 0; d < 3; ++d) off[3 * (size_t)k + d] = (unsigned short)(3 * (long long)t->aux_atom[k] + d);   // used only when 3 n_atoms < 65536
+        UP(aux_off16, off.data(), off.size());
+    }
     UP(vcut, t->vdw_cut, K2); UP(hp_base, t->hp_base, t->n_hp_base); UP(atom_class, t->atom_class, t->n_atoms);
     // fold the measure-contacts cutoffs into the per-element-pair acceptance thresholds
     DevParams& P = ctx->P;
@@ -230,21 +249,39 @@ extern "C" int chc_create(chc_ctx** out, const chc_topology* t, const chc_params
     else CK(cudaFuncSetAttribute(pair_frames_kernel<PAIR_THREADS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->L.total));
     // binning kernel variant: registers hold the frame's pair atoms when they fit (one HBM pass), else three gather passes
     ctx->bin_variant = T.n_pair <= 512 * 8 ? 1 : (T.n_pair <= 1024 * 8 ? 2 : 0);
-    // frames that fit twice in shared memory stream through bulk async copies (bin_tma_kernel.cuh)
-    {
+    // frames that fit in shared memory stream through bulk async copies (bin_tma_kernel.cuh)
+    auto plan_bin_tma = [&](int variant) -> bool {
         BinTmaLayout& Y = ctx->Y;
-        Y.cap_groups = (ctx->B.max_cells + 2047) / 2048;
-        Y.buf_bytes = (int)al16(std::max<size_t>(12 * (size_t)T.n_atoms + 28, (size_t)ctx->B.off_aux + 8 * (size_t)std::max(T.n_hp_base, 0)));
-        Y.off_auxtab = (int)(16 * (size_t)Y.cap_groups * 512);
-        Y.off_buf0 = (int)(((size_t)Y.off_auxtab + 6 * (size_t)std::max(T.n_aux, 0) + 127) & ~size_t(127));
-        Y.off_buf1 = (int)(((size_t)Y.off_buf0 + Y.buf_bytes + 127) & ~size_t(127));
-        Y.total = Y.off_buf1 + Y.buf_bytes;
-        if (Y.cap_groups <= BT_MAXG && T.n_pair <= 8192 && 3 * (size_t)T.n_atoms < 65536 && (size_t)Y.total + 1024 <= SMEM_LIMIT) ctx->bin_variant = T.n_pair <= 4096 ? 3 : 4;
+        const int threads = variant == 3 ? 256 : 512, nbuf = variant == 3 ? 1 : 2, ctas = variant == 3 ? 2 : 1;
+        const int apt_need = (T.n_pair + threads - 1) / threads;
+        if (T.n_pair < 1 || apt_need > 16 || 3 * (size_t)T.n_atoms >= 65536) return false;
+        static const int apts[] = {2, 4, 6, 8, 10, 12, 13, 14, 16};
+        int apt = 16;
+        for (int a : apts) if (a >= apt_need) { apt = a; break; }
+        if (variant == 4) apt = apt_need <= 8 ? 8 : 16;
+        Y.buf_bytes = (int)al16(std::max<size_t>(12 * (size_t)T.n_atoms + 28, (size_t)ctx->B.off_aux + 4 * (size_t)std::max(T.n_hp_base, 0)));
+        // as many counters as fit (a full grid needs B.max_cells of them; fewer only means coarser cells for wide frames)
+        for (int cap = std::min(BT_MAXG, (ctx->B.max_cells + 4 * threads) / (4 * threads)); cap >= 1; --cap) {
+            Y.cap_groups = cap;
+            Y.max_cells = std::min(ctx->B.max_cells, 4 * cap * threads - 1);
+            Y.off_buf0 = (int)((16 * (size_t)cap * threads + 127) & ~size_t(127));
+            Y.off_buf1 = nbuf == 2 ? (int)(((size_t)Y.off_buf0 + Y.buf_bytes + 127) & ~size_t(127)) : Y.off_buf0;
+            Y.total = Y.off_buf1 + Y.buf_bytes;
+            // ~1.5 cells per pair atom keep the cell edge at the cutoff for protein-like densities
+            if (Y.max_cells < 2048 || 2 * (long long)Y.max_cells < 3 * (long long)T.n_pair) break;
+            if ((size_t)ctas * ((size_t)Y.total + 1024 + 512) <= SMEM_LIMIT) { ctx->tma_apt = apt; return true; }
+        }
+        return false;
+    };
+    if (plan_bin_tma(3)) ctx->bin_variant = 3;
+    else if (plan_bin_tma(4)) ctx->bin_variant = 4;
+    if (const char* e = getenv("CHACRA_BIN_VARIANT")) {           // test hook
+        const int v = atoi(e);
+        if (v < 3 || plan_bin_tma(v)) ctx->bin_variant = v;
     }
-    if (getenv("CHACRA_BIN_VARIANT")) ctx->bin_variant = atoi(getenv("CHACRA_BIN_VARIANT"));
     ctx->bin_tma = ctx->bin_variant >= 3;
     if (ctx->bin_tma) ctx->bin_smem = ctx->Y.total;
-    const void* bin_fn = bin_kernel_fn(ctx->bin_variant, &ctx->bin_threads);
+    const void* bin_fn = bin_kernel_fn(ctx->bin_variant, ctx->tma_apt, &ctx->bin_threads);
     CK(cudaFuncSetAttribute(bin_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->bin_smem));
     ctx->pair_grid = ctx->sm_count;
     if (const char* e = getenv("CHACRA_PAIR_GRID")) ctx->pair_grid = std::max(1, std::min(ctx->sm_count, atoi(e)));   // test hook
@@ -253,11 +290,13 @@ extern "C" int chc_create(chc_ctx** out, const chc_topology* t, const chc_params
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bin_fn, ctx->bin_threads, ctx->bin_smem));
         ctx->bin_grid = ctx->sm_count * std::max(1, per_sm);
     }
-    // frames per (bin, pair) launch pair: the binned records of a chunk should stay in L2 (126 MB) between the two
+    // frames per (bin, pair) launch pair: large enough that launch latency, the kernels' prologues and their tails are
+    // amortised (the pair kernel is issue bound and does not care whether the records come from L2 or HBM), bounded by
+    // ~1.5 GB of binned records and 80 frames per SM
     {
-        int64_t by_l2 = (int64_t)((80u << 20) / (size_t)ctx->B.stride);
+        int64_t by_mem = (int64_t)((1500ull << 20) / (size_t)ctx->B.stride);
         int64_t g = ctx->pair_grid;
-        ctx->chunk_frames = std::max<int64_t>(g, by_l2 / g * g);
+        ctx->chunk_frames = std::max<int64_t>(g, std::min<int64_t>(by_mem, 80 * g) / g * g);
         if (const char* e = getenv("CHACRA_CHUNK_FRAMES")) ctx->chunk_frames = std::max<int64_t>(1, atoll(e));
     }
     CK(cudaMalloc(&ctx->binned, (size_t)ctx->chunk_frames * (size_t)ctx->B.stride));
@@ -384,7 +423,7 @@ extern "C" int chc_submit_frames(chc_ctx* ctx, int state, const float* d_xyz, in
             long long slot0 = fi / F - frag0;
             void* args_reg[] = {&ctx->T, &ctx->P, &ctx->B, &x, &fs, &nn, &fi, &ff, &fr0, &ctx->binned, &ctx->hpmask};
             void* args_tma[] = {&ctx->T, &ctx->P, &ctx->B, &Y, &x, &fs, &nn, &ff, &slot0, &ctx->binned, &ctx->hpmask, &fuse};
-            CK(cudaLaunchKernel(bin_kernel_fn(ctx->bin_variant, nullptr), dim3(std::min(n, ctx->bin_grid)), dim3(ctx->bin_threads),
+            CK(cudaLaunchKernel(bin_kernel_fn(ctx->bin_variant, ctx->tma_apt, nullptr), dim3(std::min(n, ctx->bin_grid)), dim3(ctx->bin_threads),
                                 ctx->bin_tma ? args_tma : args_reg, ctx->bin_smem, stream));
         }
         CK(cudaGetLastError());
@@ -425,8 +464,8 @@ extern "C" int chc_submit_frames_host(chc_ctx* ctx, int state, const float* h_xy
     CK(cudaSetDevice(ctx->device));
     const int F = ctx->prm.fragment_frames;
     const size_t fbytes = 12 * (size_t)ctx->T.n_atoms;
-    // chunk = whole fragments, about 64 MiB
-    int64_t chunk = std::max<int64_t>(1, (int64_t)((64u << 20) / fbytes) / F) * F;
+    // chunk = whole fragments, about 256 MiB
+    int64_t chunk = std::max<int64_t>(1, (int64_t)((256u << 20) / fbytes) / F) * F;
     if (ctx->stage_frames < chunk) {
         CK(cudaDeviceSynchronize());
         for (int k = 0; k < 2; ++k) {

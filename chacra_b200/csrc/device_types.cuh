@@ -43,7 +43,7 @@ struct DevTopo {
     const int* pair_solv_ord;
     const int* pair_atom; const unsigned* pair_info; const int* pair_lkey; const int* pair_res; const int* pair_resid;
     const int* pair_h_start; const int* pair_bond_start; const int* pair_bond_adj;
-    const int* aux_atom;
+    const int* aux_atom; const unsigned short* aux_off16;   // float offsets 3 a + d of the aux coordinates (small frames)
     const int* ring_aux; const int* ring_pc_aux; const int* ring_sel_aux; const unsigned char* ring_sel_flags;
     const int* ring_atoms; const int* ring_res; const int* ring_rep; const int* ring_rep_aux;
     const int* cat_aux; const int* cat_atom; const unsigned char* cat_flags; const int* cat_res; const int* cat_excl;

@@ -18,7 +18,7 @@
 #include "water_phase.cuh"
 
 #define Q1_CAP 96           // (i, j) survivors per warp (>= 64: see the flush in E1)
-#define Q2_CAP 64           // classified pairs per warp
+#define Q2_CAP 64           // classified pairs per warp and queue (plain, polar)
 
 struct PairLayout {         // shared-memory plan of the pair kernel (bytes)
     int off_rec;            // SMALL: header | spos | aux  (B.fixed_bytes)
@@ -48,7 +48,7 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
     float* th = reinterpret_cast<float*>(smem + L.off_th);
     PairMisc* M = reinterpret_cast<PairMisc*>(smem + L.off_misc);
     unsigned* q1 = reinterpret_cast<unsigned*>(smem + L.off_q1) + warp * (2 * Q1_CAP);       // i[Q1_CAP], j[Q1_CAP]
-    unsigned* q2 = reinterpret_cast<unsigned*>(smem + L.off_q2) + warp * (4 * Q2_CAP);       // i, j, cls, d2
+    unsigned* q2 = reinterpret_cast<unsigned*>(smem + L.off_q2) + warp * (8 * Q2_CAP);       // plain | polar: i, j, cls, d2
     for (int k = tid; k < T.K * T.K; k += THREADS) { tv[k] = T.tv[k]; th[k] = T.th[k]; }
     int* s_lkey = reinterpret_cast<int*>(smem + L.off_lkey);
     unsigned* bits;
@@ -119,7 +119,7 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
         }
         // ---- E: pair interactions ------------------------------------------------------------------------------
         const float cut2 = P.pre2;            // largest exact float32 cutoff^2 of the enabled pair types
-        int q1n = 0, q2n = 0;
+        int q1n = 0, q2n = 0, q3n = 0;
         // E1 state.  A tile = 32 consecutive cell-sorted atoms of grid A, one per lane (atom i).  Lane ranges:
         // 0..4 = half shell of grid A (own row from the slot after i to the end of cell x+1, then rows (y+1,z) (y-1,z+1)
         // (y,z+1) (y+1,z+1) from x-1 to x+1); 5..13 (only with unselected solvent) = the full 3x3 rows of grid B.
@@ -201,9 +201,10 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                 }
                 mask = m;
             }
-            if (q1n == 0 && q2n == 0) break;           // only reachable when exhausted
+            if (q1n == 0 && q2n == 0 && q3n == 0) break;           // only reachable when exhausted
             __syncwarp();
-            // ---- E2: up to 32 survivors ----
+            // ---- E2: up to 32 survivors; classified pairs go to the plain queue (vdW / hydrophobic only) or to the
+            //      polar queue (salt bridge, hydrogen bond, water edge), so that an E3 batch runs one kind of code ----
             {
                 const int nb = min(q1n, 32);
                 q1n -= nb;
@@ -212,21 +213,28 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                     ei = q1[q1n + lane]; ej = q1[Q1_CAP + q1n + lane];
                     cls = e2_classify(T, P, F, spos[ei], spos[ej], d2);
                 }
-                const unsigned bal = __ballot_sync(FULL, cls != 0u);
+                const bool polar = (cls & (C_SB | C_HB | C_HBW)) != 0u;
+                const unsigned balp = __ballot_sync(FULL, polar), balv = __ballot_sync(FULL, cls != 0u && !polar);
                 if (cls) {
-                    const int at = q2n + __popc(bal & ((1u << lane) - 1u));
-                    q2[at] = ei; q2[Q2_CAP + at] = ej; q2[2 * Q2_CAP + at] = cls; q2[3 * Q2_CAP + at] = __float_as_uint(d2);
+                    const unsigned below = (1u << lane) - 1u;
+                    unsigned* q = polar ? q2 + 4 * Q2_CAP : q2;
+                    const int at = polar ? q3n + __popc(balp & below) : q2n + __popc(balv & below);
+                    q[at] = ei; q[Q2_CAP + at] = ej; q[2 * Q2_CAP + at] = cls; q[3 * Q2_CAP + at] = __float_as_uint(d2);
                 }
-                q2n += __popc(bal);
+                q2n += __popc(balv); q3n += __popc(balp);
                 __syncwarp();
             }
-            // ---- E3: 32 classified pairs (or the rest when nothing else is left) ----
-            if (q2n >= 32 || (exhausted && q1n == 0 && q2n > 0)) {
-                const int nb = min(q2n, 32);
-                q2n -= nb;
+            // ---- E3: 32 classified pairs of one queue (or the rest when nothing else is left) ----
+            const bool drain = exhausted && q1n == 0;
+            while (q2n >= 32 || q3n >= 32 || (drain && (q2n | q3n) != 0)) {
+                const bool plain = q2n >= 32 || (q3n < 32 && q2n > 0);
+                int& qn = plain ? q2n : q3n;
+                const unsigned* q = plain ? q2 : q2 + 4 * Q2_CAP;
+                const int nb = min(qn, 32);
+                qn -= nb;
                 if (lane < nb)
-                    e3_finish(T, P, O, F, (int)q2[q2n + lane], (int)q2[Q2_CAP + q2n + lane], q2[2 * Q2_CAP + q2n + lane],
-                              __uint_as_float(q2[3 * Q2_CAP + q2n + lane]));
+                    e3_finish(T, P, O, F, (int)q[qn + lane], (int)q[Q2_CAP + qn + lane], q[2 * Q2_CAP + qn + lane],
+                              __uint_as_float(q[3 * Q2_CAP + qn + lane]));
                 __syncwarp();
             }
         }
