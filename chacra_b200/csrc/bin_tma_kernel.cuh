@@ -22,13 +22,14 @@
 #pragma once
 #include "frame_kernel.cuh"
 
-#define BT_MAXG 8               // int4 groups of cell counters per thread in the scan
+#define BT_MAXG 8               // uint4 groups (8 16-bit counters each) per thread in the scan
 
 struct BinTmaLayout {
+    int off_auxtab;             // uint16 [3 n_aux]: float offset inside the frame of every aux coordinate
     int off_buf0, off_buf1;     // frame buffers, bytes from the start of dynamic shared memory (cell counters come first)
     int buf_bytes;              // one frame buffer: >= 12 n_atoms + 28 and >= 32 + 16 n_pair + 4 n_hp_base (P5 / record image)
-    int cap_groups;             // capacity of the counter array in int4 groups per thread
-    int max_cells;              // cells the grid may use (<= BinLayout::max_cells and < 4 cap_groups THREADS)
+    int cap_groups;             // capacity of the counter array in uint4 groups (8 counters) per thread
+    int max_cells;              // cells the grid may use (<= BinLayout::max_cells and < 8 cap_groups THREADS)
     int open_phase;             // first_index % fragment_frames of the launch (set per launch)
     int total;
 };
@@ -50,14 +51,17 @@ bin_frames_tma_kernel(DevTopo T, DevParams P, BinLayout B, BinTmaLayout Y, const
                       int n_frames, int frag_frames, long long frag_slot0, unsigned char* __restrict__ binned,
                       unsigned char* __restrict__ hpmask, int fuse_hp) {
     constexpr bool STAGE = NBUF == 2;     // record image in shared memory + bulk store, or direct global stores
-    extern __shared__ __align__(128) unsigned char bsm[];      // counters int[4 cap_groups THREADS] | frame buffer(s)
+    extern __shared__ __align__(128) unsigned char bsm[];      // counters u16[8 cap_groups THREADS] | aux table | frame buffer(s)
     __shared__ BinTmaShared M;
-    int* cells = reinterpret_cast<int*>(bsm);
+    // cell counters / starts are 16 bit (counts and starts are at most n_pair <= 8 192): half the shared memory and
+    // half the scan traffic of 32-bit ones; atomics work on the containing word
+    unsigned short* cells = reinterpret_cast<unsigned short*>(bsm);
+    unsigned* cellw = reinterpret_cast<unsigned*>(bsm);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int NP = T.n_pair;
     const bool gridb = T.n_pair_a < NP;
     const unsigned frame_bytes = 12u * (unsigned)T.n_atoms;
-    const int dummy = 4 * Y.cap_groups * THREADS - 1;          // counter nobody reads: padding slots count there
+    const int dummy = 8 * Y.cap_groups * THREADS - 1;          // counter nobody reads: padding slots count there
     // bulk copy of frame f into buffer b: source rounded down / size rounded up to 16 bytes (the consumer skips the
     // leading floats); the rounding never leaves the 16-byte granule the caller's allocation ends in
     auto issue = [&](int f, int b) {
@@ -88,9 +92,14 @@ bin_frames_tma_kernel(DevTopo T, DevParams P, BinLayout B, BinTmaLayout Y, const
         const int p = tid + k * THREADS;
         r_atom[k] = 3 * T.pair_atom[p < NP ? p : min(tid, NP - 1)];
     }
-    const unsigned short* __restrict__ auxtab = T.aux_off16;      // 6 n_aux bytes, read every frame: stays in L1
+    {                                     // float offsets of the aux coordinates: a shared-memory copy (read every frame)
+        const uint4* src = reinterpret_cast<const uint4*>(T.aux_off16);
+        uint4* dst = reinterpret_cast<uint4*>(bsm + Y.off_auxtab);
+        for (int q = tid; q < (3 * T.n_aux + 7) / 8; q += THREADS) dst[q] = __ldg(&src[q]);
+    }
+    const unsigned short* auxtab = reinterpret_cast<const unsigned short*>(bsm + Y.off_auxtab);
     const int n_aux3 = 3 * T.n_aux;
-    for (int g = 0; g < Y.cap_groups; ++g) reinterpret_cast<int4*>(cells)[g * THREADS + tid] = make_int4(0, 0, 0, 0);
+    for (int g = 0; g < Y.cap_groups; ++g) reinterpret_cast<uint4*>(bsm)[g * THREADS + tid] = make_uint4(0u, 0u, 0u, 0u);
     __syncthreads();
     int it = 0, used_groups = 0;          // int4 groups per thread the previous frame dirtied
     int fphase = (Y.open_phase + (int)blockIdx.x) % frag_frames;      // (open_phase + f) % frag_frames, kept incrementally
@@ -105,7 +114,7 @@ bin_frames_tma_kernel(DevTopo T, DevParams P, BinLayout B, BinTmaLayout Y, const
         if (it > 0) { fphase += (int)gridDim.x; while (fphase >= frag_frames) fphase -= frag_frames; }
         const bool opens = fuse_hp && fphase == 0;
         // counters the previous frame used go back to zero (nobody reads them any more: S6)
-        for (int g = 0; g < used_groups; ++g) reinterpret_cast<int4*>(cells)[tid * used_groups + g] = make_int4(0, 0, 0, 0);
+        for (int g = 0; g < used_groups; ++g) reinterpret_cast<uint4*>(bsm)[tid * used_groups + g] = make_uint4(0u, 0u, 0u, 0u);
         if (tid == 0 && refill_f >= 0) {
             asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
             if (refill_f < n_frames) issue(refill_f, refill_b);
@@ -135,7 +144,7 @@ bin_frames_tma_kernel(DevTopo T, DevParams P, BinLayout B, BinTmaLayout Y, const
             // aux atoms (donor hydrogens, ring atoms, cations) straight to the record, one float per thread: coalesced
             float* aux = reinterpret_cast<float*>(rec + B.off_aux);
 #pragma unroll 4
-            for (int e = tid; e < n_aux3; e += THREADS) aux[e] = Xs[__ldg(&auxtab[e])];
+            for (int e = tid; e < n_aux3; e += THREADS) aux[e] = Xs[auxtab[e]];
         }
         __syncthreads();                                                                    // S1: the frame lives in registers
         if (!STAGE && tid == 0 && !opens && f + NBUF * (int)gridDim.x < n_frames) issue(f + NBUF * gridDim.x, b);
@@ -158,10 +167,10 @@ bin_frames_tma_kernel(DevTopo T, DevParams P, BinLayout B, BinTmaLayout Y, const
         }
         const int px = nc[0] + 2, pxy = px * (nc[1] + 2), ncell = pxy * (nc[2] + 2);
         const int nkey = gridb ? 2 * ncell : ncell;
-        const int groups = (nkey + 4 * THREADS) / (4 * THREADS);        // covers counters 0..nkey
+        const int groups = (nkey + 8 * THREADS) / (8 * THREADS);        // covers counters 0..nkey
         used_groups = groups;
         // ---- P2: cell of every atom; the shared atomic returns the atom's rank inside its cell -----------------------
-        unsigned r_cr[APT];               // cell | rank << 16   (max_cells <= 16 384, n_pair <= 8 192 on this path)
+        unsigned r_cr[APT];               // cell | rank << 16   (max_cells <= 16 384 < 65 536, n_pair <= 8 192 on this path)
 #pragma unroll
         for (int k = 0; k < APT; ++k) {
             const int p = tid + k * THREADS;
@@ -176,18 +185,23 @@ bin_frames_tma_kernel(DevTopo T, DevParams P, BinLayout B, BinTmaLayout Y, const
             }
         }
 #pragma unroll
-        for (int k = 0; k < APT; ++k) r_cr[k] |= (unsigned)atomicAdd(&cells[r_cr[k]], 1) << 16;
+        for (int k = 0; k < APT; ++k) {
+            const unsigned sh = (r_cr[k] & 1u) << 4;
+            const unsigned old = atomicAdd(&cellw[r_cr[k] >> 1], 1u << sh);
+            r_cr[k] |= ((old >> sh) & 0xffffu) << 16;
+        }
         __syncthreads();                                                                    // S2
-        // ---- P3: exclusive scan; thread t owns counters [4 groups t, 4 groups (t + 1)) ---------------------------------
+        // ---- P3: exclusive scan; thread t owns counters [8 groups t, 8 groups (t + 1)) -----------------------------------
         {
-            int4 v[BT_MAXG];
-            int s = 0;
+            uint4 v[BT_MAXG];
+            unsigned s2 = 0u;             // even counters in the low half, odd ones in the high half (no carry: sums <= 8 192)
 #pragma unroll
             for (int g = 0; g < BT_MAXG; ++g)
                 if (g < groups) {
-                    v[g] = reinterpret_cast<const int4*>(cells)[tid * groups + g];
-                    s += (v[g].x + v[g].y) + (v[g].z + v[g].w);
+                    v[g] = reinterpret_cast<const uint4*>(bsm)[tid * groups + g];
+                    s2 += (v[g].x + v[g].y) + (v[g].z + v[g].w);
                 }
+            const int s = (int)((s2 & 0xffffu) + (s2 >> 16));
             int incl = s;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += t; }
@@ -198,13 +212,18 @@ bin_frames_tma_kernel(DevTopo T, DevParams P, BinLayout B, BinTmaLayout Y, const
             int w = w0;
 #pragma unroll
             for (int o = 1; o < (THREADS >> 5); o <<= 1) { const int t = __shfl_up_sync(FULL, w, o); if (lane >= o) w += t; }
-            int run = __shfl_sync(FULL, w - w0, warp) + incl - s;
+            unsigned run = (unsigned)(__shfl_sync(FULL, w - w0, warp) + incl - s);
+            auto ex2 = [&](unsigned word) {      // two counters -> their two exclusive starts
+                const unsigned lo = word & 0xffffu, e = run | ((run + lo) << 16);
+                run += lo + (word >> 16);
+                return e;
+            };
 #pragma unroll
             for (int g = 0; g < BT_MAXG; ++g)
                 if (g < groups) {
-                    int4 e;
-                    e.x = run; run += v[g].x; e.y = run; run += v[g].y; e.z = run; run += v[g].z; e.w = run; run += v[g].w;
-                    reinterpret_cast<int4*>(cells)[tid * groups + g] = e;
+                    uint4 e;
+                    e.x = ex2(v[g].x); e.y = ex2(v[g].y); e.z = ex2(v[g].z); e.w = ex2(v[g].w);
+                    reinterpret_cast<uint4*>(bsm)[tid * groups + g] = e;
                 }
         }
         __syncthreads();                                                                    // S5
@@ -217,7 +236,7 @@ bin_frames_tma_kernel(DevTopo T, DevParams P, BinLayout B, BinTmaLayout Y, const
 #pragma unroll
             for (int k = 0; k < APT; ++k) {
                 const int p = tid + k * THREADS;
-                dst[k] = cells[r_cr[k] & 0xffffu] + (int)(r_cr[k] >> 16);
+                dst[k] = (int)cells[r_cr[k] & 0xffffu] + (int)(r_cr[k] >> 16);
                 info[k] = p < NP ? ((__ldg(&T.pair_info[p]) & I_WMASK) | ((unsigned)p << I_PIDX_SHIFT)) : 0u;
             }
             float4* out = reinterpret_cast<float4*>(img + B.off_spos);
@@ -231,7 +250,10 @@ bin_frames_tma_kernel(DevTopo T, DevParams P, BinLayout B, BinTmaLayout Y, const
             }
             // cell starts 0..nkey (the last one = total) to the record, coalesced
             int4* cells_out = reinterpret_cast<int4*>(rec + B.off_cells);
-            for (int q = tid; 4 * q <= nkey; q += THREADS) cells_out[q] = reinterpret_cast<const int4*>(cells)[q];
+            for (int q = tid; 4 * q <= nkey; q += THREADS) {
+                const uint2 w = reinterpret_cast<const uint2*>(bsm)[q];
+                cells_out[q] = make_int4((int)(w.x & 0xffffu), (int)(w.x >> 16), (int)(w.y & 0xffffu), (int)(w.y >> 16));
+            }
         }
         if (tid == 0) {
             BinHeader h;
@@ -265,8 +287,8 @@ bin_frames_tma_kernel(DevTopo T, DevParams P, BinLayout B, BinTmaLayout Y, const
                     for (int z = z0; z <= z1; ++z)
                         for (int y = y0; y <= y1; ++y) {
                             const int row = g * ncell + (z + 1) * pxy + (y + 1) * px + 1;
-                            const int je = cells[row + x1 + 1];
-                            for (int j = cells[row + x0]; j < je; ++j) {
+                            const int je = (int)cells[row + x1 + 1];
+                            for (int j = (int)cells[row + x0]; j < je; ++j) {
                                 const float4 o = stage[j];
                                 if (dist2_exact(o.x, o.y, o.z, me.x, me.y, me.z) <= r2 &&
                                     !((P.elem_ch_mask >> (__float_as_uint(o.w) & I_ELEM)) & 1u)) other = 1u;

@@ -261,10 +261,12 @@ extern "C" int chc_create(chc_ctx** out, const chc_topology* t, const chc_params
         if (variant == 4) apt = apt_need <= 8 ? 8 : 16;
         Y.buf_bytes = (int)al16(std::max<size_t>(12 * (size_t)T.n_atoms + 28, (size_t)ctx->B.off_aux + 4 * (size_t)std::max(T.n_hp_base, 0)));
         // as many counters as fit (a full grid needs B.max_cells of them; fewer only means coarser cells for wide frames)
-        for (int cap = std::min(BT_MAXG, (ctx->B.max_cells + 4 * threads) / (4 * threads)); cap >= 1; --cap) {
+        const size_t auxtab = al16(6 * (size_t)std::max(T.n_aux, 1));
+        for (int cap = std::min(BT_MAXG, (ctx->B.max_cells + 8 * threads) / (8 * threads)); cap >= 1; --cap) {
             Y.cap_groups = cap;
-            Y.max_cells = std::min(ctx->B.max_cells, 4 * cap * threads - 1);
-            Y.off_buf0 = (int)((16 * (size_t)cap * threads + 127) & ~size_t(127));
+            Y.max_cells = std::min(ctx->B.max_cells, 8 * cap * threads - 1);
+            Y.off_auxtab = 16 * cap * threads;
+            Y.off_buf0 = (int)(((size_t)Y.off_auxtab + auxtab + 127) & ~size_t(127));
             Y.off_buf1 = nbuf == 2 ? (int)(((size_t)Y.off_buf0 + Y.buf_bytes + 127) & ~size_t(127)) : Y.off_buf0;
             Y.total = Y.off_buf1 + Y.buf_bytes;
             // ~1.5 cells per pair atom keep the cell edge at the cutoff for protein-like densities
