@@ -102,7 +102,7 @@ static int plan(chc_ctx* ctx) {
     B.off_aux = B.off_spos + 16 * T.n_pair;
     B.fixed_bytes = (int)al16((size_t)B.off_aux + 12 * (size_t)std::max(T.n_aux, 1));
     B.off_cells = B.fixed_bytes;
-    const size_t queues = al16(8 * (size_t)warps * Q1_CAP) + al16(32 * (size_t)warps * Q2_CAP);
+    const size_t queues = al16(8 * (size_t)warps * Q1_CAP) + al16(8 * (size_t)warps * QF_CAP) + al16(32 * (size_t)warps * Q2_CAP);
     const size_t tables = 2 * al16(4 * (size_t)T.K * T.K) + al16(sizeof(PairMisc));
     // ~3 cells per pair atom keeps the cells at the cutoff size for protein-like densities
     size_t want_cells = std::min<size_t>(49152, std::max<size_t>(2048, 3 * (size_t)T.n_pair));
@@ -128,6 +128,7 @@ static int plan(chc_ctx* ctx) {
         L.bits_words = (int)((ctx->n_pairs + 23) / 24);
     }
     L.off_q1 = (int)off; off += al16(8 * (size_t)warps * Q1_CAP);
+    L.off_qf = (int)off; off += al16(8 * (size_t)warps * QF_CAP);
     L.off_q2 = (int)off; off += al16(32 * (size_t)warps * Q2_CAP);
     L.off_tv = (int)off; off += al16(4 * (size_t)T.K * T.K);
     L.off_th = (int)off; off += al16(4 * (size_t)T.K * T.K);

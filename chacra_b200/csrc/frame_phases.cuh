@@ -121,6 +121,17 @@ __device__ __forceinline__ void ring_stack_task(const DevTopo& T, const DevParam
     }
 }
 
+// ---- F: can this pair get any class at all?  A cheap SUFFICIENT test for e2_classify(...) == 0 (every class below needs
+// one of the things tested here): vdW / hydrophobic / their near-cutoff reports need dl >= vdw_res_diff; a salt bridge
+// needs an anion and a cation; a hydrogen bond needs both atoms in the hydrogen-bond selection; a water edge needs
+// exactly one solvent atom.
+__device__ __forceinline__ bool e2_may_classify(const DevParams& P, const FrameCtx& F, unsigned wi, unsigned wj) {
+    const bool polar = (((wi & I_ANION) && (wj & I_CATION)) || ((wj & I_ANION) && (wi & I_CATION))) || (wi & wj & I_HBU) ||
+                       ((wi ^ wj) & I_SOLV);
+    const int dl = abs(F.lkey[wi >> I_PIDX_SHIFT] - F.lkey[wj >> I_PIDX_SHIFT]);
+    return polar || dl >= P.vdw_rd;
+}
+
 // ---- E2: exact float32 d2 and class tests for one prefilter survivor ---------------------------------------
 __device__ __forceinline__ unsigned e2_classify(const DevTopo& T, const DevParams& P, const FrameCtx& F, float4 a, float4 b,
                                                 float& d2_out) {

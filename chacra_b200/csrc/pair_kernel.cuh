@@ -18,6 +18,7 @@
 #include "water_phase.cuh"
 
 #define Q1_CAP 96           // (i, j) survivors per warp (>= 64: see the flush in E1)
+#define QF_CAP 64           // survivors that passed the cheap filter, per warp
 #define Q2_CAP 64           // classified pairs per warp and queue (plain, polar)
 
 struct PairLayout {         // shared-memory plan of the pair kernel (bytes)
@@ -25,7 +26,7 @@ struct PairLayout {         // shared-memory plan of the pair kernel (bytes)
     int off_cells;          // SMALL: cell starts
     int off_lkey;           // SMALL: locality keys by pair index
     int off_bits;           // SMALL: residue-pair bitset
-    int off_q1, off_q2, off_tv, off_th, off_misc;
+    int off_q1, off_qf, off_q2, off_tv, off_th, off_misc;
     int bits_words;         // words of the residue-pair set (plain: P/32, stamped: P/24)
     int total;
 };
@@ -48,6 +49,7 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
     float* th = reinterpret_cast<float*>(smem + L.off_th);
     PairMisc* M = reinterpret_cast<PairMisc*>(smem + L.off_misc);
     unsigned* q1 = reinterpret_cast<unsigned*>(smem + L.off_q1) + warp * (2 * Q1_CAP);       // i[Q1_CAP], j[Q1_CAP]
+    unsigned* qf = reinterpret_cast<unsigned*>(smem + L.off_qf) + warp * (2 * QF_CAP);       // filtered survivors: i, j
     unsigned* q2 = reinterpret_cast<unsigned*>(smem + L.off_q2) + warp * (8 * Q2_CAP);       // plain | polar: i, j, cls, d2
     for (int k = tid; k < T.K * T.K; k += THREADS) { tv[k] = T.tv[k]; th[k] = T.th[k]; }
     int* s_lkey = reinterpret_cast<int*>(smem + L.off_lkey);
@@ -119,7 +121,7 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
         }
         // ---- E: pair interactions ------------------------------------------------------------------------------
         const float cut2 = P.pre2;            // largest exact float32 cutoff^2 of the enabled pair types
-        int q1n = 0, q2n = 0, q3n = 0;
+        int q1n = 0, qfn = 0, q2n = 0, q3n = 0;
         // E1 state.  A tile = 32 consecutive cell-sorted atoms of grid A, one per lane (atom i).  Lane ranges:
         // 0..4 = half shell of grid A (own row from the slot after i to the end of cell x+1, then rows (y+1,z) (y-1,z+1)
         // (y,z+1) (y+1,z+1) from x-1 to x+1); 5..13 (only with unselected solvent) = the full 3x3 rows of grid B.
@@ -201,16 +203,35 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                 }
                 mask = m;
             }
-            if (q1n == 0 && q2n == 0 && q3n == 0) break;           // only reachable when exhausted
+            if (q1n == 0 && qfn == 0 && q2n == 0 && q3n == 0) break;           // only reachable when exhausted
             __syncwarp();
-            // ---- E2: up to 32 survivors; classified pairs go to the plain queue (vdW / hydrophobic only) or to the
-            //      polar queue (salt bridge, hydrogen bond, water edge), so that an E3 batch runs one kind of code ----
-            {
+            // ---- F: up to 32 survivors through the cheap sufficient test for "no class": most close pairs sit in the
+            //      same or adjacent residues and only matter when both atoms are polar ----
+            if (q1n > 0) {
                 const int nb = min(q1n, 32);
                 q1n -= nb;
-                unsigned cls = 0u; float d2 = 0.f; unsigned ei = 0u, ej = 0u;
+                bool keep = false; unsigned ei = 0u, ej = 0u;
                 if (lane < nb) {
                     ei = q1[q1n + lane]; ej = q1[Q1_CAP + q1n + lane];
+                    keep = e2_may_classify(P, F, __float_as_uint(spos[ei].w), __float_as_uint(spos[ej].w));
+                }
+                const unsigned bal = __ballot_sync(FULL, keep);
+                if (keep) {
+                    const int at = qfn + __popc(bal & ((1u << lane) - 1u));
+                    qf[at] = ei; qf[QF_CAP + at] = ej;
+                }
+                qfn += __popc(bal);
+                __syncwarp();
+            }
+            // ---- E2: 32 filtered survivors; classified pairs go to the plain queue (vdW / hydrophobic only) or to the
+            //      polar queue (salt bridge, hydrogen bond, water edge), so that an E3 batch runs one kind of code ----
+            const bool drain1 = exhausted && q1n == 0;
+            if (qfn >= 32 || (drain1 && qfn > 0)) {
+                const int nb = min(qfn, 32);
+                qfn -= nb;
+                unsigned cls = 0u; float d2 = 0.f; unsigned ei = 0u, ej = 0u;
+                if (lane < nb) {
+                    ei = qf[qfn + lane]; ej = qf[QF_CAP + qfn + lane];
                     cls = e2_classify(T, P, F, spos[ei], spos[ej], d2);
                 }
                 const bool polar = (cls & (C_SB | C_HB | C_HBW)) != 0u;
@@ -225,7 +246,7 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                 __syncwarp();
             }
             // ---- E3: 32 classified pairs of one queue (or the rest when nothing else is left) ----
-            const bool drain = exhausted && q1n == 0;
+            const bool drain = drain1 && qfn == 0;
             while (q2n >= 32 || q3n >= 32 || (drain && (q2n | q3n) != 0)) {
                 const bool plain = q2n >= 32 || (q3n < 32 && q2n > 0);
                 int& qn = plain ? q2n : q3n;
