@@ -125,7 +125,7 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
         // E1 state.  A tile = 32 consecutive cell-sorted atoms of grid A, one per lane (atom i).  Lane ranges:
         // 0..4 = half shell of grid A (own row from the slot after i to the end of cell x+1, then rows (y+1,z) (y-1,z+1)
         // (y,z+1) (y+1,z+1) from x-1 to x+1); 5..13 (only with unselected solvent) = the full 3x3 rows of grid B.
-        const int nA = T.n_pair_a, last = T.n_pair - 1;
+        const int nA = T.n_pair_a;
         const int nr = T.n_pair_a < T.n_pair ? 14 : 5;
         const int ntiles = (nA + 31) >> 5;
         int r = nr, k0 = 0, maxlen = 0;                // warp-uniform: current range, chunk offset, longest lane range
@@ -190,17 +190,24 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                     k0 = 0;
                     if (maxlen == 0) continue;
                 }
-                // 32 candidate slots of every lane's range: exact float32 d2 against the largest cutoff
+                // 32 candidate slots of every lane's range, four at a time: exact float32 d2 against the largest cutoff.
+                // Slots past the lane's own range are computed too (they lie inside the record: at most 35 slots after
+                // the sorted atoms, where the aux atoms and the cell starts follow) and masked off afterwards.
                 const int n = min(32, maxlen - k0);
                 const int lim = len - k0;
                 mbase = beg + k0;
+                const float4* pj = spos + mbase;
                 unsigned m = 0u;
-#pragma unroll 4
-                for (int k = 0; k < n; ++k) {
-                    const float4 pj = spos[min(mbase + k, last)];
-                    const float d2 = dist2_exact(ix, iy, iz, pj.x, pj.y, pj.z);
-                    if (k < lim && d2 <= cut2) m |= 1u << k;
+#pragma unroll 2
+                for (int k4 = 0; k4 < n; k4 += 4) {
+                    const float4 a = pj[k4], b = pj[k4 + 1], c = pj[k4 + 2], d = pj[k4 + 3];
+                    const unsigned nib = (dist2_exact(ix, iy, iz, a.x, a.y, a.z) <= cut2 ? 1u : 0u) |
+                                         (dist2_exact(ix, iy, iz, b.x, b.y, b.z) <= cut2 ? 2u : 0u) |
+                                         (dist2_exact(ix, iy, iz, c.x, c.y, c.z) <= cut2 ? 4u : 0u) |
+                                         (dist2_exact(ix, iy, iz, d.x, d.y, d.z) <= cut2 ? 8u : 0u);
+                    m |= nib << k4;
                 }
+                m = lim >= 32 ? m : (lim > 0 ? m & ((1u << lim) - 1u) : 0u);
                 mask = m;
             }
             if (q1n == 0 && qfn == 0 && q2n == 0 && q3n == 0) break;           // only reachable when exhausted
