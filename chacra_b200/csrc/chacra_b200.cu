@@ -467,8 +467,9 @@ extern "C" int chc_submit_frames_host(chc_ctx* ctx, int state, const float* h_xy
     CK(cudaSetDevice(ctx->device));
     const int F = ctx->prm.fragment_frames;
     const size_t fbytes = 12 * (size_t)ctx->T.n_atoms;
-    // chunk = whole fragments, about 256 MiB
-    int64_t chunk = std::max<int64_t>(1, (int64_t)((256u << 20) / fbytes) / F) * F;
+    // chunk = whole fragments, about 64 MiB: small enough that the copy of chunk k+1 hides behind the kernels of chunk k
+    // from the first chunk on (the host path is PCIe bound, not kernel bound)
+    int64_t chunk = std::max<int64_t>(1, (int64_t)((64u << 20) / fbytes) / F) * F;
     if (ctx->stage_frames < chunk) {
         CK(cudaDeviceSynchronize());
         for (int k = 0; k < 2; ++k) {
