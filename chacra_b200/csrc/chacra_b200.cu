@@ -10,7 +10,7 @@
 #include "bin_tma_kernel.cuh"
 #include "pair_kernel.cuh"
 
-#define PAIR_THREADS 768
+#define PAIR_THREADS 1024
 #define SMEM_LIMIT (227 * 1024)
 
 struct chc_ctx {
@@ -102,7 +102,14 @@ static int plan(chc_ctx* ctx) {
     B.off_aux = B.off_spos + 16 * T.n_pair;
     B.fixed_bytes = (int)al16((size_t)B.off_aux + 12 * (size_t)std::max(T.n_aux, 1));
     B.off_cells = B.fixed_bytes;
-    const size_t queues = al16(8 * (size_t)warps * Q1_CAP) + al16(8 * (size_t)warps * QF_CAP) + al16(32 * (size_t)warps * Q2_CAP);
+    auto queue_bytes = [&](bool small, size_t* q1, size_t* qf, size_t* q2) {
+        const size_t qw = small ? 1 : 2;
+        *q1 = al16(4 * qw * (size_t)warps * Q1_CAP); *qf = al16(4 * qw * (size_t)warps * QF_CAP);
+        *q2 = al16(8 * (qw + 1) * (size_t)warps * Q2_CAP);
+        return *q1 + *qf + *q2;
+    };
+    size_t q1b, qfb, q2b;
+    const size_t queues = queue_bytes(true, &q1b, &qfb, &q2b);
     const size_t tables = 2 * al16(4 * (size_t)T.K * T.K) + al16(sizeof(PairMisc));
     // ~3 cells per pair atom keeps the cells at the cutoff size for protein-like densities
     size_t want_cells = std::min<size_t>(49152, std::max<size_t>(2048, 3 * (size_t)T.n_pair));
@@ -127,9 +134,10 @@ static int plan(chc_ctx* ctx) {
         if ((ctx->n_pairs + 23) / 24 > 0x7fffffff) return CHC_E_TOO_LARGE;
         L.bits_words = (int)((ctx->n_pairs + 23) / 24);
     }
-    L.off_q1 = (int)off; off += al16(8 * (size_t)warps * Q1_CAP);
-    L.off_qf = (int)off; off += al16(8 * (size_t)warps * QF_CAP);
-    L.off_q2 = (int)off; off += al16(32 * (size_t)warps * Q2_CAP);
+    queue_bytes(ctx->small_path, &q1b, &qfb, &q2b);
+    L.off_q1 = (int)off; off += q1b;
+    L.off_qf = (int)off; off += qfb;
+    L.off_q2 = (int)off; off += q2b;
     L.off_tv = (int)off; off += al16(4 * (size_t)T.K * T.K);
     L.off_th = (int)off; off += al16(4 * (size_t)T.K * T.K);
     L.off_misc = (int)off; off += al16(sizeof(PairMisc));

@@ -207,8 +207,9 @@ __device__ __forceinline__ bool hb_direction(const DevTopo& T, const DevParams& 
 
 // ---- E3: everything that needs the global tables, for one classified pair ---------------------------------------
 __device__ __forceinline__ void e3_finish(const DevTopo& T, const DevParams& P, const DevOut& O, const FrameCtx& F,
-                                          int i, int j, unsigned cls, float d2) {
+                                          int i, int j, unsigned cls) {
     float4 a = F.spos[i], b = F.spos[j];
+    const float d2 = dist2_exact(a.x, a.y, a.z, b.x, b.y, b.z);      // as in e2_classify (same operands, same order)
     unsigned wi = __float_as_uint(a.w), wj = __float_as_uint(b.w);
     int pi = wi >> I_PIDX_SHIFT, pj = wj >> I_PIDX_SHIFT;
     int ai = T.pair_atom[pi], aj = T.pair_atom[pj];

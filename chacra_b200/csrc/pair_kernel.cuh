@@ -48,9 +48,17 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
     float* tv = reinterpret_cast<float*>(smem + L.off_tv);
     float* th = reinterpret_cast<float*>(smem + L.off_th);
     PairMisc* M = reinterpret_cast<PairMisc*>(smem + L.off_misc);
-    unsigned* q1 = reinterpret_cast<unsigned*>(smem + L.off_q1) + warp * (2 * Q1_CAP);       // i[Q1_CAP], j[Q1_CAP]
-    unsigned* qf = reinterpret_cast<unsigned*>(smem + L.off_qf) + warp * (2 * QF_CAP);       // filtered survivors: i, j
-    unsigned* q2 = reinterpret_cast<unsigned*>(smem + L.off_q2) + warp * (8 * Q2_CAP);       // plain | polar: i, j, cls, d2
+    // queue entries: the pair (i, j) of sorted slots is one word on the shared-memory path (slots < 65 536), two otherwise
+    constexpr int QW = SMALL ? 1 : 2;
+    unsigned* q1 = reinterpret_cast<unsigned*>(smem + L.off_q1) + warp * (QW * Q1_CAP);            // survivors
+    unsigned* qf = reinterpret_cast<unsigned*>(smem + L.off_qf) + warp * (QW * QF_CAP);            // filtered survivors
+    unsigned* q2 = reinterpret_cast<unsigned*>(smem + L.off_q2) + warp * (2 * (QW + 1) * Q2_CAP);  // plain | polar: pair, class
+    auto qput = [](unsigned* q, int cap, int at, unsigned i, unsigned j) {
+        if (SMALL) q[at] = i | (j << 16); else { q[at] = i; q[cap + at] = j; }
+    };
+    auto qget = [](const unsigned* q, int cap, int at, unsigned& i, unsigned& j) {
+        if (SMALL) { const unsigned w = q[at]; i = w & 0xffffu; j = w >> 16; } else { i = q[at]; j = q[cap + at]; }
+    };
     for (int k = tid; k < T.K * T.K; k += THREADS) { tv[k] = T.tv[k]; th[k] = T.th[k]; }
     int* s_lkey = reinterpret_cast<int*>(smem + L.off_lkey);
     unsigned* bits;
@@ -150,7 +158,7 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                         while (m) {
                             const int k = __ffs(m) - 1;
                             m &= m - 1u;
-                            q1[at] = (unsigned)my_i; q1[Q1_CAP + at] = (unsigned)(mbase + k);
+                            qput(q1, Q1_CAP, at, (unsigned)my_i, (unsigned)(mbase + k));
                             ++at;
                         }
                         mask = 0u;
@@ -219,13 +227,13 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                 q1n -= nb;
                 bool keep = false; unsigned ei = 0u, ej = 0u;
                 if (lane < nb) {
-                    ei = q1[q1n + lane]; ej = q1[Q1_CAP + q1n + lane];
+                    qget(q1, Q1_CAP, q1n + lane, ei, ej);
                     keep = e2_may_classify(P, F, __float_as_uint(spos[ei].w), __float_as_uint(spos[ej].w));
                 }
                 const unsigned bal = __ballot_sync(FULL, keep);
                 if (keep) {
                     const int at = qfn + __popc(bal & ((1u << lane) - 1u));
-                    qf[at] = ei; qf[QF_CAP + at] = ej;
+                    qput(qf, QF_CAP, at, ei, ej);
                 }
                 qfn += __popc(bal);
                 __syncwarp();
@@ -238,16 +246,16 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                 qfn -= nb;
                 unsigned cls = 0u; float d2 = 0.f; unsigned ei = 0u, ej = 0u;
                 if (lane < nb) {
-                    ei = qf[qfn + lane]; ej = qf[QF_CAP + qfn + lane];
+                    qget(qf, QF_CAP, qfn + lane, ei, ej);
                     cls = e2_classify(T, P, F, spos[ei], spos[ej], d2);
                 }
                 const bool polar = (cls & (C_SB | C_HB | C_HBW)) != 0u;
                 const unsigned balp = __ballot_sync(FULL, polar), balv = __ballot_sync(FULL, cls != 0u && !polar);
                 if (cls) {
                     const unsigned below = (1u << lane) - 1u;
-                    unsigned* q = polar ? q2 + 4 * Q2_CAP : q2;
+                    unsigned* q = polar ? q2 + (QW + 1) * Q2_CAP : q2;
                     const int at = polar ? q3n + __popc(balp & below) : q2n + __popc(balv & below);
-                    q[at] = ei; q[Q2_CAP + at] = ej; q[2 * Q2_CAP + at] = cls; q[3 * Q2_CAP + at] = __float_as_uint(d2);
+                    qput(q, Q2_CAP, at, ei, ej); q[QW * Q2_CAP + at] = cls;
                 }
                 q2n += __popc(balv); q3n += __popc(balp);
                 __syncwarp();
@@ -257,12 +265,14 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
             while (q2n >= 32 || q3n >= 32 || (drain && (q2n | q3n) != 0)) {
                 const bool plain = q2n >= 32 || (q3n < 32 && q2n > 0);
                 int& qn = plain ? q2n : q3n;
-                const unsigned* q = plain ? q2 : q2 + 4 * Q2_CAP;
+                const unsigned* q = plain ? q2 : q2 + (QW + 1) * Q2_CAP;
                 const int nb = min(qn, 32);
                 qn -= nb;
-                if (lane < nb)
-                    e3_finish(T, P, O, F, (int)q[qn + lane], (int)q[Q2_CAP + qn + lane], q[2 * Q2_CAP + qn + lane],
-                              __uint_as_float(q[3 * Q2_CAP + qn + lane]));
+                if (lane < nb) {
+                    unsigned ei, ej;
+                    qget(q, Q2_CAP, qn + lane, ei, ej);
+                    e3_finish(T, P, O, F, (int)ei, (int)ej, q[QW * Q2_CAP + qn + lane]);
+                }
                 __syncwarp();
             }
         }
