@@ -87,6 +87,12 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                 mbar_expect_tx(&M->bar, (unsigned)B.fixed_bytes + cbytes);
                 bulk_g2s(smem + L.off_rec, rec, (unsigned)B.fixed_bytes, &M->bar);
                 bulk_g2s(smem + L.off_cells, rec + B.off_cells, cbytes, &M->bar);
+                // the record this CTA needs next: on its way to L2 while this frame is enumerated (large chunks spill to HBM)
+                if (f + (int)gridDim.x < n_frames) {
+                    const unsigned char* nxt = rec + (size_t)gridDim.x * B.stride;
+                    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(nxt), "r"((unsigned)B.fixed_bytes) : "memory");
+                    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(nxt + B.off_cells), "r"(cbytes) : "memory");
+                }
                 M->cursor = 0; M->nmark = 0;
             }
             for (int w = tid; w < L.bits_words; w += THREADS) bits[w] = 0u;

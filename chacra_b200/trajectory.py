@@ -104,6 +104,6 @@ def open_trajectory(path: str):
     if low.endswith(".pdb") or low.endswith(".ent"):
         return PDBFrames(path)
     if low.endswith(".xtc"):
-        from .xtc import XTCFile
-        return XTCFile(path)
-    raise ValueError("unsupported trajectory format: %s (dcd, xtc and pdb are read)" % path)
+        raise ValueError("%s: XTC input is not decoded yet (SURVEY 8(f) row X1); write the state trajectory as DCD "
+                         "(MDAnalysis: Writer('state_0.dcd')) and pass that" % path)
+    raise ValueError("unsupported trajectory format: %s (dcd and pdb are read)" % path)
