@@ -34,6 +34,7 @@ struct PairLayout {         // shared-memory plan of the pair kernel (bytes)
 struct PairMisc {
     unsigned long long bar;     // mbarrier of the bulk copies
     int cursor;                 // next tile of 32 sorted atoms
+    int ring_cursor;            // next unit of 32 ring tasks
     int nmark;                  // waters with at least one hydrogen bond to a non-solvent atom (this frame)
 };
 
@@ -93,7 +94,7 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(nxt), "r"((unsigned)B.fixed_bytes) : "memory");
                     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(nxt + B.off_cells), "r"(cbytes) : "memory");
                 }
-                M->cursor = 0; M->nmark = 0;
+                M->cursor = 0; M->ring_cursor = 0; M->nmark = 0;
             }
             for (int w = tid; w < L.bits_words; w += THREADS) bits[w] = 0u;
             mbar_wait(&M->bar, phase);
@@ -103,7 +104,7 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
             aux = reinterpret_cast<const float*>(smem + L.off_rec + B.off_aux);
             cells = reinterpret_cast<const int*>(smem + L.off_cells);
         } else {
-            if (tid == 0) { M->cursor = 0; M->nmark = 0; }
+            if (tid == 0) { M->cursor = 0; M->ring_cursor = 0; M->nmark = 0; }
             gen = gen + 1u;
             if (gen > 255u) {               // generations wrapped: wipe the table once per 255 frames
                 for (int w = tid; w < L.bits_words; w += THREADS) bits[w] = 0u;
@@ -119,20 +120,6 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
         FrameCtx F{spos, SMALL ? s_lkey : T.pair_lkey, aux, bits, gen, tv, th,
                    hpmask + (size_t)(gidx / frag_frames - frag0) * T.n_pair, (int)gidx,
                    water_scratch(wscratch, blockIdx.x, T.n_solv), &M->nmark};
-        // ---- R: ring interactions (small lists; float prefilter, float64 geometry) ------------------------------
-        if (P.itypes & CHC_IT_PC) {
-            const int n = T.n_cat * T.n_rings;
-            for (int t = tid; t < n; t += THREADS) ring_pc_task(T, P, O, F, t / T.n_rings, t % T.n_rings);
-        }
-        if (P.itypes & (CHC_IT_PS | CHC_IT_TS)) {
-            const int n = T.n_rings * (T.n_rings - 1) / 2;
-            for (int t = tid; t < n; t += THREADS) {
-                int r2 = (int)((1.0f + sqrtf(1.0f + 8.0f * (float)t)) * 0.5f);
-                while (r2 * (r2 - 1) / 2 > t) --r2;
-                while ((r2 + 1) * r2 / 2 <= t) ++r2;
-                ring_stack_task(T, P, O, F, t - r2 * (r2 - 1) / 2, r2);
-            }
-        }
         // ---- E: pair interactions ------------------------------------------------------------------------------
         const float cut2 = P.pre2;            // largest exact float32 cutoff^2 of the enabled pair types
         int q1n = 0, qfn = 0, q2n = 0, q3n = 0;
@@ -278,6 +265,32 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                     unsigned ei, ej;
                     qget(q, Q2_CAP, qn + lane, ei, ej);
                     e3_finish(T, P, O, F, (int)ei, (int)ej, q[QW * Q2_CAP + qn + lane]);
+                }
+                __syncwarp();
+            }
+        }
+        // ---- R: ring interactions (small lists; float prefilter, float64 geometry), in units of 32 tasks handed out through a
+        //      shared counter AFTER the pair phase: warps that run out of atom tiles early fill the end-of-frame tail ----
+        {
+            const int n_pc = (P.itypes & CHC_IT_PC) ? T.n_cat * T.n_rings : 0;
+            const int n_st = (P.itypes & (CHC_IT_PS | CHC_IT_TS)) ? T.n_rings * (T.n_rings - 1) / 2 : 0;
+            const int u_pc = (n_pc + 31) >> 5, u_all = u_pc + ((n_st + 31) >> 5);
+            for (;;) {
+                int u = 0;
+                if (lane == 0) u = atomicAdd(&M->ring_cursor, 1);
+                u = __shfl_sync(FULL, u, 0);
+                if (u >= u_all) break;
+                if (u < u_pc) {
+                    const int t = u * 32 + lane;
+                    if (t < n_pc) ring_pc_task(T, P, O, F, t / T.n_rings, t % T.n_rings);
+                } else {
+                    const int t = (u - u_pc) * 32 + lane;
+                    if (t < n_st) {
+                        int r2 = (int)((1.0f + sqrtf(1.0f + 8.0f * (float)t)) * 0.5f);
+                        while (r2 * (r2 - 1) / 2 > t) --r2;
+                        while ((r2 + 1) * r2 / 2 <= t) ++r2;
+                        ring_stack_task(T, P, O, F, t - r2 * (r2 - 1) / 2, r2);
+                    }
                 }
                 __syncwarp();
             }
