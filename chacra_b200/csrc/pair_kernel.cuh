@@ -129,7 +129,8 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
         const int nA = T.n_pair_a;
         const int nr = T.n_pair_a < T.n_pair ? 14 : 5;
         const int ntiles = (nA + 31) >> 5;
-        int r = nr, k0 = 0, maxlen = 0;                // warp-uniform: current range, chunk offset, longest lane range
+        const int nunits = ntiles * nr;
+        int r = 0, tile = -1, k0 = 0, maxlen = 0;      // warp-uniform: current range and tile, chunk offset, longest lane range
         int my_i = -1, my_c = 0, beg = 0, len = 0;     // this lane's atom, its cell, its current range
         float ix = 0.f, iy = 0.f, iz = 0.f;
         unsigned mask = 0u; int mbase = 0;             // this lane's hits of the last chunk not yet queued: j = mbase + bit
@@ -160,12 +161,15 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                     continue;
                 }
                 k0 += 32;
-                if (k0 >= maxlen) {                    // next range, or next tile
-                    if (++r >= nr) {
-                        int t = 0;
-                        if (lane == 0) t = atomicAdd(&M->cursor, 1);
-                        t = __shfl_sync(FULL, t, 0);
-                        if (t >= ntiles) { exhausted = true; break; }
+                if (k0 >= maxlen) {                    // next unit of work = (tile, range); fine grain keeps the frame's tail short
+                    int u = 0;
+                    if (lane == 0) u = atomicAdd(&M->cursor, 1);
+                    u = __shfl_sync(FULL, u, 0);
+                    if (u >= nunits) { exhausted = true; break; }
+                    const int t = u / nr;
+                    r = u - t * nr;
+                    if (t != tile) {
+                        tile = t;
                         my_i = t * 32 + lane;
                         if (my_i < nA) {
                             const float4 p = spos[my_i];
@@ -174,7 +178,6 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                                    (cell_of(iy, hdr->org[1], hdr->inv, hdr->nc[1]) + 1) * px +
                                    cell_of(ix, hdr->org[0], hdr->inv, hdr->nc[0]) + 1;
                         } else my_i = -1;
-                        r = 0;
                     }
                     len = 0;
                     if (my_i >= 0) {
