@@ -34,6 +34,8 @@ def compute_contacts(top, traj, output, itypes, geom_criterion_values, cores, be
     sele2 = sele1 if sele2 is None else sele2
     atoms = read_pdb(top)
     trj = open_trajectory(traj)
+    if hasattr(trj, "device"):
+        trj.device = int(device)                          # readers that decode on the GPU (XTC)
     if trj.n_atoms != atoms.n:
         raise ChacraError("topology has %d atoms but the trajectory has %d" % (atoms.n, trj.n_atoms))
     sim_length = trj.n_frames
@@ -70,7 +72,9 @@ def compute_contacts(top, traj, output, itypes, geom_criterion_values, cores, be
                 room = int(0.5 * _RECORD_CAPACITY / max(per_frame, 1.0))
                 n = min(max(TRAJ_FRAG_SIZE, room // TRAJ_FRAG_SIZE * TRAJ_FRAG_SIZE), total_frames - done)
             first = beg + done * stride
-            frames = trj.read(first, min(first + (n - 1) * stride, end), stride)
+            # XTC frames are decoded on the device and stay there; the other readers hand host arrays to the staging path
+            reader = getattr(trj, "read_device", trj.read)
+            frames = reader(first, min(first + (n - 1) * stride, end), stride)
             eng.submit(frames, 0, done)
             eng.synchronize()
             rec = eng.drain_contacts()

@@ -9,6 +9,7 @@
 #include "bin_kernel.cuh"
 #include "bin_tma_kernel.cuh"
 #include "pair_kernel.cuh"
+#include "xtc_decode.cuh"
 
 #define PAIR_THREADS 1024
 #define SMEM_LIMIT (227 * 1024)
@@ -592,4 +593,31 @@ extern "C" int chc_get_stats(chc_ctx* ctx, chc_stats* out) {
     }
     *out = ctx->st;
     return CHC_OK;
+}
+
+// ---- XTC decode ---------------------------------------------------------------------------------------
+static_assert(sizeof(XtcFrameMeta) == sizeof(chc_xtc_frame) && sizeof(chc_xtc_frame) == 64, "chc_xtc_frame layout");
+
+extern "C" int chc_xtc_decode(const void* d_blob, const chc_xtc_frame* d_meta, int64_t n_frames, int32_t n_atoms, float* d_xyz,
+                              int64_t frame_stride, int device, void* stream_) {
+    if (n_frames == 0) return CHC_OK;
+    if (!d_blob || !d_meta || !d_xyz || n_frames < 0 || n_frames > 0x7fffffff || n_atoms < 1) return CHC_E_INVALID;
+    if (((uintptr_t)d_blob & 3) != 0) return CHC_E_INVALID;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (cudaSetDevice(device) != cudaSuccess) return CHC_E_CUDA;
+    if (frame_stride == 0) frame_stride = 3 * (int64_t)n_atoms;
+    unsigned* status = nullptr;
+    if (cudaMalloc(&status, 4) != cudaSuccess) return CHC_E_CUDA;
+    cudaMemsetAsync(status, 0, 4, stream);
+    const int threads = 128;
+    const int blocks = (int)std::min<int64_t>((n_frames + threads - 1) / threads, 148 * 16);
+    xtc_decode_kernel<<<blocks, threads, 0, stream>>>(static_cast<const unsigned*>(d_blob), reinterpret_cast<const XtcFrameMeta*>(d_meta),
+                                                    (int)n_frames, n_atoms, d_xyz, frame_stride, status);
+    unsigned st = 0;
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&st, status, 4, cudaMemcpyDeviceToHost, stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+    cudaFree(status);
+    if (e != cudaSuccess) return CHC_E_CUDA;
+    return st ? CHC_E_INVALID : CHC_OK;
 }

@@ -1,0 +1,166 @@
+// xtc_decode.cuh -- GROMACS XTC frames -> float32 [F][N][3] Angstrom on the device.
+//
+// Replaces, for `state_{i}.xtc` (chacra/scripts/process_hremd_output.py:147), VMD's gromacs molfile plugin that the
+// reference reaches through contact_utils.py:89-116.  The host only walks the frame headers (chacra_b200/xtc.py) and
+// ships the COMPRESSED bit streams (about a third of the float32 bytes) over PCIe; this kernel undoes xdrfile's
+// xdr3dfcoord coding: per atom three "large" integers (mixed radix, offset by minint) or small differences to the
+// previous atom in runs (flag bit + 5 bits; the first two atoms of a run swapped), the small radix index stepping
+// through `magicints`.  The bit stream of a frame is inherently sequential, frames are independent: one thread per
+// frame.  Parity: unpinned against real files (oracle/xtc_oracle.py header); bit-exact against the oracle codec.
+#pragma once
+#include "device_types.cuh"
+
+struct XtcFrameMeta {           // mirror of chc_xtc_frame (include/chacra_b200.h)
+    long long offset;           // bytes from the start of the blob, multiple of 4
+    int nbytes;                 // compressed bytes (raw frames: 12 n_atoms)
+    float precision;
+    int minint[3], maxint[3];
+    int smallidx;
+    int raw;                    // 1: n_atoms <= 9, big-endian float32 nm instead of a bit stream
+    int bitsize;                // bits of one packed large triple (0: three separate fields of bitsizeint bits), host-computed
+    int bitsizeint[3];
+};
+
+__device__ const int xtc_magicints[73] = {
+    0, 0, 0, 0, 0, 0, 0, 0, 0, 8, 10, 12, 16, 20, 25, 32, 40, 50, 64, 80, 101, 128, 161, 203, 256, 322, 406, 512, 645, 812, 1024, 1290,
+    1625, 2048, 2580, 3250, 4096, 5060, 6501, 8192, 10321, 13003, 16384, 20642, 26007, 32768, 41285, 52015, 65536, 82570, 104031,
+    131072, 165140, 208063, 262144, 330280, 416127, 524287, 660561, 832255, 1048576, 1321122, 1664510, 2097152, 2642245, 3329021,
+    4194304, 5284491, 6658042, 8388607, 10568983, 13316085, 16777216};
+#define XTC_FIRSTIDX 9
+#define XTC_LASTIDX 72
+
+struct XtcBits {                // MSB-first bit stream over big-endian 32-bit words
+    const unsigned* w; unsigned long long acc; int avail;
+    __device__ __forceinline__ unsigned get(int k) {           // 0 <= k <= 32
+        if (k == 0) return 0u;
+        if (avail < k) { acc = (acc << 32) | __byte_perm(*w++, 0u, 0x0123); avail += 32; }
+        avail -= k;
+        return (unsigned)(acc >> avail) & (k == 32 ? 0xffffffffu : ((1u << k) - 1u));
+    }
+};
+
+// three mixed-radix digits (radices sz[1], sz[2] < 2^24 matter) from `nbits` bits: whole bytes least significant first,
+// the remaining bits on top (xdrfile receiveints)
+__device__ __forceinline__ void xtc_ints(XtcBits& B, int nbits, const unsigned sz[3], int out[3]) {
+    if (nbits <= 32) {
+        unsigned v = 0u; int sh = 0, n = nbits;
+        while (n >= 8) { v |= B.get(8) << sh; sh += 8; n -= 8; }
+        if (n) v |= B.get(n) << sh;
+        const unsigned q = v / sz[2];
+        out[2] = (int)(v - q * sz[2]);
+        const unsigned q1 = q / sz[1];
+        out[1] = (int)(q - q1 * sz[1]);
+        out[0] = (int)q1;
+    } else if (nbits <= 64) {
+        unsigned long long v = 0ull; int sh = 0, n = nbits;
+        while (n >= 8) { v |= (unsigned long long)B.get(8) << sh; sh += 8; n -= 8; }
+        if (n) v |= (unsigned long long)B.get(n) << sh;
+        const unsigned long long q = v / sz[2];
+        out[2] = (int)(v - q * sz[2]);
+        const unsigned long long q1 = q / sz[1];
+        out[1] = (int)(q - q1 * sz[1]);
+        out[0] = (int)q1;
+    } else {                    // up to 72 bits: three 32-bit limbs, schoolbook division by a radix < 2^24
+        unsigned limb[3] = {0u, 0u, 0u};
+        int sh = 0, n = nbits;
+        while (n >= 8) { limb[sh >> 5] |= B.get(8) << (sh & 31); sh += 8; n -= 8; }
+        if (n) limb[sh >> 5] |= B.get(n) << (sh & 31);
+#pragma unroll
+        for (int d = 2; d >= 1; --d) {
+            unsigned long long r = 0ull;
+#pragma unroll
+            for (int k = 2; k >= 0; --k) {
+                const unsigned long long cur = (r << 32) | limb[k];
+                const unsigned long long q = cur / sz[d];
+                limb[k] = (unsigned)q;
+                r = cur - q * sz[d];
+            }
+            out[d] = (int)r;
+        }
+        out[0] = (int)limb[0];
+    }
+}
+
+__global__ void __launch_bounds__(128)
+xtc_decode_kernel(const unsigned* __restrict__ blob, const XtcFrameMeta* __restrict__ meta, int n_frames, int n_atoms,
+                  float* __restrict__ xyz, long long frame_stride, unsigned* __restrict__ status) {
+    for (int f = blockIdx.x * blockDim.x + threadIdx.x; f < n_frames; f += gridDim.x * blockDim.x) {
+        const XtcFrameMeta m = meta[f];
+        float* out = xyz + (size_t)f * frame_stride;
+        const unsigned* src = blob + (m.offset >> 2);
+        if (m.raw) {
+            for (int k = 0; k < 3 * n_atoms; ++k) out[k] = __uint_as_float(__byte_perm(src[k], 0u, 0x0123)) * 10.0f;
+            continue;
+        }
+        const float inv = 1.0f / m.precision;
+        unsigned sizeint[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) sizeint[k] = (unsigned)(m.maxint[k] - m.minint[k] + 1);
+        int smallidx = m.smallidx;
+        if (smallidx < XTC_FIRSTIDX || smallidx > XTC_LASTIDX) { atomicOr(status, 1u); continue; }
+        int smaller = xtc_magicints[max(XTC_FIRSTIDX, smallidx - 1)] / 2;
+        int smallnum = xtc_magicints[smallidx] / 2;
+        unsigned sizesmall[3];
+        sizesmall[0] = sizesmall[1] = sizesmall[2] = (unsigned)xtc_magicints[smallidx];
+        XtcBits B{src, 0ull, 0};
+        const unsigned* end = src + ((m.nbytes + 3) >> 2) + 2;
+        int i = 0, run = 0;
+        bool bad = false;
+        while (i < n_atoms) {
+            int cur[3];
+            if (m.bitsize == 0) {
+#pragma unroll
+                for (int k = 0; k < 3; ++k) cur[k] = (int)B.get(m.bitsizeint[k]);
+            } else {
+                xtc_ints(B, m.bitsize, sizeint, cur);
+            }
+#pragma unroll
+            for (int k = 0; k < 3; ++k) cur[k] += m.minint[k];
+            ++i;
+            int is_smaller = 0;
+            if (B.get(1)) {
+                run = (int)B.get(5);
+                is_smaller = run % 3;
+                run -= is_smaller;
+                --is_smaller;
+            }
+            if (i + run / 3 > n_atoms || B.w > end) { bad = true; break; }
+            if (run > 0) {
+                int prev[3] = {cur[0], cur[1], cur[2]};
+                for (int k = 0; k < run; k += 3) {
+                    int d[3];
+                    xtc_ints(B, smallidx, sizesmall, d);
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) d[c] += prev[c] - smallnum;
+                    ++i;
+                    if (k == 0) {       // the first two atoms of a run are stored in swapped order (water: H O H)
+#pragma unroll
+                        for (int c = 0; c < 3; ++c) {
+                            out[3 * (i - 2) + c] = ((float)d[c] * inv) * 10.0f;
+                            out[3 * (i - 1) + c] = ((float)prev[c] * inv) * 10.0f;
+                        }
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < 3; ++c) out[3 * (i - 1) + c] = ((float)d[c] * inv) * 10.0f;
+                    }
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) prev[c] = d[c];
+                }
+            } else {
+#pragma unroll
+                for (int c = 0; c < 3; ++c) out[3 * (i - 1) + c] = ((float)cur[c] * inv) * 10.0f;
+            }
+            smallidx += is_smaller;
+            if (smallidx < XTC_FIRSTIDX || smallidx > XTC_LASTIDX) { bad = true; break; }
+            if (is_smaller < 0) {
+                smallnum = smaller;
+                smaller = smallidx > XTC_FIRSTIDX ? xtc_magicints[smallidx - 1] / 2 : 0;
+            } else if (is_smaller > 0) {
+                smaller = smallnum;
+                smallnum = xtc_magicints[smallidx] / 2;
+            }
+            sizesmall[0] = sizesmall[1] = sizesmall[2] = (unsigned)xtc_magicints[smallidx];
+        }
+        if (bad) atomicOr(status, 1u);
+    }
+}

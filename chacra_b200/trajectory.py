@@ -1,7 +1,7 @@
 """Trajectory input: CHARMM/NAMD DCD -> float32 [F][N][3] Angstrom.
 
 Replaces VMD's molfile plugins on the path (``contact_utils.py:89-116`` ``load_traj``,
-``:119-131`` ``simulation_length``).  XTC decode is the next row.
+``:119-131`` ``simulation_length``).  XTC is decoded on the GPU (``xtc.py``).
 """
 from __future__ import annotations
 
@@ -104,6 +104,6 @@ def open_trajectory(path: str):
     if low.endswith(".pdb") or low.endswith(".ent"):
         return PDBFrames(path)
     if low.endswith(".xtc"):
-        raise ValueError("%s: XTC input is not decoded yet (SURVEY 8(f) row X1); write the state trajectory as DCD "
-                         "(MDAnalysis: Writer('state_0.dcd')) and pass that" % path)
-    raise ValueError("unsupported trajectory format: %s (dcd and pdb are read)" % path)
+        from .xtc import XTCFile
+        return XTCFile(path)
+    raise ValueError("unsupported trajectory format: %s (dcd, xtc and pdb are read)" % path)

@@ -203,6 +203,27 @@ int chc_synchronize(chc_ctx* ctx, void* stream);
 /* Copy out (and clear) the records accumulated so far.  *n = records copied. */
 int chc_drain_contacts(chc_ctx* ctx, chc_contact* host_buf, int64_t cap, int64_t* n, void* stream);
 int chc_drain_near_cutoff(chc_ctx* ctx, chc_near* host_buf, int64_t cap, int64_t* n, int64_t* n_total, void* stream);
+/* ---- trajectory input: XTC frames decoded on the device -----------------------------------
+ * Replaces VMD's gromacs molfile plugin on the path (contact_utils.py:89-116 load_traj -> molecule.read(.., 'xtc', ..))
+ * for the files chacra/scripts/process_hremd_output.py:147 passes (state_{i}.xtc).  The host walks the frame headers
+ * and fills one chc_xtc_frame per frame; the compressed bit streams travel to the device as they are in the file. */
+typedef struct chc_xtc_frame {
+    int64_t offset;          /* of the frame's bit stream in the blob, bytes, multiple of 4 */
+    int32_t nbytes;          /* bytes of the bit stream (raw frames: 12 * n_atoms) */
+    float   precision;       /* as stored (usually 1000: 0.001 nm grid) */
+    int32_t minint[3], maxint[3];
+    int32_t smallidx;
+    int32_t raw;             /* 1: n_atoms <= 9, the frame holds big-endian float32 nm */
+    int32_t bitsize;         /* bits of one packed "large" triple, 0 = three fields of bitsizeint bits (xdrfile sizeofints) */
+    int32_t bitsizeint[3];
+} chc_xtc_frame;
+
+/* d_blob: DEVICE bytes (4-byte aligned, 8 bytes of slack after the last stream); d_meta: DEVICE array of n_frames
+ * entries; d_xyz: DEVICE float32 [n_frames][frame_stride] (frame_stride 0 = 3*n_atoms), Angstrom.  Synchronises the
+ * stream; CHC_E_INVALID when a bit stream is inconsistent with n_atoms. */
+int chc_xtc_decode(const void* d_blob, const chc_xtc_frame* d_meta, int64_t n_frames, int32_t n_atoms, float* d_xyz,
+                   int64_t frame_stride, int device, void* stream);
+
 int chc_get_stats(chc_ctx* ctx, chc_stats* out);
 int chc_set_timing(chc_ctx* ctx, int on);
 

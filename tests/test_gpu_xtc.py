@@ -1,0 +1,99 @@
+"""XTC frames decoded by the CUDA kernel behind chc_xtc_decode vs the CPU codec restatement (oracle/xtc_oracle.py), and
+the drop-in script on an XTC trajectory (what ChACRA's process-output passes: state_{i}.xtc)."""
+import os
+import struct
+import sys
+from collections import Counter
+
+import numpy as np
+import pytest
+
+import xtc_oracle as xo
+from conftest import GOLDEN, ROOT
+
+pytestmark = pytest.mark.gpu
+GC = os.path.join(ROOT, "chacra_b200", "getcontacts")
+TOP = os.path.join(GOLDEN, "5xnd_topology.pdb")
+TRJ = os.path.join(GOLDEN, "5xnd_trajectory.dcd")
+
+
+def _write_int_frames(path, frames_ints, precision=1000.0, **kw):
+    with open(path, "wb") as fh:
+        for k, ints in enumerate(frames_ints):
+            n = len(ints)
+            data, mn, mx, si = xo.encode_ints(ints, **kw)
+            fh.write(struct.pack(">iiif", 1995, n, k, float(k)) + b"\0" * 36 + struct.pack(">i", n))
+            fh.write(struct.pack(">f3i3iii", precision, *mn, *mx, si, len(data)) + data + b"\0" * ((-len(data)) % 4))
+
+
+@pytest.mark.parametrize("wide", [False, True])
+def test_decoder_matches_oracle_on_every_stream_feature(tmp_path, wide):
+    """Random walks with jumps (runs of every length, both radix directions, flag-0 repeats); `wide`: one axis spans
+    more than 2^24 grid steps, so the large integers are three separate bit fields instead of one packed number
+    (also exercises packed numbers of more than 64 bits when narrow axes are still large)."""
+    from chacra_b200.xtc import XTCFile
+    rng = np.random.default_rng(11 + wide)
+    n = 777
+    frames = []
+    for f in range(37):
+        steps = rng.integers(-150, 150, (n, 3))
+        jumps = (rng.random((n, 1)) < 0.1) * rng.integers(-5000, 5000, (n, 3))
+        ints = np.cumsum(steps + jumps, 0) + rng.integers(-100000, 100000, 3)
+        if wide:
+            ints[:, 0] *= 300
+        elif f % 3 == 0:
+            ints = ints * np.array([60, 70, 80])       # ~2^22 per axis: a packed triple of about 67 bits
+        frames.append(ints)
+    path = str(tmp_path / "r.xtc")
+    _write_int_frames(path, frames, adapt=True)
+    x = XTCFile(path)
+    assert (x.n_frames, x.n_atoms) == (37, n)
+    got = x.read()
+    want = np.stack([xo.ints_to_angstrom(i) for i in frames])
+    assert np.array_equal(got, want)
+    assert np.array_equal(got, xo.read_xtc(path))
+    # strided and partial reads gather the right frames
+    assert np.array_equal(x.read(3, 30, 4), want[3:31:4])
+    assert np.array_equal(x.read(36, None, 1), want[36:])
+
+
+def test_small_raw_frames_and_corrupt_streams(tmp_path):
+    from chacra_b200.xtc import XTCFile
+    xyz = np.linspace(-3, 7, 2 * 7 * 3, dtype=np.float32).reshape(2, 7, 3)
+    p = str(tmp_path / "s.xtc")
+    xo.write_xtc(p, xyz)
+    assert np.array_equal(XTCFile(p).read(), xo.read_xtc(p))
+    # a bit stream that announces more atoms in a run than the frame has left
+    rng = np.random.default_rng(0)
+    ints = np.cumsum(rng.integers(-50, 50, (64, 3)), 0)
+    q = str(tmp_path / "c.xtc")
+    _write_int_frames(q, [ints])
+    raw = bytearray(open(q, "rb").read())
+    raw[4:8] = struct.pack(">i", 40)                 # both atom counts say 40: the last run overshoots
+    raw[52:56] = struct.pack(">i", 40)
+    open(q, "wb").write(bytes(raw))
+    with pytest.raises(ValueError):
+        XTCFile(q).read()
+
+
+def test_dynamic_contacts_from_xtc(tmp_path):
+    """The script on state.xtc = the script on a DCD holding the coordinates the XTC grid (0.001 nm) stores."""
+    from chacra_b200.trajectory import read_dcd
+    if GC not in sys.path:
+        sys.path.insert(0, GC)
+    import get_dynamic_contacts as dyn
+    frames = read_dcd(TRJ)
+    xtc = str(tmp_path / "state_0.xtc")
+    xo.write_xtc(xtc, frames)
+    out_x = tmp_path / "cont_xtc.tsv"
+    dyn.main(["--topology", TOP, "--trajectory", xtc, "--output", str(out_x), "--itypes", "all", "--distout"])
+    # the same quantised coordinates through the engine's host path, contact sets compared by atom index
+    import torch
+    import getcontacts_oracle as o
+    grid = xo.ints_to_angstrom(xo.quantize_nm(frames / np.float32(10.0)))
+    res = o.run(TOP, TOP, ["sb", "pc", "ps", "ts", "vdw", "hb", "hp"], frames=grid)
+    want = Counter((str(c[0]), c[1]) for c in res["contacts"])
+    body = [ln.rstrip("\n").split("\t") for ln in open(out_x)][2:]
+    got = Counter((t[0], t[1]) for t in body)
+    assert got == want and len(body) == len(res["contacts"])
+    assert {int(t[0]) for t in body} == set(range(20))
