@@ -282,8 +282,8 @@ def main():
                                     "kernel": "bin_frames_kernel", "avg_launch_ms": bin_ms,
                                     "algorithmic_bytes_per_launch": bytes_per_launch,
                                     "kernel_share_of_step": st["bin_ms_total"] / ms},
-                "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": int(S * F * N * 12),
-                        "d2h_bytes_per_step": int(eng.counts_tensor.numel() * 4), "steps": args.e2e_steps},
+                "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": int(S * F * N * 12) * world,
+                        "d2h_bytes_per_step": int(eng.counts_tensor.numel() * 4) * world, "steps": args.e2e_steps},
                 "gpu_launches": int(launches), "clocks": clocks,
                 "engine": {k: st[k] for k in ("path", "smem_bytes", "threads", "grid", "bin_smem_bytes", "bin_grid", "chunk_frames", "record_bytes")}}
         if world == 1 and not args.no_cpu_baseline:
