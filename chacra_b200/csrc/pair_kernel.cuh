@@ -121,7 +121,7 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                    hpmask + (size_t)(gidx / frag_frames - frag0) * T.n_pair, (int)gidx,
                    water_scratch(wscratch, blockIdx.x, T.n_solv), &M->nmark};
         // ---- E: pair interactions ------------------------------------------------------------------------------
-        const float cut2 = P.pre2;            // largest exact float32 cutoff^2 of the enabled pair types
+        const float cut2p = P.pre2 * 1.000002f;       // largest cutoff^2 of the enabled pair types, padded for the fused filter
         int q1n = 0, qfn = 0, q2n = 0, q3n = 0;
         // E1 state.  A tile = 32 consecutive cell-sorted atoms of grid A, one per lane (atom i).  Lane ranges:
         // 0..4 = half shell of grid A (own row from the slot after i to the end of cell x+1, then rows (y+1,z) (y-1,z+1)
@@ -194,7 +194,8 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                     k0 = 0;
                     if (maxlen == 0) continue;
                 }
-                // 32 candidate slots of every lane's range, four at a time: exact float32 d2 against the largest cutoff.
+                // 32 candidate slots of every lane's range, four at a time: fused-multiply-add d2 against the padded largest cutoff
+                // (a superset filter: every class test in E2 compares the EXACT float32 d2 with its own cutoff).
                 // Slots past the lane's own range are computed too (they lie inside the record: at most 35 slots after
                 // the sorted atoms, where the aux atoms and the cell starts follow) and masked off afterwards.
                 const int n = min(32, maxlen - k0);
@@ -205,10 +206,10 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
 #pragma unroll 2
                 for (int k4 = 0; k4 < n; k4 += 4) {
                     const float4 a = pj[k4], b = pj[k4 + 1], c = pj[k4 + 2], d = pj[k4 + 3];
-                    const unsigned nib = (dist2_exact(ix, iy, iz, a.x, a.y, a.z) <= cut2 ? 1u : 0u) |
-                                         (dist2_exact(ix, iy, iz, b.x, b.y, b.z) <= cut2 ? 2u : 0u) |
-                                         (dist2_exact(ix, iy, iz, c.x, c.y, c.z) <= cut2 ? 4u : 0u) |
-                                         (dist2_exact(ix, iy, iz, d.x, d.y, d.z) <= cut2 ? 8u : 0u);
+                    const unsigned nib = (dist2_fused(ix, iy, iz, a.x, a.y, a.z) <= cut2p ? 1u : 0u) |
+                                         (dist2_fused(ix, iy, iz, b.x, b.y, b.z) <= cut2p ? 2u : 0u) |
+                                         (dist2_fused(ix, iy, iz, c.x, c.y, c.z) <= cut2p ? 4u : 0u) |
+                                         (dist2_fused(ix, iy, iz, d.x, d.y, d.z) <= cut2p ? 8u : 0u);
                     m |= nib << k4;
                 }
                 m = lim >= 32 ? m : (lim > 0 ? m & ((1u << lim) - 1u) : 0u);
