@@ -174,10 +174,11 @@ bin_frames_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__
             h.org[0] = org[0]; h.org[1] = org[1]; h.org[2] = org[2]; h.inv = inv;
             h.nc[0] = nc[0]; h.nc[1] = nc[1]; h.nc[2] = nc[2]; h.ncell = ncell;
             *reinterpret_cast<BinHeader*>(rec) = h;
-            cells_out[0] = 0;
+            if (B.cell16) reinterpret_cast<unsigned short*>(cells_out)[0] = 0; else cells_out[0] = 0;
         }
         __syncthreads();
-        for (int c = tid; c < nkey; c += THREADS) cells_out[c + 1] = cells[c];
+        if (B.cell16) for (int c = tid; c < nkey; c += THREADS) reinterpret_cast<unsigned short*>(cells_out)[c + 1] = (unsigned short)cells[c];
+        else for (int c = tid; c < nkey; c += THREADS) cells_out[c + 1] = cells[c];
         __syncthreads();
     }
 }
@@ -200,7 +201,9 @@ hp_mask_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__ xy
     const unsigned char* rec = binned + (size_t)f * B.stride;
     const BinHeader h = *reinterpret_cast<const BinHeader*>(rec);
     const float4* spos = reinterpret_cast<const float4*>(rec + B.off_spos);
-    const int* cells = reinterpret_cast<const int*>(rec + B.off_cells);
+    const int* cells32 = reinterpret_cast<const int*>(rec + B.off_cells);
+    const unsigned short* cells16 = reinterpret_cast<const unsigned short*>(rec + B.off_cells);
+    const bool c16 = B.cell16 != 0;
     unsigned char* hm = hpmask + (size_t)(gidx / frag_frames - frag0) * T.n_pair;
     const int px = h.nc[0] + 2, pxy = px * (h.nc[1] + 2);
     const int lane = threadIdx.x & 31, warps = blockDim.x >> 5;
@@ -218,7 +221,8 @@ hp_mask_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__ xy
 #pragma unroll
             for (int r = 0; r < 9; ++r) {               // all eighteen bounds first: independent loads
                 const int base = c0 + g * h.ncell + (r % 3 - 1) * px + (r / 3 - 1) * pxy;
-                jb[r] = cells[base - 1]; je[r] = cells[base + 2];
+                jb[r] = c16 ? (int)cells16[base - 1] : cells32[base - 1];
+                je[r] = c16 ? (int)cells16[base + 2] : cells32[base + 2];
             }
 #pragma unroll
             for (int r = 0; r < 9; ++r)

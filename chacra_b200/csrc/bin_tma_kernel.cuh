@@ -249,10 +249,15 @@ bin_frames_tma_kernel(DevTopo T, DevParams P, BinLayout B, BinTmaLayout Y, const
                     if (tid + k * THREADS < NP && (info[k] & (I_HP1 | I_HP2))) list[atomicAdd(&M.nlist, 1)] = dst[k];
             }
             // cell starts 0..nkey (the last one = total) to the record, coalesced
-            int4* cells_out = reinterpret_cast<int4*>(rec + B.off_cells);
-            for (int q = tid; 4 * q <= nkey; q += THREADS) {
-                const uint2 w = reinterpret_cast<const uint2*>(bsm)[q];
-                cells_out[q] = make_int4((int)(w.x & 0xffffu), (int)(w.x >> 16), (int)(w.y & 0xffffu), (int)(w.y >> 16));
+            if (B.cell16) {                 // the packed scan result as it is
+                uint4* cells_out = reinterpret_cast<uint4*>(rec + B.off_cells);
+                for (int q = tid; 8 * q <= nkey; q += THREADS) cells_out[q] = reinterpret_cast<const uint4*>(bsm)[q];
+            } else {
+                int4* cells_out = reinterpret_cast<int4*>(rec + B.off_cells);
+                for (int q = tid; 4 * q <= nkey; q += THREADS) {
+                    const uint2 w = reinterpret_cast<const uint2*>(bsm)[q];
+                    cells_out[q] = make_int4((int)(w.x & 0xffffu), (int)(w.x >> 16), (int)(w.y & 0xffffu), (int)(w.y >> 16));
+                }
             }
         }
         if (tid == 0) {

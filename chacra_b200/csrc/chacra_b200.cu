@@ -93,7 +93,7 @@ static size_t al16(size_t v) { return (v + 15) & ~size_t(15); }
 
 // Decide where a frame lives while its pairs are enumerated (shared memory or in place in global memory) and lay
 // out the binned record and the pair kernel's shared memory.
-static int plan(chc_ctx* ctx) {
+static int plan(chc_ctx* ctx, size_t cells_cap = 49152) {
     const DevTopo& T = ctx->T;
     PairLayout& L = ctx->L;
     BinLayout& B = ctx->B;
@@ -113,20 +113,23 @@ static int plan(chc_ctx* ctx) {
     const size_t queues = queue_bytes(true, &q1b, &qfb, &q2b);
     const size_t tables = 2 * al16(4 * (size_t)T.K * T.K) + al16(sizeof(PairMisc));
     // ~3 cells per pair atom keeps the cells at the cutoff size for protein-like densities
-    size_t want_cells = std::min<size_t>(49152, std::max<size_t>(2048, 3 * (size_t)T.n_pair));
+    if (const char* e = getenv("CHACRA_MAX_CELLS")) cells_cap = std::min<size_t>(cells_cap, (size_t)std::max(2048, atoi(e)));   // test hook
+    size_t want_cells = std::min<size_t>(cells_cap, std::max<size_t>(2048, 3 * (size_t)T.n_pair));
     const size_t plain_bits = al16(4 * (size_t)((ctx->n_pairs + 31) / 32));
     ctx->small_path = false;
     for (size_t cells = std::min<size_t>(want_cells, 16384); cells >= 2048 && cells >= (size_t)T.n_pair; cells -= 1024) {
-        size_t need = 128 + (size_t)B.fixed_bytes + al16(4 * cells) + al16(4 * (size_t)T.n_pair) + plain_bits + queues + tables;
+        size_t need = 128 + (size_t)B.fixed_bytes + al16(2 * cells) + al16(4 * (size_t)T.n_pair) + plain_bits + queues + tables;
         if (need <= SMEM_LIMIT) { ctx->small_path = true; want_cells = cells; break; }
     }
     if (getenv("CHACRA_FORCE_LARGE")) ctx->small_path = false;     // test hook: exercise the in-place path on small systems
     B.max_cells = (int)want_cells;
-    B.stride = (long long)((B.off_cells + al16(4 * (size_t)B.max_cells) + 127) & ~size_t(127));
+    B.cell16 = ctx->small_path ? 1 : 0;     // n_pair < 65 536 there by a wide margin; the large path keeps 32-bit starts
+    const size_t cell_bytes = B.cell16 ? 2 : 4;
+    B.stride = (long long)((B.off_cells + al16(cell_bytes * (size_t)B.max_cells) + 127) & ~size_t(127));
     size_t off = 0;
     if (ctx->small_path) {
         L.off_rec = (int)off;   off += al16((size_t)B.fixed_bytes); off = (off + 127) & ~size_t(127);
-        L.off_cells = (int)off; off += al16(4 * (size_t)B.max_cells);
+        L.off_cells = (int)off; off += al16(cell_bytes * (size_t)B.max_cells);
         L.off_lkey = (int)off;  off += al16(4 * (size_t)T.n_pair);
         L.off_bits = (int)off;  off += plain_bits;
         L.bits_words = (int)((ctx->n_pairs + 31) / 32);
@@ -290,6 +293,13 @@ extern "C" int chc_create(chc_ctx** out, const chc_topology* t, const chc_params
     if (const char* e = getenv("CHACRA_BIN_VARIANT")) {           // test hook
         const int v = atoi(e);
         if (v < 3 || plan_bin_tma(v)) ctx->bin_variant = v;
+    }
+    if (ctx->bin_variant >= 3 && ctx->Y.max_cells + 1 < ctx->B.max_cells) {
+        // the record need not hold more cell starts than this binning kernel can count
+        const int v = ctx->bin_variant;
+        const bool was_small = ctx->small_path;
+        rc = plan(ctx, (size_t)ctx->Y.max_cells + 1);
+        if (rc != CHC_OK || ctx->small_path != was_small || !plan_bin_tma(v)) return fail(ctx, CHC_E_INVALID, "internal: cell capacity replanning failed");
     }
     ctx->bin_tma = ctx->bin_variant >= 3;
     if (ctx->bin_tma) ctx->bin_smem = ctx->Y.total;
@@ -609,8 +619,9 @@ extern "C" int chc_xtc_decode(const void* d_blob, const chc_xtc_frame* d_meta, i
     unsigned* status = nullptr;
     if (cudaMalloc(&status, 4) != cudaSuccess) return CHC_E_CUDA;
     cudaMemsetAsync(status, 0, 4, stream);
-    const int threads = 128;
-    const int blocks = (int)std::min<int64_t>((n_frames + threads - 1) / threads, 148 * 16);
+    const char* tenv = getenv("CHACRA_XTC_THREADS");
+    const int threads = tenv ? atoi(tenv) : 32;    // one frame per thread and the chain is serial: spread the warps over the SMs
+    const int blocks = (int)std::min<int64_t>((n_frames + threads - 1) / threads, 148 * 64);
     xtc_decode_kernel<<<blocks, threads, 0, stream>>>(static_cast<const unsigned*>(d_blob), reinterpret_cast<const XtcFrameMeta*>(d_meta),
                                                     (int)n_frames, n_atoms, d_xyz, frame_stride, status);
     unsigned st = 0;

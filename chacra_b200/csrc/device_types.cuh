@@ -82,7 +82,7 @@ struct DevOut {
 
 // ---- binned frames: what the streaming/binning kernel hands to the pair kernel -----------------------
 // One record per frame in a device buffer, every section 16-byte aligned:
-//   BinHeader | spos float4[NP] (cell-sorted x, y, z, flags|pair_index<<14) | aux float[3*NA] | cells int[ncell+1]
+//   BinHeader | spos float4[NP] (cell-sorted x, y, z, flags|pair_index<<14) | aux float[3*NA] | cells u16|int[ncell+1]
 // `cells` are exclusive starts over a padded (nc+2)^3 grid (one guard layer), x fastest.
 struct BinHeader {
     float org[3]; float inv;
@@ -92,6 +92,7 @@ struct BinLayout {
     int off_spos, off_aux, off_cells;   // bytes from the start of the record
     int fixed_bytes;                    // header + spos + aux (multiple of 16): one bulk copy
     int max_cells;                      // capacity of the cells section (entries incl. the end sentinel)
+    int cell16;                         // cell starts are unsigned 16-bit (records the pair kernel keeps in shared memory)
     long long stride;                   // bytes per record
 };
 

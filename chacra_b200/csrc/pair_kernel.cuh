@@ -14,6 +14,7 @@
 // The three stages form one resumable loop so that E2 and E3 are emitted exactly once in the SASS (the first
 // version inlined them at ~45 sites and stalled on instruction fetch, profiles/r01_v1_*).
 #pragma once
+#include <type_traits>
 #include "frame_phases.cuh"
 #include "water_phase.cuh"
 
@@ -51,6 +52,7 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
     PairMisc* M = reinterpret_cast<PairMisc*>(smem + L.off_misc);
     // queue entries: the pair (i, j) of sorted slots is one word on the shared-memory path (slots < 65 536), two otherwise
     constexpr int QW = SMALL ? 1 : 2;
+    using cell_t = typename std::conditional<SMALL, unsigned short, int>::type;     // BinLayout::cell16 <=> SMALL
     unsigned* q1 = reinterpret_cast<unsigned*>(smem + L.off_q1) + warp * (QW * Q1_CAP);            // survivors
     unsigned* qf = reinterpret_cast<unsigned*>(smem + L.off_qf) + warp * (QW * QF_CAP);            // filtered survivors
     unsigned* q2 = reinterpret_cast<unsigned*>(smem + L.off_q2) + warp * (2 * (QW + 1) * Q2_CAP);  // plain | polar: pair, class
@@ -78,11 +80,11 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
     for (int f = blockIdx.x; f < n_frames; f += gridDim.x) {
         const unsigned char* rec = binned + (size_t)f * B.stride;
         const long long gidx = first_index + f;
-        const float4* spos; const float* aux; const int* cells; const BinHeader* hdr;
+        const float4* spos; const float* aux; const cell_t* cells; const BinHeader* hdr;
         if (SMALL) {
             if (tid == 0) {
                 const int ncell = __ldcg(&reinterpret_cast<const BinHeader*>(rec)->ncell);
-                const unsigned cbytes = (unsigned)((4 * ((T.n_pair_a < T.n_pair ? 2 : 1) * ncell + 1) + 15) & ~15);
+                const unsigned cbytes = (unsigned)((sizeof(cell_t) * ((T.n_pair_a < T.n_pair ? 2 : 1) * ncell + 1) + 15) & ~15);
                 // the previous frame's generic-proxy reads of these buffers are ordered before the async-proxy writes
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 mbar_expect_tx(&M->bar, (unsigned)B.fixed_bytes + cbytes);
@@ -102,7 +104,7 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
             hdr = reinterpret_cast<const BinHeader*>(smem + L.off_rec);
             spos = reinterpret_cast<const float4*>(smem + L.off_rec + B.off_spos);
             aux = reinterpret_cast<const float*>(smem + L.off_rec + B.off_aux);
-            cells = reinterpret_cast<const int*>(smem + L.off_cells);
+            cells = reinterpret_cast<const cell_t*>(smem + L.off_cells);
         } else {
             if (tid == 0) { M->cursor = 0; M->ring_cursor = 0; M->nmark = 0; }
             gen = gen + 1u;
@@ -113,7 +115,7 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
             hdr = reinterpret_cast<const BinHeader*>(rec);
             spos = reinterpret_cast<const float4*>(rec + B.off_spos);
             aux = reinterpret_cast<const float*>(rec + B.off_aux);
-            cells = reinterpret_cast<const int*>(rec + B.off_cells);
+            cells = reinterpret_cast<const cell_t*>(rec + B.off_cells);
         }
         __syncthreads();
         const int px = hdr->nc[0] + 2, pxy = px * (hdr->nc[1] + 2), ncell = hdr->ncell;
@@ -181,13 +183,13 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                     }
                     len = 0;
                     if (my_i >= 0) {
-                        if (r == 0) { beg = my_i + 1; len = cells[my_c + 2] - beg; }
+                        if (r == 0) { beg = my_i + 1; len = (int)cells[my_c + 2] - beg; }
                         else {
                             int base;
                             if (r < 5) base = my_c + ((r == 1 || r == 4) - (r == 2)) * px + (r >= 2 ? pxy : 0);
                             else { const int q = r - 5; base = my_c + ncell + (q % 3 - 1) * px + (q / 3 - 1) * pxy; }
-                            beg = cells[base - 1];
-                            len = cells[base + 2] - beg;
+                            beg = (int)cells[base - 1];
+                            len = (int)cells[base + 2] - beg;
                         }
                     }
                     maxlen = __reduce_max_sync(FULL, len);

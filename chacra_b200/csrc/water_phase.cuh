@@ -28,8 +28,9 @@ __device__ __forceinline__ void bridge_emit(const DevTopo& T, const DevParams& P
                     sqrtf(dist2_exact(xa.x, xa.y, xa.z, xb.x, xb.y, xb.z)));
 }
 
+template <class cell_t>
 __device__ __forceinline__ void water_bridges(const DevTopo& T, const DevParams& P, const DevOut& O, const FrameCtx& F,
-                                              const WaterScratch& W, const int* cells, int px, int pxy, int ncell,
+                                              const WaterScratch& W, const cell_t* cells, int px, int pxy, int ncell,
                                               const BinHeader* hdr, const int* nmark, int tid, int nthreads) {
     const int lane = tid & 31, nwarps = nthreads >> 5;
     const int nm = *nmark;
@@ -59,7 +60,7 @@ __device__ __forceinline__ void water_bridges(const DevTopo& T, const DevParams&
         for (int g = 0; g < ngrid; ++g)
             for (int r = 0; r < 9; ++r) {
                 const int base = c0 + g * ncell + (r % 3 - 1) * px + (r / 3 - 1) * pxy;
-                const int jb = cells[base - 1], je = cells[base + 2];
+                const int jb = (int)cells[base - 1], je = (int)cells[base + 2];
                 for (int j = jb + lane; j < je; j += 32) {
                     const float4 xj = F.spos[j];
                     const unsigned wj = __float_as_uint(xj.w);

@@ -45,6 +45,7 @@ def main():
     dev = x.read_device(0, n - 1)
     torch.cuda.synchronize()
     t_read = time.time() - t0
+    t_host, t_dev = x.last_timing
     want = xo.ints_to_angstrom(xo.quantize_nm(base[:3] / 10.0))
     assert (dev[:3].cpu().numpy() == want).all() and (dev[200:203].cpu().numpy() == want).all()
     eng = ContactEngine(compile_topology(atoms), bench.ITYPES, n_states=1)
@@ -58,8 +59,8 @@ def main():
     t_all = time.time() - t0
     comp = x.compressed_bytes() * n / x.n_frames
     print("xtc: %d frames x %d atoms, %.1f MB compressed (%.2f of float32) | encode(oracle, 200 frames) %.1f s | header walk %.2f s | "
-          "read_device %.3f s = %.0f frames/s (%.2f GB/s of float32 out) | read + contacts %.3f s = %.0f frames/s" % (
-              n, x.n_atoms, comp / 1e6, comp / (12.0 * x.n_atoms * n), t_enc, t_index, t_read, n / t_read,
+          "read_device %.3f s (file->pinned %.3f, H2D+decode %.3f) = %.0f frames/s (%.2f GB/s of float32 out) | read + contacts %.3f s = %.0f frames/s" % (
+              n, x.n_atoms, comp / 1e6, comp / (12.0 * x.n_atoms * n), t_enc, t_index, t_read, t_host, t_dev, n / t_read,
               12.0 * x.n_atoms * n / t_read / 1e9, t_all, n / t_all))
     os.unlink(xtc)
 
