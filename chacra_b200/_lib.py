@@ -89,6 +89,7 @@ SYMBOLS = {
     "chc_read_counts": (C.c_int, [vp, C.c_int, vp, C.c_int64, vp]),
     "chc_submit_frames": (C.c_int, [vp, C.c_int, vp, C.c_int64, C.c_int64, C.c_int64, vp]),
     "chc_submit_frames_host": (C.c_int, [vp, C.c_int, vp, C.c_int64, C.c_int64, vp]),
+    "chc_submit_frames_indexed": (C.c_int, [vp, C.c_int, vp, vp, C.c_int64, C.c_int64, C.c_int64, vp]),
     "chc_synchronize": (C.c_int, [vp, vp]),
     "chc_drain_contacts": (C.c_int, [vp, vp, C.c_int64, C.POINTER(C.c_int64), vp]),
     "chc_drain_near_cutoff": (C.c_int, [vp, vp, C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_int64), vp]),

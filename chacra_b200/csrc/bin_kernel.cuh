@@ -27,7 +27,7 @@ template <int THREADS, int APT, int MINB>
 __global__ void __launch_bounds__(THREADS, MINB)
 bin_frames_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__ xyz, long long frame_stride, int n_frames,
                   long long first_index, int frag_frames, long long frag0, unsigned char* __restrict__ binned,
-                  unsigned char* __restrict__ hpmask) {
+                  unsigned char* __restrict__ hpmask, const long long* __restrict__ src_index) {
     extern __shared__ __align__(16) int cells[];          // [B.max_cells]
     __shared__ BinShared M;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -45,7 +45,7 @@ bin_frames_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__
         }
     }
     for (int f = blockIdx.x; f < n_frames; f += gridDim.x) {
-        const float* __restrict__ X = xyz + (size_t)f * frame_stride;
+        const float* __restrict__ X = frame_ptr(xyz, src_index, f, frame_stride);
         unsigned char* rec = binned + (size_t)f * B.stride;
         float4* spos = reinterpret_cast<float4*>(rec + B.off_spos);
         float* aux = reinterpret_cast<float*>(rec + B.off_aux);
@@ -192,12 +192,12 @@ bin_frames_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__
 __global__ void __launch_bounds__(256)
 hp_mask_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__ xyz, long long frame_stride, int n_frames,
                long long first_index, int frag_frames, long long frag0, const unsigned char* __restrict__ binned,
-               unsigned char* __restrict__ hpmask) {
+               unsigned char* __restrict__ hpmask, const long long* __restrict__ src_index) {
     const int f0 = (int)((frag_frames - first_index % frag_frames) % frag_frames);
     const long long f = f0 + (long long)blockIdx.x * frag_frames;
     if (f >= n_frames) return;
     const long long gidx = first_index + f;
-    const float* __restrict__ X = xyz + (size_t)f * frame_stride;
+    const float* __restrict__ X = frame_ptr(xyz, src_index, f, frame_stride);
     const unsigned char* rec = binned + (size_t)f * B.stride;
     const BinHeader h = *reinterpret_cast<const BinHeader*>(rec);
     const float4* spos = reinterpret_cast<const float4*>(rec + B.off_spos);

@@ -49,7 +49,7 @@ template <int THREADS, int APT, int NBUF>
 __global__ void __launch_bounds__(THREADS, NBUF == 1 ? 2 : 1)
 bin_frames_tma_kernel(DevTopo T, DevParams P, BinLayout B, BinTmaLayout Y, const float* __restrict__ xyz, long long frame_stride,
                       int n_frames, int frag_frames, long long frag_slot0, unsigned char* __restrict__ binned,
-                      unsigned char* __restrict__ hpmask, int fuse_hp) {
+                      unsigned char* __restrict__ hpmask, int fuse_hp, const long long* __restrict__ src_index) {
     constexpr bool STAGE = NBUF == 2;     // record image in shared memory + bulk store, or direct global stores
     extern __shared__ __align__(128) unsigned char bsm[];      // counters u16[8 cap_groups THREADS] | aux table | frame buffer(s)
     __shared__ BinTmaShared M;
@@ -65,7 +65,7 @@ bin_frames_tma_kernel(DevTopo T, DevParams P, BinLayout B, BinTmaLayout Y, const
     // bulk copy of frame f into buffer b: source rounded down / size rounded up to 16 bytes (the consumer skips the
     // leading floats); the rounding never leaves the 16-byte granule the caller's allocation ends in
     auto issue = [&](int f, int b) {
-        const unsigned long long a = reinterpret_cast<unsigned long long>(xyz + (size_t)f * frame_stride);
+        const unsigned long long a = reinterpret_cast<unsigned long long>(frame_ptr(xyz, src_index, f, frame_stride));
         const unsigned long long a0 = a & ~15ull;
         const unsigned bytes = ((unsigned)(a - a0) + frame_bytes + 15u) & ~15u;
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -109,7 +109,7 @@ bin_frames_tma_kernel(DevTopo T, DevParams P, BinLayout B, BinTmaLayout Y, const
         unsigned char* rec = binned + (size_t)f * B.stride;
         unsigned char* fbuf = bsm + (b ? Y.off_buf1 : Y.off_buf0);
         const float* Xs = reinterpret_cast<const float*>(fbuf) +
-                          (int)((reinterpret_cast<unsigned long long>(xyz + (size_t)f * frame_stride) & 15ull) >> 2);
+                          (int)((reinterpret_cast<unsigned long long>(frame_ptr(xyz, src_index, f, frame_stride)) & 15ull) >> 2);
         const int fidx = Y.open_phase + f;                      // position inside the fragment sequence of this launch
         if (it > 0) { fphase += (int)gridDim.x; while (fphase >= frag_frames) fphase -= frag_frames; }
         const bool opens = fuse_hp && fphase == 0;

@@ -398,8 +398,8 @@ static int ensure_hpmask(chc_ctx* ctx, int64_t frags) {
     return CHC_OK;
 }
 
-extern "C" int chc_submit_frames(chc_ctx* ctx, int state, const float* d_xyz, int64_t n_frames, int64_t first_index,
-                                 int64_t frame_stride, void* stream_) {
+static int submit_impl(chc_ctx* ctx, int state, const float* d_xyz, const long long* d_src, int64_t n_frames, int64_t first_index,
+                       int64_t frame_stride, void* stream_) {
     if (!ctx) return CHC_E_INVALID;
     if (n_frames == 0) return CHC_OK;
     if (!d_xyz || n_frames < 0 || first_index < 0 || state < 0 || state >= ctx->prm.n_states)
@@ -429,7 +429,8 @@ extern "C" int chc_submit_frames(chc_ctx* ctx, int state, const float* d_xyz, in
     // kernel consumes them (from L2 when the chunk fits)
     for (int64_t c0 = 0; c0 < n_frames; c0 += ctx->chunk_frames) {
         const int n = (int)std::min<int64_t>(ctx->chunk_frames, n_frames - c0);
-        const float* x = d_xyz + (size_t)c0 * frame_stride;
+        const float* x = d_src ? d_xyz : d_xyz + (size_t)c0 * frame_stride;     // indexed: offsets count from the caller's base
+        const long long* src = d_src ? d_src + c0 : nullptr;
         chc_ctx::Ev3 ev{nullptr, nullptr, nullptr};
         if (ctx->timing) {
             if (!ctx->ev_free.empty()) { ev = ctx->ev_free.back(); ctx->ev_free.pop_back(); }
@@ -443,8 +444,8 @@ extern "C" int chc_submit_frames(chc_ctx* ctx, int state, const float* d_xyz, in
             BinTmaLayout Y = ctx->Y;
             Y.open_phase = (int)(fi % F);
             long long slot0 = fi / F - frag0;
-            void* args_reg[] = {&ctx->T, &ctx->P, &ctx->B, &x, &fs, &nn, &fi, &ff, &fr0, &ctx->binned, &ctx->hpmask};
-            void* args_tma[] = {&ctx->T, &ctx->P, &ctx->B, &Y, &x, &fs, &nn, &ff, &slot0, &ctx->binned, &ctx->hpmask, &fuse};
+            void* args_reg[] = {&ctx->T, &ctx->P, &ctx->B, &x, &fs, &nn, &fi, &ff, &fr0, &ctx->binned, &ctx->hpmask, &src};
+            void* args_tma[] = {&ctx->T, &ctx->P, &ctx->B, &Y, &x, &fs, &nn, &ff, &slot0, &ctx->binned, &ctx->hpmask, &fuse, &src};
             CK(cudaLaunchKernel(bin_kernel_fn(ctx->bin_variant, ctx->tma_apt, nullptr), dim3(std::min(n, ctx->bin_grid)), dim3(ctx->bin_threads),
                                 ctx->bin_tma ? args_tma : args_reg, ctx->bin_smem, stream));
         }
@@ -457,7 +458,7 @@ extern "C" int chc_submit_frames(chc_ctx* ctx, int state, const float* d_xyz, in
                 const int n_open = (int)((n - f0 + F - 1) / F);
                 const int by = std::max(1, std::min(1024, (ctx->T.n_hp_base + 7) / 8));     // one base carbon per warp
                 hp_mask_kernel<<<dim3(n_open, by), 256, 0, stream>>>(ctx->T, ctx->P, ctx->B, x, frame_stride, n, fi, F, frag0,
-                                                                     ctx->binned, ctx->hpmask);
+                                                                     ctx->binned, ctx->hpmask, src);
                 CK(cudaGetLastError());
                 ctx->st.kernel_launches++;
             }
@@ -476,6 +477,21 @@ extern "C" int chc_submit_frames(chc_ctx* ctx, int state, const float* d_xyz, in
     ctx->st.frames_submitted += n_frames;
     ctx->last_state = state; ctx->next_index = first_index + n_frames;
     return CHC_OK;
+}
+
+extern "C" int chc_submit_frames(chc_ctx* ctx, int state, const float* d_xyz, int64_t n_frames, int64_t first_index,
+                                 int64_t frame_stride, void* stream_) {
+    return submit_impl(ctx, state, d_xyz, nullptr, n_frames, first_index, frame_stride, stream_);
+}
+
+// frame f of the state trajectory is the stored frame d_source_index[f] of d_xyz (all replicas' frames in
+// one device buffer).  Replaces get_state_coordinates_from_replica + write_state_trajectory
+// (chacra/trajectories/process_hremd.py:184-230): no state trajectory is ever materialised.
+extern "C" int chc_submit_frames_indexed(chc_ctx* ctx, int state, const float* d_xyz, const int64_t* d_source_index, int64_t n_frames,
+                                         int64_t first_index, int64_t frame_stride, void* stream_) {
+    if (ctx && n_frames > 0 && !d_source_index) return fail(ctx, CHC_E_INVALID, "submit_frames_indexed: null source index");
+    static_assert(sizeof(long long) == sizeof(int64_t), "index width");
+    return submit_impl(ctx, state, d_xyz, reinterpret_cast<const long long*>(d_source_index), n_frames, first_index, frame_stride, stream_);
 }
 
 extern "C" int chc_submit_frames_host(chc_ctx* ctx, int state, const float* h_xyz, int64_t n_frames, int64_t first_index, void* stream_) {

@@ -31,6 +31,11 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned by
 }
 
 // grid coordinate of x along one axis; the binning kernel and the pair kernel must agree bit for bit (-fmad=false)
+// frame f of a submission: consecutive, or picked through a source index (replica -> state demultiplexing)
+__device__ __forceinline__ const float* frame_ptr(const float* xyz, const long long* __restrict__ src, long long f, long long frame_stride) {
+    return xyz + (size_t)(src ? __ldg(src + f) : f) * (size_t)frame_stride;
+}
+
 __device__ __forceinline__ int cell_of(float x, float origin, float inv, int n) {
     int c = (int)((x - origin) * inv);
     return min(max(c, 0), n - 1);

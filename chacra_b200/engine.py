@@ -159,6 +159,23 @@ class ContactEngine:
         self._check(self.lib.chc_submit_frames_host(self._ctx, state, ptr, nf, first_index, self._stream()))
         self._keepalive = xyz
 
+    def submit_indexed(self, pool, source_index, state: int = 0, first_index: int = 0):
+        """Frame k of the submission is ``pool[source_index[k]]`` (replica -> state demultiplexing).
+        ``pool``: contiguous CUDA float32 [M][N][3]; ``source_index``: int64, CUDA tensor or host array."""
+        torch = self._torch
+        n = self.topo.n_atoms
+        if not (isinstance(pool, torch.Tensor) and pool.is_cuda and pool.dtype == torch.float32 and pool.dim() == 3
+                and tuple(pool.shape[1:]) == (n, 3) and pool.is_contiguous() and pool.device.index == self.device):
+            raise ChacraError("frame pool must be a contiguous float32 [M][%d][3] tensor on cuda:%d" % (n, self.device))
+        idx = source_index if isinstance(source_index, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(source_index, dtype=np.int64))
+        idx = idx.to(device=pool.device, dtype=torch.int64).contiguous()
+        if idx.dim() != 1:
+            raise ChacraError("source_index must be one-dimensional")
+        if idx.numel() and (int(idx.min()) < 0 or int(idx.max()) >= pool.shape[0]):
+            raise ChacraError("source_index outside the pool of %d frames" % pool.shape[0])
+        self._check(self.lib.chc_submit_frames_indexed(self._ctx, state, pool.data_ptr(), idx.data_ptr(), idx.numel(), first_index, 0, self._stream()))
+        self._keepalive_idx = getattr(self, "_keepalive_idx", [])[-63:] + [idx]      # read by kernels still in the stream
+
     def synchronize(self):
         self._check(self.lib.chc_synchronize(self._ctx, self._stream()))
 

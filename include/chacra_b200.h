@@ -198,6 +198,12 @@ int chc_submit_frames(chc_ctx* ctx, int state, const float* d_xyz, int64_t n_fra
  * the device itself (double buffered). */
 int chc_submit_frames_host(chc_ctx* ctx, int state, const float* h_xyz, int64_t n_frames, int64_t first_index,
                            void* stream);
+/* Replica -> state demultiplexing without a state trajectory (replaces
+ * get_state_coordinates_from_replica / write_state_trajectory, chacra/trajectories/process_hremd.py:184-230):
+ * frame k of the submission is read from d_xyz + d_source_index[k]*frame_stride floats.  d_source_index is a
+ * DEVICE array of n_frames entries and must stay valid until the work has run; everything else as above. */
+int chc_submit_frames_indexed(chc_ctx* ctx, int state, const float* d_xyz, const int64_t* d_source_index,
+                              int64_t n_frames, int64_t first_index, int64_t frame_stride, void* stream);
 int chc_synchronize(chc_ctx* ctx, void* stream);
 
 /* Copy out (and clear) the records accumulated so far.  *n = records copied. */
