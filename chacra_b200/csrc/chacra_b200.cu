@@ -10,6 +10,7 @@
 #include "bin_tma_kernel.cuh"
 #include "pair_kernel.cuh"
 #include "xtc_decode.cuh"
+#include "pca_perm.cuh"
 
 #define PAIR_THREADS 1024
 #define SMEM_LIMIT (227 * 1024)
@@ -601,6 +602,37 @@ extern "C" int chc_set_timing(chc_ctx* ctx, int on) {
     ctx->timing = on != 0;
     if (on) { ctx->st.pair_ms_total = 0.0; ctx->st.bin_ms_total = 0.0; ctx->st.timed_chunks = 0; }
     return CHC_OK;
+}
+
+// ---- ContactPCA permutation test (X4) -------------------------------------------------------------------------
+extern "C" int chc_permuted_pca(const double* d_vals, int32_t n, int32_t p, int32_t n_perm, const uint8_t* d_perms_in,
+                                uint8_t* d_perms_out, uint64_t seed, double* d_work, double* d_evr, int device, void* stream_) {
+    if (n_perm == 0) return CHC_OK;
+    if (!d_vals || !d_work || !d_evr || n < 1 || n > PCA_MAXN || p < 1 || n_perm < 0) return CHC_E_INVALID;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (cudaSetDevice(device) != cudaSuccess) return CHC_E_CUDA;
+    pca_center_kernel<<<(p + 255) / 256, 256, 0, stream>>>(d_vals, n, p, d_work);
+    const int npairs = n * (n + 1) / 2;
+    const int k = (npairs + PCA_THREADS - 1) / PCA_THREADS;
+    PcaSmem S;
+    S.tile_cols = n <= 32 ? 256 : 128;
+    size_t off = 0;
+    S.off_v = (int)off;     off += al16(8 * (size_t)S.tile_cols * n);
+    S.off_g = (int)off;     off += al16(8 * (size_t)n * n);
+    S.off_perm = (int)off;  off += al16((size_t)S.tile_cols * n);
+    S.off_pairs = (int)off; off += al16(2 * (size_t)npairs);
+    S.total = (int)off;
+    const void* fn = k <= 1 ? (const void*)pca_perm_kernel<1> : k <= 3 ? (const void*)pca_perm_kernel<3> : (const void*)pca_perm_kernel<9>;
+    if (cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, S.total) != cudaSuccess) return CHC_E_CUDA;
+    int sms = 148, per_sm = 1;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, PCA_THREADS, S.total);
+    const int grid = std::min(n_perm, sms * std::max(per_sm, 1));
+    const unsigned char* pin = d_perms_in; unsigned char* pout = d_perms_out; unsigned long long sd = seed;
+    const double* xct = d_work;
+    void* args[] = {&xct, &n, &p, &n_perm, &pin, &pout, &sd, &S, &d_evr};
+    if (cudaLaunchKernel(fn, dim3(grid), dim3(PCA_THREADS), args, S.total, stream) != cudaSuccess) return CHC_E_CUDA;
+    return cudaGetLastError() == cudaSuccess ? CHC_OK : CHC_E_CUDA;
 }
 
 extern "C" int chc_get_stats(chc_ctx* ctx, chc_stats* out) {

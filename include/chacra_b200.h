@@ -230,6 +230,18 @@ typedef struct chc_xtc_frame {
 int chc_xtc_decode(const void* d_blob, const chc_xtc_frame* d_meta, int64_t n_frames, int32_t n_atoms, float* d_xyz,
                    int64_t frame_stride, int device, void* stream);
 
+/* ContactPCA permutation test (replaces run_permuted_pca + de_correlate,
+ * chacra/ContactFrequencies.py:631-656, called from ContactPCA.permuted_pca :910-964).
+ * d_vals: DEVICE float64 [n_samples][n_features] row major (the contact-frequency table, states x contacts),
+ * n_samples <= 64.  For each of n_perm permutations every column gets its rows reordered independently and the PCA
+ * explained-variance ratios (min(n_samples, n_features) values, descending) go to d_evr [n_perm][n_comp] (DEVICE).
+ * d_perms_in (DEVICE uint8 [n_perm][n_features][n_samples], entry i = the source row of row i; may be NULL): use
+ * these row orders instead of generating them from `seed`.  d_perms_out (same shape, may be NULL): receives the
+ * row orders used.  The call is asynchronous on `stream`; d_work (DEVICE, 8*n_samples*n_features bytes) is scratch. */
+int chc_permuted_pca(const double* d_vals, int32_t n_samples, int32_t n_features, int32_t n_perm,
+                     const uint8_t* d_perms_in, uint8_t* d_perms_out, uint64_t seed, double* d_work, double* d_evr,
+                     int device, void* stream);
+
 int chc_get_stats(chc_ctx* ctx, chc_stats* out);
 int chc_set_timing(chc_ctx* ctx, int on);
 
