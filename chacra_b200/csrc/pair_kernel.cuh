@@ -130,6 +130,7 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
         // (y,z+1) (y+1,z+1) from x-1 to x+1); 5..13 (only with unselected solvent) = the full 3x3 rows of grid B.
         const int nA = T.n_pair_a;
         const int nr = T.n_pair_a < T.n_pair ? 14 : 5;
+        const unsigned nr_magic = 0xffffffffu / (unsigned)nr + 1u;
         const int ntiles = (nA + 31) >> 5;
         const int nunits = ntiles * nr;
         int r = 0, tile = -1, k0 = 0, maxlen = 0;      // warp-uniform: current range and tile, chunk offset, longest lane range
@@ -168,7 +169,7 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                     if (lane == 0) u = atomicAdd(&M->cursor, 1);
                     u = __shfl_sync(FULL, u, 0);
                     if (u >= nunits) { exhausted = true; break; }
-                    const int t = u / nr;
+                    const int t = (int)__umulhi((unsigned)u, nr_magic);         // u / nr (u < 2^16: exact with the rounded-up reciprocal)
                     r = u - t * nr;
                     if (t != tile) {
                         tile = t;

@@ -39,25 +39,39 @@ struct XtcBits {                // MSB-first bit stream over big-endian 32-bit w
     }
 };
 
-// three mixed-radix digits (radices sz[1], sz[2] < 2^24 matter) from `nbits` bits: whole bytes least significant first,
-// the remaining bits on top (xdrfile receiveints)
-__device__ __forceinline__ void xtc_ints(XtcBits& B, int nbits, const unsigned sz[3], int out[3]) {
-    if (nbits <= 32) {
-        unsigned v = 0u; int sh = 0, n = nbits;
-        while (n >= 8) { v |= B.get(8) << sh; sh += 8; n -= 8; }
-        if (n) v |= B.get(n) << sh;
-        const unsigned q = v / sz[2];
+// v / d for v < 2^52 (exact in binary64) and d < 2^24 with a precomputed reciprocal: the estimate is off by at most one
+__device__ __forceinline__ unsigned long long xtc_div(unsigned long long v, unsigned d, double inv) {
+    unsigned long long q = __double2ull_rz(__ull2double_rn(v) * inv);
+    const long long rem = (long long)(v - q * d);
+    if (rem < 0) --q; else if (rem >= (long long)d) ++q;
+    return q;
+}
+
+// the byte order of xdrfile's receiveints: whole bytes least significant first, the remaining bits on top.  W = the
+// nbits bits as one MSB-first number (nbits <= 64)
+__device__ __forceinline__ unsigned long long xtc_reorder(unsigned long long W, int nbits) {
+    const int r = nbits & 7, k = nbits >> 3;
+    if (k == 0) return W;
+    const unsigned long long rest = r ? (W & ((1ull << r) - 1ull)) : 0ull;
+    const unsigned long long top = W >> r;                                   // k bytes, first byte most significant
+    const unsigned lo = (unsigned)top, hi = (unsigned)(top >> 32);
+    const unsigned long long swapped = ((unsigned long long)__byte_perm(lo, 0u, 0x0123) << 32) | __byte_perm(hi, 0u, 0x0123);
+    const unsigned long long rev = swapped >> (64 - 8 * k);
+    return k == 8 ? rev : (rev | (rest << (8 * k)));
+}
+
+// three mixed-radix digits (radices sz[1], sz[2] < 2^24 matter) from `nbits` bits (xdrfile receiveints); inv1, inv2 =
+// 1.0 / sz[1], 1.0 / sz[2]
+__device__ __forceinline__ void xtc_ints(XtcBits& B, int nbits, const unsigned sz[3], double inv1, double inv2, int out[3]) {
+    if (nbits <= 64) {
+        unsigned long long W;
+        if (nbits <= 32) W = B.get(nbits);
+        else { const unsigned hi = B.get(nbits - 32); W = ((unsigned long long)hi << 32) | B.get(32); }
+        const unsigned long long v = xtc_reorder(W, nbits);
+        unsigned long long q, q1;
+        if (nbits <= 52) { q = xtc_div(v, sz[2], inv2); q1 = xtc_div(q, sz[1], inv1); }
+        else { q = v / sz[2]; q1 = q / sz[1]; }
         out[2] = (int)(v - q * sz[2]);
-        const unsigned q1 = q / sz[1];
-        out[1] = (int)(q - q1 * sz[1]);
-        out[0] = (int)q1;
-    } else if (nbits <= 64) {
-        unsigned long long v = 0ull; int sh = 0, n = nbits;
-        while (n >= 8) { v |= (unsigned long long)B.get(8) << sh; sh += 8; n -= 8; }
-        if (n) v |= (unsigned long long)B.get(n) << sh;
-        const unsigned long long q = v / sz[2];
-        out[2] = (int)(v - q * sz[2]);
-        const unsigned long long q1 = q / sz[1];
         out[1] = (int)(q - q1 * sz[1]);
         out[0] = (int)q1;
     } else {                    // up to 72 bits: three 32-bit limbs, schoolbook division by a radix < 2^24
@@ -84,6 +98,9 @@ __device__ __forceinline__ void xtc_ints(XtcBits& B, int nbits, const unsigned s
 __global__ void __launch_bounds__(128)
 xtc_decode_kernel(const unsigned* __restrict__ blob, const XtcFrameMeta* __restrict__ meta, int n_frames, int n_atoms,
                   float* __restrict__ xyz, long long frame_stride, unsigned* __restrict__ status) {
+    __shared__ double inv_magic[XTC_LASTIDX + 1];
+    for (int k = threadIdx.x; k <= XTC_LASTIDX; k += blockDim.x) inv_magic[k] = xtc_magicints[k] > 0 ? 1.0 / (double)xtc_magicints[k] : 0.0;
+    __syncthreads();
     for (int f = blockIdx.x * blockDim.x + threadIdx.x; f < n_frames; f += gridDim.x * blockDim.x) {
         const XtcFrameMeta m = meta[f];
         float* out = xyz + (size_t)f * frame_stride;
@@ -102,6 +119,8 @@ xtc_decode_kernel(const unsigned* __restrict__ blob, const XtcFrameMeta* __restr
         int smallnum = xtc_magicints[smallidx] / 2;
         unsigned sizesmall[3];
         sizesmall[0] = sizesmall[1] = sizesmall[2] = (unsigned)xtc_magicints[smallidx];
+        const double inv1 = 1.0 / (double)sizeint[1], inv2 = 1.0 / (double)sizeint[2];
+        double invs = inv_magic[smallidx];
         XtcBits B{src, 0ull, 0};
         const unsigned* end = src + ((m.nbytes + 3) >> 2) + 2;
         int i = 0, run = 0;
@@ -112,7 +131,7 @@ xtc_decode_kernel(const unsigned* __restrict__ blob, const XtcFrameMeta* __restr
 #pragma unroll
                 for (int k = 0; k < 3; ++k) cur[k] = (int)B.get(m.bitsizeint[k]);
             } else {
-                xtc_ints(B, m.bitsize, sizeint, cur);
+                xtc_ints(B, m.bitsize, sizeint, inv1, inv2, cur);
             }
 #pragma unroll
             for (int k = 0; k < 3; ++k) cur[k] += m.minint[k];
@@ -129,7 +148,7 @@ xtc_decode_kernel(const unsigned* __restrict__ blob, const XtcFrameMeta* __restr
                 int prev[3] = {cur[0], cur[1], cur[2]};
                 for (int k = 0; k < run; k += 3) {
                     int d[3];
-                    xtc_ints(B, smallidx, sizesmall, d);
+                    xtc_ints(B, smallidx, sizesmall, invs, invs, d);
 #pragma unroll
                     for (int c = 0; c < 3; ++c) d[c] += prev[c] - smallnum;
                     ++i;
@@ -160,6 +179,7 @@ xtc_decode_kernel(const unsigned* __restrict__ blob, const XtcFrameMeta* __restr
                 smallnum = xtc_magicints[smallidx] / 2;
             }
             sizesmall[0] = sizesmall[1] = sizesmall[2] = (unsigned)xtc_magicints[smallidx];
+            invs = inv_magic[smallidx];
         }
         if (bad) atomicOr(status, 1u);
     }

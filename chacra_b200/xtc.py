@@ -99,6 +99,8 @@ class XTCFile:
             self.n_atoms = 0
 
     # ------------------------------------------------------------------------------------------------
+    CHUNK_BYTES = 48 << 20           # compressed bytes per pipeline stage (file read of chunk k+1 under the H2D copy of chunk k)
+
     def read_device(self, beg: int = 0, end: int | None = None, stride: int = 1):
         """Frames beg, beg+stride, ... <= end (inclusive) as a CUDA float32 [F][N][3] tensor, Angstrom."""
         import torch
@@ -111,34 +113,78 @@ class XTCFile:
         if len(idx) == 0:
             return out
         t0 = time.perf_counter()
+        sizes = (self._index["nbytes"][idx].astype(np.int64) + 3) & ~3
+        cuts = [0]
+        acc = 0
+        for k, n in enumerate(sizes.tolist()):         # chunk boundaries by compressed size
+            if acc + n > self.CHUNK_BYTES and acc > 0:
+                cuts.append(k)
+                acc = 0
+            acc += n
+        cuts.append(len(idx))
+        # the file is read in chunks by a helper thread while the previous chunk crosses PCIe; the decode is ONE launch
+        # over all frames (a frame's bit stream is serial, so a launch takes as long as its slowest thread: more frames
+        # per launch cost nothing until every SM sub-partition has a warp)
+        d_blob = torch.empty(int(sizes.sum()) + 64 * len(idx) * 2 + 4096, dtype=torch.uint8, device=dev) if len(cuts) > 2 else None
+        metas, off, t_host = [], 0, 0.0
+        if len(cuts) == 2:
+            meta, used = self._stage(idx, 0)
+            d_blob = self._stage_bufs[0][:used + 8].to(dev, non_blocking=True)
+            metas.append(meta)
+            t_host = time.perf_counter() - t0
+        else:
+            from concurrent.futures import ThreadPoolExecutor
+            done = [torch.cuda.Event(), torch.cuda.Event()]
+            with ThreadPoolExecutor(1) as reader:
+                pending = reader.submit(self._stage, idx[cuts[0]:cuts[1]], 0)
+                for c in range(len(cuts) - 1):
+                    t1 = time.perf_counter()
+                    meta, used = pending.result()
+                    t_host += time.perf_counter() - t1          # time the device side had to wait for the file
+                    if off + used + 8 > d_blob.numel():         # spans carry the frame headers too; grow if the estimate was short
+                        bigger = torch.empty(off + used + 8 + (d_blob.numel() >> 2), dtype=torch.uint8, device=dev)
+                        bigger[:off].copy_(d_blob[:off])
+                        d_blob = bigger
+                    d_blob[off:off + used + 8].copy_(self._stage_bufs[c & 1][:used + 8], non_blocking=True)
+                    done[c & 1].record()
+                    meta["offset"] += off
+                    metas.append(meta)
+                    off += used
+                    if c + 2 < len(cuts):
+                        if c >= 1:
+                            done[(c + 1) & 1].synchronize()     # the copy out of that pinned buffer has finished
+                        pending = reader.submit(self._stage, idx[cuts[c + 1]:cuts[c + 2]], (c + 1) & 1)
+        t1 = time.perf_counter()
+        meta = np.concatenate(metas)
+        d_meta = torch.from_numpy(meta.view(np.uint8).reshape(-1)).to(dev)
+        lib = _lib.load()
+        stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        rc = lib.chc_xtc_decode(d_blob.data_ptr(), d_meta.data_ptr(), len(meta), self.n_atoms, out.data_ptr(), 0, self.device, stream)
+        if rc != 0:
+            raise ValueError("%s: XTC bit stream inconsistent with %d atoms (chc_xtc_decode returned %d)" % (self.path, self.n_atoms, rc))
+        self.last_timing = (t_host, time.perf_counter() - t1)   # (waiting for file -> pinned, rest of H2D + decode) seconds
+        return out
+
+    def _stage(self, idx, which: int):
+        """compressed streams of frames idx -> pinned buffer `which`; returns (frame table with buffer offsets, bytes used)"""
         meta = self._index[idx].copy()
         sizes = (meta["nbytes"].astype(np.int64) + 3) & ~3
         lo, hi = int(meta["offset"][0]), int(meta["offset"][-1] + sizes[-1])
         if hi - lo <= 1.25 * sizes.sum() + 4096:        # (nearly) consecutive frames: one span, headers and all
-            host = self._pinned(hi - lo + 8)
+            host = self._pinned(hi - lo + 8, which)
             self._pread(memoryview(host.numpy())[:hi - lo], lo)        # straight from the file into pinned memory
             meta["offset"] -= lo                        # file offsets are multiples of 4 (XDR), so these are too
             used = hi - lo
         else:
             starts = np.concatenate([[0], np.cumsum(sizes)[:-1]])
             used = int(sizes.sum())
-            host = self._pinned(used + 8)
+            host = self._pinned(used + 8, which)
             view = host.numpy()
             for src, n, dst in zip(meta["offset"], sizes, starts):
                 view[dst:dst + n] = self._mm[src:src + n]
             meta["offset"] = starts
         host.numpy()[used:used + 8] = 0
-        blob = host[:used + 8]
-        t1 = time.perf_counter()
-        d_blob = blob.to(dev, non_blocking=True)
-        d_meta = torch.from_numpy(meta.view(np.uint8).reshape(-1)).to(dev)
-        lib = _lib.load()
-        stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
-        rc = lib.chc_xtc_decode(d_blob.data_ptr(), d_meta.data_ptr(), len(idx), self.n_atoms, out.data_ptr(), 0, self.device, stream)
-        self.last_timing = (t1 - t0, time.perf_counter() - t1)     # (file -> pinned, H2D + decode) seconds
-        if rc != 0:
-            raise ValueError("%s: XTC bit stream inconsistent with %d atoms (chc_xtc_decode returned %d)" % (self.path, self.n_atoms, rc))
-        return out
+        return meta, used
 
     def _pread(self, dst: memoryview, offset: int, piece: int = 8 << 20, workers: int = 8) -> None:
         """fill dst from the file at offset; large spans as parallel preads (the page-cache copy of one thread, about
@@ -163,15 +209,16 @@ class XTCFile:
         finally:
             os.close(fd)
 
-    def _pinned(self, nbytes: int):
-        """a pinned staging buffer that is kept between reads (allocating pinned memory costs more than the decode)"""
+    def _pinned(self, nbytes: int, which: int = 0):
+        """pinned staging buffers kept between reads (allocating pinned memory costs more than the decode)"""
         import torch
-        buf = getattr(self, "_stage", None)
+        bufs = self.__dict__.setdefault("_stage_bufs", [None, None])
+        buf = bufs[which]
         if buf is None or buf.numel() < nbytes:
             if buf is not None:
                 torch.cuda.synchronize()                # an earlier asynchronous copy may still read the old buffer
             buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, pin_memory=True)
-            self._stage = buf
+            bufs[which] = buf
         return buf
 
     def read(self, beg: int = 0, end: int | None = None, stride: int = 1) -> np.ndarray:

@@ -43,6 +43,8 @@ def test_decoder_matches_oracle_on_every_stream_feature(tmp_path, wide):
             ints[:, 0] *= 300
         elif f % 3 == 0:
             ints = ints * np.array([60, 70, 80])       # ~2^22 per axis: a packed triple of about 67 bits
+        elif f % 3 == 1:
+            ints = ints // 16                          # compact box: packed triples of at most 52 bits (reciprocal division path)
         frames.append(ints)
     path = str(tmp_path / "r.xtc")
     _write_int_frames(path, frames, adapt=True)
@@ -55,6 +57,10 @@ def test_decoder_matches_oracle_on_every_stream_feature(tmp_path, wide):
     # strided and partial reads gather the right frames
     assert np.array_equal(x.read(3, 30, 4), want[3:31:4])
     assert np.array_equal(x.read(36, None, 1), want[36:])
+    # the pipelined read (file read of chunk k+1 under the decode of chunk k) is the same function
+    x.CHUNK_BYTES = 20000
+    assert np.array_equal(x.read(), want)
+    assert np.array_equal(x.read(1, 35, 3), want[1:36:3])
 
 
 def test_small_raw_frames_and_corrupt_streams(tmp_path):
