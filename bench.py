@@ -26,8 +26,8 @@ ITYPES = ["sb", "pc", "ps", "ts", "vdw", "hb", "hp"]
 WORKLOAD = "1tnf solvated HREMD synthetic: 20 states x 10k frames, ~7k protein atoms, all itypes, 1 GPU"
 METRIC = "contact frames/sec (all itypes)"
 # dram__bytes_read.sum + dram__bytes_write.sum per frame of this workload, from the committed ncu --set full capture
-# (profiles/r01_v3_ncu_summary.txt, 11 840 frames per launch): pair kernel 1.093 GB + 5 MB, streaming kernel 0.935 GB + 1.012 GB
-NCU_DRAM_BYTES_PER_FRAME = {"pair_frames_kernel": (1.092721e9 + 5.219e6) / 11840, "bin_frames_kernel": (934.828544e6 + 1.012439e9) / 11840}
+# (profiles/r01_v4_ncu_summary.txt, 11 840 frames per launch): pair kernel 0.923 GB + 5 MB, streaming kernel 0.931 GB + 0.862 GB
+NCU_DRAM_BYTES_PER_FRAME = {"pair_frames_kernel": (922.934528e6 + 5.139968e6) / 11840, "bin_frames_kernel": (931.195136e6 + 862.322432e6) / 11840}
 
 
 def make_topology(copies=4):
@@ -278,7 +278,7 @@ def main():
                              "kernel_share_of_step": st["pair_ms_total"] / ms},
                 "roofline_stream": {"bound": "hbm", "achieved": stream_gbs, "peak": peak, "unit": "GB/s", "frac": stream_gbs / peak,
                                     "traffic": NCU_DRAM_BYTES_PER_FRAME["bin_frames_kernel"] * frames_per_chunk if N == 6516 else None,
-                                    "traffic_note": "12 B/atom read once (no re-reads) + the binned record written once (85.5 KB per frame)",
+                                    "traffic_note": "12 B/atom read once (no re-reads) + the binned record written once (83 KB per frame, 73 KB of it used)",
                                     "kernel": "bin_frames_kernel", "avg_launch_ms": bin_ms,
                                     "algorithmic_bytes_per_launch": bytes_per_launch,
                                     "kernel_share_of_step": st["bin_ms_total"] / ms},
