@@ -151,7 +151,7 @@ def main():
     import torch.distributed as dist
     from chacra_b200 import compile_topology
     from chacra_b200.engine import ContactEngine
-    from chacra_b200.sharding import merge_count_tables
+    from chacra_b200.sharding import bind_to_gpu_numa_node, merge_count_tables
     from chacra_b200.synthetic import FrameGenerator
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -159,6 +159,7 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa = bind_to_gpu_numa_node(local) if world > 1 and not os.environ.get("CHACRA_NO_NUMA_BIND") else {"bound": False, "reason": "single rank"}
     # stdout carries exactly one JSON line: anything libraries print there (NCCL's version banner ...) goes to stderr
     sys.stdout.flush()
     saved_stdout = os.dup(1)
@@ -283,7 +284,8 @@ def main():
                                     "algorithmic_bytes_per_launch": bytes_per_launch,
                                     "kernel_share_of_step": st["bin_ms_total"] / ms},
                 "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": int(S * F * N * 12) * world,
-                        "d2h_bytes_per_step": int(eng.counts_tensor.numel() * 4) * world, "steps": args.e2e_steps},
+                        "d2h_bytes_per_step": int(eng.counts_tensor.numel() * 4) * world, "steps": args.e2e_steps,
+                        "host_numa": numa},
                 "gpu_launches": int(launches), "clocks": clocks,
                 "engine": {k: st[k] for k in ("path", "smem_bytes", "threads", "grid", "bin_smem_bytes", "bin_grid", "chunk_frames", "record_bytes")}}
         if world == 1 and not args.no_cpu_baseline:

@@ -11,6 +11,7 @@
 #include "pair_kernel.cuh"
 #include "xtc_decode.cuh"
 #include "pca_perm.cuh"
+#include "dcd_unpack.cuh"
 
 #define PAIR_THREADS 1024
 #define SMEM_LIMIT (227 * 1024)
@@ -602,6 +603,21 @@ extern "C" int chc_set_timing(chc_ctx* ctx, int on) {
     ctx->timing = on != 0;
     if (on) { ctx->st.pair_ms_total = 0.0; ctx->st.bin_ms_total = 0.0; ctx->st.timed_chunks = 0; }
     return CHC_OK;
+}
+
+// ---- DCD frames (X1) ----------------------------------------------------------------------------------------------
+extern "C" int chc_dcd_unpack(const void* d_raw, int64_t first, int64_t pitch, int64_t n_frames, int32_t n_atoms, int big_endian,
+                              float* d_xyz, int64_t frame_stride, int device, void* stream_) {
+    if (n_frames == 0) return CHC_OK;
+    if (!d_raw || !d_xyz || n_frames < 0 || n_frames > 0x7fffffff || n_atoms < 1 || first < 0 || pitch < 0) return CHC_E_INVALID;
+    if ((((uintptr_t)d_raw + (uintptr_t)first) & 3) != 0 || (pitch & 3) != 0) return CHC_E_INVALID;
+    if (cudaSetDevice(device) != cudaSuccess) return CHC_E_CUDA;
+    if (frame_stride == 0) frame_stride = 3 * (int64_t)n_atoms;
+    const int ntiles = (n_atoms + DCD_TILE - 1) / DCD_TILE;
+    const dim3 grid((unsigned)std::min(ntiles, 64), (unsigned)std::min<int64_t>(n_frames, 65535));
+    dcd_unpack_kernel<<<grid, DCD_TILE, 0, (cudaStream_t)stream_>>>(static_cast<const unsigned char*>(d_raw), first, pitch, (int)n_frames,
+                                                                     n_atoms, big_endian ? 1 : 0, d_xyz, frame_stride);
+    return cudaGetLastError() == cudaSuccess ? CHC_OK : CHC_E_CUDA;
 }
 
 // ---- ContactPCA permutation test (X4) -------------------------------------------------------------------------

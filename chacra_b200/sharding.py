@@ -47,3 +47,37 @@ def merge_count_tables(counts, group=None):
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.all_reduce(counts, op=dist.ReduceOp.SUM, group=group)
     return counts
+
+
+def bind_to_gpu_numa_node(device: int) -> dict:
+    """Pin this process to the CPUs next to ``cuda:device`` (sysfs ``local_cpulist`` of the GPU's PCI function) so that
+    pinned host buffers allocated afterwards land on that NUMA node: with one rank per GPU every rank then feeds its
+    GPU from local memory instead of all ranks pulling from the node the launcher happened to start on.
+    Returns what was done; a no-op (reason given) when the topology is not exposed or has one node."""
+    import os
+    info = {"bound": False}
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(device)
+        bdf = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        base = "/sys/bus/pci/devices/" + bdf
+        node = int(open(base + "/numa_node").read().strip())
+        info.update(pci=bdf, node=node)
+        if node < 0:
+            info["reason"] = "numa_node not reported"
+            return info
+        cpus = set()
+        for part in open(base + "/local_cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        allowed = os.sched_getaffinity(0)
+        use = cpus & allowed
+        if not use or use == allowed:
+            info["reason"] = "no narrower CPU set available (%d local, %d allowed)" % (len(cpus), len(allowed))
+            return info
+        os.sched_setaffinity(0, use)
+        info.update(bound=True, cpus=len(use))
+    except (OSError, ValueError, AttributeError, RuntimeError, AssertionError) as exc:
+        info["reason"] = "%s: %s" % (type(exc).__name__, exc)
+    return info
+

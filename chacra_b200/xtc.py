@@ -19,6 +19,7 @@ import time
 import numpy as np
 
 from . import _lib
+from ._hostio import FileStager
 
 XTC_MAGIC = 1995
 _HEADER = 52                      # magic, natoms, step, time, box[9]
@@ -43,7 +44,7 @@ def _sizeofints(sizes) -> int:
     return max(prod.bit_length(), 1)
 
 
-class XTCFile:
+class XTCFile(FileStager):
     """Frame index of an XTC file + device decode.  ``read`` returns host float32 [F][N][3] (like the other readers),
     ``read_device`` a CUDA tensor that ``ContactEngine.submit`` takes without another copy."""
 
@@ -185,41 +186,6 @@ class XTCFile:
             meta["offset"] = starts
         host.numpy()[used:used + 8] = 0
         return meta, used
-
-    def _pread(self, dst: memoryview, offset: int, piece: int = 8 << 20, workers: int = 8) -> None:
-        """fill dst from the file at offset; large spans as parallel preads (the page-cache copy of one thread, about
-        6 GB/s, is otherwise the slowest stage of the XTC path)"""
-        fd = os.open(self.path, os.O_RDONLY)
-        try:
-            def one(beg):
-                end = min(beg + piece, len(dst))
-                while beg < end:
-                    got = os.preadv(fd, [dst[beg:end]], offset + beg)
-                    if got <= 0:
-                        raise ValueError("%s: short read" % self.path)
-                    beg += got
-            starts = range(0, len(dst), piece)
-            if len(starts) <= 1:
-                for b in starts:
-                    one(b)
-            else:
-                from concurrent.futures import ThreadPoolExecutor
-                with ThreadPoolExecutor(min(workers, len(starts), os.cpu_count() or 1)) as pool:
-                    list(pool.map(one, starts))
-        finally:
-            os.close(fd)
-
-    def _pinned(self, nbytes: int, which: int = 0):
-        """pinned staging buffers kept between reads (allocating pinned memory costs more than the decode)"""
-        import torch
-        bufs = self.__dict__.setdefault("_stage_bufs", [None, None])
-        buf = bufs[which]
-        if buf is None or buf.numel() < nbytes:
-            if buf is not None:
-                torch.cuda.synchronize()                # an earlier asynchronous copy may still read the old buffer
-            buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, pin_memory=True)
-            bufs[which] = buf
-        return buf
 
     def read(self, beg: int = 0, end: int | None = None, stride: int = 1) -> np.ndarray:
         return self.read_device(beg, end, stride).cpu().numpy()

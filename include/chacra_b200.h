@@ -230,6 +230,14 @@ typedef struct chc_xtc_frame {
 int chc_xtc_decode(const void* d_blob, const chc_xtc_frame* d_meta, int64_t n_frames, int32_t n_atoms, float* d_xyz,
                    int64_t frame_stride, int device, void* stream);
 
+/* Raw DCD frames -> interleaved coordinates (replaces VMD's dcd molfile plugin behind load_traj,
+ * contact_calc/contact_utils.py:89-116).  d_raw: DEVICE copy of file bytes; the x record payload of frame k starts at
+ * d_raw + first_x_offset + k*frame_pitch (4-byte aligned), y and z follow at +(4*n_atoms+8) bytes each, as in the file.
+ * big_endian: the file's byte order differs from the device's.  d_xyz: DEVICE float32, frame k at k*frame_stride floats
+ * (0 = 3*n_atoms).  Asynchronous on `stream`. */
+int chc_dcd_unpack(const void* d_raw, int64_t first_x_offset, int64_t frame_pitch, int64_t n_frames, int32_t n_atoms,
+                   int big_endian, float* d_xyz, int64_t frame_stride, int device, void* stream);
+
 /* ContactPCA permutation test (replaces run_permuted_pca + de_correlate,
  * chacra/ContactFrequencies.py:631-656, called from ContactPCA.permuted_pca :910-964).
  * d_vals: DEVICE float64 [n_samples][n_features] row major (the contact-frequency table, states x contacts),
