@@ -8,6 +8,8 @@ What stays on the host: argument handling, the one-off topology compilation (the
 from __future__ import annotations
 
 import math
+import os
+import time
 import sys
 
 import numpy as np
@@ -64,6 +66,7 @@ def compute_contacts(top, traj, output, itypes, geom_criterion_values, cores, be
         fd.write(header_lines(total_frames, beg, end, stride, itypes, distout))
         writer = ContactWriter(fd, labels, beg, stride, distout, TRAJ_FRAG_SIZE)
         done = 0                                         # selected frames processed so far
+        stage = [0.0, 0.0, 0.0]                          # seconds: trajectory input, contacts + drain, TSV text
         per_frame = None                                 # measured records per frame
         while done < total_frames:
             if per_frame is None:
@@ -72,15 +75,22 @@ def compute_contacts(top, traj, output, itypes, geom_criterion_values, cores, be
                 room = int(0.5 * _RECORD_CAPACITY / max(per_frame, 1.0))
                 n = min(max(TRAJ_FRAG_SIZE, room // TRAJ_FRAG_SIZE * TRAJ_FRAG_SIZE), total_frames - done)
             first = beg + done * stride
-            # XTC frames are decoded on the device and stay there; the other readers hand host arrays to the staging path
+            # DCD and XTC frames are unpacked on the device and stay there; other readers hand host arrays to the staging path
             reader = getattr(trj, "read_device", trj.read)
+            t0 = time.perf_counter()
             frames = reader(first, min(first + (n - 1) * stride, end), stride)
+            t1 = time.perf_counter()
             eng.submit(frames, 0, done)
             eng.synchronize()
-            rec = eng.drain_contacts()
+            rec = eng.drain_contacts(copy=False)          # reordered in place by the writer, gone before the next drain
+            t2 = time.perf_counter()
             writer.write(rec)
+            t3 = time.perf_counter()
+            stage[0] += t1 - t0; stage[1] += t2 - t1; stage[2] += t3 - t2
             per_frame = max(per_frame or 0.0, len(rec) / float(len(frames)))
             done += len(frames)
+    if os.environ.get("CHACRA_TIMING"):
+        print("stages: trajectory input %.3f s, contacts + drain %.3f s, TSV text %.3f s" % tuple(stage), file=sys.stderr)
     if frequency_output:
         from .frequencies import ALL_FREQ_ITYPES, counts_to_table, write_frequency_table
         table = counts_to_table(topo.residue_label, eng.counts(0))

@@ -12,6 +12,7 @@
 #include "xtc_decode.cuh"
 #include "pca_perm.cuh"
 #include "dcd_unpack.cuh"
+#include "tsv_writer.h"
 
 #define PAIR_THREADS 1024
 #define SMEM_LIMIT (227 * 1024)
@@ -603,6 +604,24 @@ extern "C" int chc_set_timing(chc_ctx* ctx, int on) {
     ctx->timing = on != 0;
     if (on) { ctx->st.pair_ms_total = 0.0; ctx->st.bin_ms_total = 0.0; ctx->st.timed_chunks = 0; }
     return CHC_OK;
+}
+
+// ---- contact-list TSV (A13), host threads ------------------------------------------------------------------------
+extern "C" int64_t chc_write_contacts_tsv(int fd, chc_contact* rec, int64_t n, const char* label_text, const int64_t* label_off,
+                                          const int32_t* label_rank, int32_t n_atoms, int32_t ranks_unique, const char* itype_text,
+                                          const int32_t* itype_off, const int32_t* block_rank, int32_t n_itypes, int64_t beg,
+                                          int64_t stride, int32_t distout, int32_t n_threads) {
+    static_assert(sizeof(tsvw::Rec) == sizeof(chc_contact), "record layout");
+    tsvw::Tables T{label_text, label_off, label_rank, n_atoms, ranks_unique != 0, itype_text, itype_off, block_rank, n_itypes,
+                   (long long)beg, (long long)stride, distout != 0};
+    const int64_t r = tsvw::write_contacts(fd, reinterpret_cast<tsvw::Rec*>(rec), n, T, n_threads);
+    return r == -1 ? CHC_E_INVALID : (r == -2 ? CHC_E_IO : (r == -3 ? CHC_E_NOMEM : r));
+}
+
+extern "C" int chc_format_fixed3(float value, char* out32) {
+    char* e = tsvw::put_fixed3(out32, value);
+    *e = 0;
+    return (int)(e - out32);
 }
 
 // ---- DCD frames (X1) ----------------------------------------------------------------------------------------------

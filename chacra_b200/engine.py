@@ -188,15 +188,21 @@ class ContactEngine:
     def reset_counts(self):
         self._check(self.lib.chc_reset_counts(self._ctx, self._stream()))
 
-    def drain_contacts(self) -> np.ndarray:
-        buf = np.empty(self.contact_capacity, CONTACT_DTYPE)
+    def drain_contacts(self, copy: bool = True) -> np.ndarray:
+        """Records emitted since the last drain.  They land in a pinned host buffer the engine keeps; ``copy=False``
+        returns a view of it that is valid until the next drain (the streaming TSV path uses that)."""
+        if getattr(self, "_drain_buf", None) is None:
+            pinned = self._torch.empty(self.contact_capacity * CONTACT_DTYPE.itemsize, dtype=self._torch.uint8, pin_memory=True)
+            self._drain_pin = pinned
+            self._drain_buf = pinned.numpy().view(CONTACT_DTYPE)
+        buf = self._drain_buf
         n = C.c_int64(0)
         self._check(self.lib.chc_drain_contacts(self._ctx, buf.ctypes.data, self.contact_capacity, C.byref(n), self._stream()))
         st = self.stats()
         if st["contacts_dropped"]:
             raise ChacraError("contact buffer overflow: %d records dropped; raise contact_capacity or submit fewer frames "
                               "between drains" % st["contacts_dropped"])
-        return buf[:n.value].copy()
+        return buf[:n.value].copy() if copy else buf[:n.value]
 
     def drain_near(self):
         buf = np.empty(self.near_capacity, NEAR_DTYPE)

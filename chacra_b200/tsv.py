@@ -14,9 +14,12 @@ Input is the binary record array drained from the device (``engine.CONTACT_DTYPE
 """
 from __future__ import annotations
 
+import os
+
 import numpy as np
 
-from .engine import ITYPE_NAMES
+from . import _lib
+from .engine import CONTACT_DTYPE, ITYPE_NAMES
 
 # rank of every record itype inside a frame (compute order of compute_contacts.py:85-101; hbonds.py emits the
 # hydrogen bonds first and the water bridges after them)
@@ -34,60 +37,58 @@ def header_lines(total_frames: int, beg: int, end: int, stride: int, itypes, dis
 
 
 class ContactWriter:
-    def __init__(self, fd, atom_labels, beg: int, stride: int, distout: bool, fragment_frames: int = 100):
+    """Orders, de-duplicates and formats drained contact records through the native writer of libchacra_b200
+    (``chc_write_contacts_tsv``, csrc/tsv_writer.h: host threads, straight to the file descriptor)."""
+
+    def __init__(self, fd, atom_labels, beg: int, stride: int, distout: bool, fragment_frames: int = 100, threads: int | None = None):
         self.fd = fd
-        self.labels = np.asarray(atom_labels, dtype=object)
+        labels = [str(x) for x in atom_labels]
         # atoms with identical label strings share a rank, so that line identity is decided on integers
-        uniq, inv = np.unique(self.labels.astype(str), return_inverse=True)
-        self.label_rank = inv.astype(np.int64)          # order of ranks == Python string order of the labels
+        uniq, inv = np.unique(np.asarray(labels, dtype=str), return_inverse=True)
+        self.label_rank = np.ascontiguousarray(inv, dtype=np.int32)     # order of ranks == Python string order of the labels
+        self.ranks_unique = int(len(uniq) == len(labels))
+        enc = [x.encode() for x in labels]
+        self.label_off = np.zeros(len(enc) + 1, np.int64)
+        np.cumsum([len(x) for x in enc], out=self.label_off[1:])
+        self.label_text = b"".join(enc)
+        names = [x.encode() for x in ITYPE_NAMES]
+        self.itype_off = np.zeros(len(names) + 1, np.int32)
+        np.cumsum([len(x) for x in names], out=self.itype_off[1:])
+        self.itype_text = b"".join(names)
+        self.block_rank = np.ascontiguousarray(BLOCK_RANK, dtype=np.int32)
         self.beg, self.stride, self.distout, self.frag = int(beg), int(stride), bool(distout), int(fragment_frames)
+        self.threads = int(threads or min(32, os.cpu_count() or 1))
         self.lines_written = 0
+        self.lib = _lib.load()
 
     def write(self, rec: np.ndarray) -> int:
-        """Write the records of a set of WHOLE fragments (any order).  Returns the number of lines."""
+        """Write the records of a set of WHOLE frames (any order; the array is reordered in place).  Returns the number
+        of lines."""
         if len(rec) == 0:
             return 0
-        a1, a2 = rec["atom1"].astype(np.int64), rec["atom2"].astype(np.int64)
-        w1, w2 = rec["water1"].astype(np.int64), rec["water2"].astype(np.int64)
-        swap = self.label_rank[a2] < self.label_rank[a1]                 # "if interaction[3] < interaction[2]"
-        a1, a2 = np.where(swap, a2, a1), np.where(swap, a1, a2)
-        two = w2 >= 0
-        w1, w2 = np.where(swap & two, w2, w1), np.where(swap & two, w1, w2)
-        frame = rec["frame"].astype(np.int64)
-        it = rec["itype"].astype(np.int64)
-        order = np.lexsort((w2, w1, a2, a1, BLOCK_RANK[it], frame))
-        frame, it, a1, a2, w1, w2 = frame[order], it[order], a1[order], a2[order], w1[order], w2[order]
-        dist = rec["distance"][order]
-        dtxt = np.array(["%.3f" % d for d in dist.tolist()], dtype=object) if self.distout else None
-        # per-fragment de-duplication of identical text lines (label ranks + the printed distance decide identity)
-        lr1, lr2 = self.label_rank[a1], self.label_rank[a2]
-        lw1 = np.where(w1 >= 0, self.label_rank[np.maximum(w1, 0)], -1)
-        lw2 = np.where(w2 >= 0, self.label_rank[np.maximum(w2, 0)], -1)
-        seen, out = set(), []
-        lab = self.labels
-        names = ITYPE_NAMES
-        frag_of = frame // self.frag
-        cur_frag = -1
-        fr_l, it_l, a1_l, a2_l, w1_l, w2_l = frame.tolist(), it.tolist(), a1.tolist(), a2.tolist(), w1.tolist(), w2.tolist()
-        k1, k2, k3, k4 = lr1.tolist(), lr2.tolist(), lw1.tolist(), lw2.tolist()
-        fg = frag_of.tolist()
-        for n in range(len(fr_l)):
-            if fg[n] != cur_frag:
-                cur_frag, seen = fg[n], set()
-            key = (fr_l[n], it_l[n], k1[n], k2[n], k3[n], k4[n], dtxt[n] if dtxt is not None else None)
-            if key in seen:
-                continue
-            seen.add(key)
-            cols = [str(self.beg + fr_l[n] * self.stride), names[it_l[n]], lab[a1_l[n]], lab[a2_l[n]]]
-            if w1_l[n] >= 0:
-                cols.append(lab[w1_l[n]])
-                if w2_l[n] >= 0:
-                    cols.append(lab[w2_l[n]])
-            if dtxt is not None:
-                cols.append(dtxt[n])
-            out.append("\t".join(cols))
-        if out:
-            self.fd.write("\n".join(out))
-            self.fd.write("\n")
-        self.lines_written += len(out)
-        return len(out)
+        if not (isinstance(rec, np.ndarray) and rec.dtype == CONTACT_DTYPE and rec.flags.c_contiguous and rec.flags.writeable):
+            rec = np.array(rec, dtype=CONTACT_DTYPE, order="C")
+        try:
+            fileno = self.fd.fileno()
+        except (AttributeError, OSError):
+            fileno = None
+        if fileno is not None:
+            self.fd.flush()
+            n = self._native(fileno, rec)
+        else:                                            # in-memory text streams: through a temporary file
+            import tempfile
+            with tempfile.TemporaryFile() as tmp:
+                n = self._native(tmp.fileno(), rec)
+                tmp.seek(0)
+                self.fd.write(tmp.read().decode())
+        self.lines_written += n
+        return n
+
+    def _native(self, fileno: int, rec: np.ndarray) -> int:
+        n = self.lib.chc_write_contacts_tsv(fileno, rec.ctypes.data, len(rec), self.label_text, self.label_off.ctypes.data,
+                                            self.label_rank.ctypes.data, len(self.label_rank), self.ranks_unique, self.itype_text,
+                                            self.itype_off.ctypes.data, self.block_rank.ctypes.data, len(self.block_rank),
+                                            self.beg, self.stride, int(self.distout), self.threads)
+        if n < 0:
+            raise RuntimeError("chc_write_contacts_tsv failed (%d)" % n)
+        return int(n)

@@ -230,6 +230,21 @@ typedef struct chc_xtc_frame {
 int chc_xtc_decode(const void* d_blob, const chc_xtc_frame* d_meta, int64_t n_frames, int32_t n_atoms, float* d_xyz,
                    int64_t frame_stride, int device, void* stream);
 
+/* Contact-list TSV writer (host code, no GPU work; replaces contact_consumer, gc/contact_calc/compute_contacts.py:306-359).
+ * rec[n]: records from chc_drain_contacts covering WHOLE frames (reordered in place).  Labels: atom a's text is
+ * label_text[label_off[a] .. label_off[a+1]) ("chain:resname:resid:name"), label_rank[a] its position in string order
+ * (equal strings share a rank; ranks_unique = no two atoms share one).  itype_text / itype_off / block_rank: token and
+ * block position of every chc_itype.  Output line: frame*stride+beg, itype, atom_1, atom_2[, water_1[, water_2]][, "%.3f"
+ * distance], TAB separated; atoms ordered by label, identical lines once, frames ascending.  Writes to file descriptor
+ * fd with up to n_threads formatting threads.  Returns the number of lines, or CHC_E_INVALID / CHC_E_IO. */
+#define CHC_E_IO -6
+int64_t chc_write_contacts_tsv(int fd, chc_contact* rec, int64_t n, const char* label_text, const int64_t* label_off,
+                               const int32_t* label_rank, int32_t n_atoms, int32_t ranks_unique, const char* itype_text,
+                               const int32_t* itype_off, const int32_t* block_rank, int32_t n_itypes, int64_t beg,
+                               int64_t stride, int32_t distout, int32_t n_threads);
+/* printf("%.3f") of a float32 distance as the writer formats it (exposed for tests); returns the length */
+int chc_format_fixed3(float value, char* out32);
+
 /* Raw DCD frames -> interleaved coordinates (replaces VMD's dcd molfile plugin behind load_traj,
  * contact_calc/contact_utils.py:89-116).  d_raw: DEVICE copy of file bytes; the x record payload of frame k starts at
  * d_raw + first_x_offset + k*frame_pitch (4-byte aligned), y and z follow at +(4*n_atoms+8) bytes each, as in the file.

@@ -46,3 +46,64 @@ def test_duplicate_lines_dropped_per_fragment():
     fd = io.StringIO()
     w = ContactWriter(fd, LABELS, beg=0, stride=1, distout=True)
     assert w.write(_rec([(0, "vdw", 2, 3, -1, -1, 3.0), (0, "vdw", 6, 3, -1, -1, 3.2)])) == 2
+
+
+def _random_records(rng, n_atoms, frames, per_frame, dup_share=0.05):
+    n = frames * per_frame
+    r = np.zeros(n, CONTACT_DTYPE)
+    r["frame"] = rng.permutation(np.repeat(np.arange(frames) * 3 + 7, per_frame))      # any order, gaps between frames
+    r["itype"] = rng.integers(0, len(ITYPE_NAMES), n)
+    r["atom1"] = rng.integers(0, n_atoms, n)
+    r["atom2"] = rng.integers(0, n_atoms, n)
+    wb = np.isin(r["itype"], [ITYPE_NAMES.index(x) for x in ("wb", "lwb", "wb2", "lwb2")])
+    wb2 = np.isin(r["itype"], [ITYPE_NAMES.index(x) for x in ("wb2", "lwb2")])
+    r["water1"] = np.where(wb, rng.integers(0, n_atoms, n), -1)
+    r["water2"] = np.where(wb2, rng.integers(0, n_atoms, n), -1)
+    r["distance"] = (rng.integers(0, 1 << 16, n) / 4096.0).astype(np.float32)              # many ties at the third decimal
+    k = int(n * dup_share)
+    r[rng.integers(0, n, k)] = r[rng.integers(0, n, k)]                                  # exact duplicate records
+    return r
+
+
+def test_native_writer_equals_the_python_restatement(tmp_path):
+    import tsv_oracle
+    rng = np.random.default_rng(3)
+    for labels, distout, threads in [([("A:RES:%d:X%d" % (k // 3, k % 3)) for k in range(300)], True, 5),
+                                     ([("A:RES:%d:X%d" % (k // 3, k % 2)) for k in range(300)], False, 3),     # shared labels
+                                     ([("A:RES:%d:X%d" % (k // 3, k % 2)) for k in range(300)], True, 1),
+                                     (LABELS, True, 64)]:
+        rec = _random_records(rng, len(labels), 23, 400)
+        want = io.StringIO()
+        n_want = tsv_oracle.ContactWriterPy(want, labels, 100, 10, distout).write(rec.copy())
+        path = tmp_path / "out.tsv"
+        with open(path, "w") as fd:
+            fd.write("# header\n")
+            w = ContactWriter(fd, labels, 100, 10, distout, threads=threads)
+            n_got = w.write(rec)
+            fd.write("# trailer\n")                                                    # Python-level writes stay in order
+        text = open(path).read()
+        assert text == "# header\n" + want.getvalue() + "# trailer\n"
+        assert n_got == n_want == len(want.getvalue().splitlines()) and n_got < len(rec)
+
+
+def test_distance_text_is_printf_exact():
+    import ctypes as C
+    from chacra_b200 import _lib
+    lib = _lib.load()
+    buf = C.create_string_buffer(64)
+    rng = np.random.default_rng(9)
+    vals = np.concatenate([rng.random(20000).astype(np.float32) * 12, (rng.integers(0, 1 << 18, 20000) / 16.0).astype(np.float32),
+                           np.array([0, 0.0005, 0.0625, 0.1875, 0.3125, 1e-8, 1e-30, 3.9995, 123456.789, 1e9, 8388608.5, 1e-45], np.float32)])
+    for v in vals.tolist():
+        lib.chc_format_fixed3(C.c_float(v), buf)
+        assert buf.value.decode() == "%.3f" % v
+
+
+def test_bad_records_are_refused():
+    import pytest
+    fd = io.StringIO()
+    w = ContactWriter(fd, LABELS, 0, 1, True)
+    bad = _rec([(0, "vdw", 2, 99, -1, -1, 3.0)])
+    with pytest.raises(RuntimeError):
+        w.write(bad)
+    assert w.write(_rec([])) == 0 and fd.getvalue() == ""
