@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(CSRC, "libchacra_b200.so")
 SOURCES = ["chacra_b200.cu"]
-HEADERS = ["device_types.cuh", "bin_tma_kernel.cuh", "xtc_decode.cuh", "pca_perm.cuh", "dcd_unpack.cuh", "tsv_writer.h", "frame_kernel.cuh", "frame_phases.cuh", "bin_kernel.cuh", "pair_kernel.cuh", "water_phase.cuh",
+HEADERS = ["device_types.cuh", "bin_tma_kernel.cuh", "xtc_decode.cuh", "pca_perm.cuh", "dcd_unpack.cuh", "tsv_writer.h", "tsv_counts.h", "frame_kernel.cuh", "frame_phases.cuh", "bin_kernel.cuh", "pair_kernel.cuh", "water_phase.cuh",
            os.path.join("..", "..", "include", "chacra_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-fmad=false", "-std=c++17",
               "-shared", "-Xcompiler", "-fPIC"]
@@ -99,6 +99,11 @@ SYMBOLS = {
     "chc_write_contacts_tsv": (C.c_int64, [C.c_int, vp, C.c_int64, vp, vp, vp, C.c_int32, C.c_int32, vp, vp, vp, C.c_int32, C.c_int64,
                                          C.c_int64, C.c_int32, C.c_int32]),
     "chc_format_fixed3": (C.c_int, [C.c_float, vp]),
+    "chc_count_tsv": (C.c_int, [C.c_char_p, C.c_char_p, C.c_int32, C.c_int32, C.POINTER(vp)]),
+    "chc_tsv_counts_sizes": (None, [vp, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "chc_tsv_counts_get": (None, [vp, vp, vp, vp, vp, vp]),
+    "chc_tsv_counts_error": (C.c_char_p, [vp]),
+    "chc_tsv_counts_free": (None, [vp]),
     "chc_dcd_unpack": (C.c_int, [vp, C.c_int64, C.c_int64, C.c_int64, C.c_int32, C.c_int, vp, C.c_int64, C.c_int, vp]),
     "chc_permuted_pca": (C.c_int, [vp, C.c_int32, C.c_int32, C.c_int32, vp, vp, C.c_uint64, vp, vp, C.c_int, vp]),
 }

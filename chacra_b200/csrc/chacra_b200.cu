@@ -13,6 +13,7 @@
 #include "pca_perm.cuh"
 #include "dcd_unpack.cuh"
 #include "tsv_writer.h"
+#include "tsv_counts.h"
 
 #define PAIR_THREADS 1024
 #define SMEM_LIMIT (227 * 1024)
@@ -623,6 +624,58 @@ extern "C" int chc_format_fixed3(float value, char* out32) {
     *e = 0;
     return (int)(e - out32);
 }
+
+// ---- contact-list TSV -> residue-pair counts (F1-F3), host threads ---------------------------------------------------
+struct chc_tsv_counts { tsvc::Result R; };
+
+extern "C" int chc_count_tsv(const char* path, const char* itypes_csv, int32_t shipped, int32_t n_threads, chc_tsv_counts** out) {
+    if (!path || !out) return CHC_E_INVALID;
+    std::vector<std::string> keep;
+    if (itypes_csv && *itypes_csv) {
+        const char* p = itypes_csv;
+        while (true) {
+            const char* c = strchr(p, ',');
+            keep.emplace_back(p, c ? (size_t)(c - p) : strlen(p));
+            if (!c) break;
+            p = c + 1;
+        }
+    }
+    chc_tsv_counts* r = new (std::nothrow) chc_tsv_counts();
+    if (!r) return CHC_E_NOMEM;
+    int rc;
+    try { rc = tsvc::count_file(path, keep, shipped != 0, n_threads, r->R); }
+    catch (const std::bad_alloc&) { delete r; return CHC_E_NOMEM; }
+    *out = r;
+    return rc == tsvc::OK ? CHC_OK : rc == tsvc::E_OPEN ? CHC_E_IO : rc == tsvc::E_PARSE ? CHC_E_INVALID : CHC_E_ORDER;
+}
+
+extern "C" void chc_tsv_counts_sizes(const chc_tsv_counts* r, int64_t* n_residues, int64_t* n_pairs, int64_t* name_bytes, int64_t* total_frames) {
+    int64_t bytes = 0;
+    for (const std::string& s : r->R.residues) bytes += (int64_t)s.size();
+    if (n_residues) *n_residues = (int64_t)r->R.residues.size();
+    if (n_pairs) *n_pairs = (int64_t)r->R.count.size();
+    if (name_bytes) *name_bytes = bytes;
+    if (total_frames) *total_frames = r->R.total_frames;
+}
+
+extern "C" void chc_tsv_counts_get(const chc_tsv_counts* r, char* name_text, int64_t* name_off, int32_t* res1, int32_t* res2, int64_t* count) {
+    int64_t off = 0;
+    for (size_t k = 0; k < r->R.residues.size(); ++k) {
+        name_off[k] = off;
+        memcpy(name_text + off, r->R.residues[k].data(), r->R.residues[k].size());
+        off += (int64_t)r->R.residues[k].size();
+    }
+    name_off[r->R.residues.size()] = off;
+    const size_t n = r->R.count.size();
+    if (n) {
+        memcpy(res1, r->R.r1.data(), n * sizeof(int32_t));
+        memcpy(res2, r->R.r2.data(), n * sizeof(int32_t));
+        memcpy(count, r->R.count.data(), n * sizeof(int64_t));
+    }
+}
+
+extern "C" const char* chc_tsv_counts_error(const chc_tsv_counts* r) { return r ? r->R.error.c_str() : ""; }
+extern "C" void chc_tsv_counts_free(chc_tsv_counts* r) { delete r; }
 
 // ---- DCD frames (X1) ----------------------------------------------------------------------------------------------
 extern "C" int chc_dcd_unpack(const void* d_raw, int64_t first, int64_t pitch, int64_t n_frames, int32_t n_atoms, int big_endian,

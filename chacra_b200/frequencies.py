@@ -97,6 +97,40 @@ def intended_counts_tsv(lines, itypes=None, as_sets=False):
     return total_frames, (dict(per_pair) if as_sets else {k: len(v) for k, v in per_pair.items()})
 
 
+def native_counts(path: str, itypes=None, shipped: bool = True, threads: int | None = None):
+    """(total_frames, {(res1, res2): frame_count}) of a contact-list TSV FILE through the library's threaded reader
+    (``chc_count_tsv``, csrc/tsv_counts.h) -- the same table as ``shipped_counts`` / ``intended_counts_tsv``.  Returns
+    None when the file's frame numbers are not strictly increasing (then only the line-by-line readers apply)."""
+    import ctypes as C
+    import os
+    from . import _lib
+    lib = _lib.load()
+    handle = C.c_void_p()
+    csv = ",".join(itypes).encode() if itypes is not None else None
+    rc = lib.chc_count_tsv(os.fsencode(path), csv, int(bool(shipped)), int(threads or min(32, os.cpu_count() or 1)), C.byref(handle))
+    try:
+        if rc == -4:                                    # CHC_E_ORDER
+            return None
+        if rc == -1:
+            raise ParseError(lib.chc_tsv_counts_error(handle).decode() or "malformed contact file")
+        if rc != 0:
+            raise OSError("cannot read %s (%d)" % (path, rc))
+        nres, npair, nbytes, total = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int64()
+        lib.chc_tsv_counts_sizes(handle, C.byref(nres), C.byref(npair), C.byref(nbytes), C.byref(total))
+        text = np.zeros(max(nbytes.value, 1), np.uint8)
+        off = np.zeros(nres.value + 1, np.int64)
+        r1, r2 = np.zeros(max(npair.value, 1), np.int32), np.zeros(max(npair.value, 1), np.int32)
+        cnt = np.zeros(max(npair.value, 1), np.int64)
+        lib.chc_tsv_counts_get(handle, text.ctypes.data, off.ctypes.data, r1.ctypes.data, r2.ctypes.data, cnt.ctypes.data)
+    finally:
+        if handle:
+            lib.chc_tsv_counts_free(handle)
+    blob = text.tobytes()
+    names = [blob[off[k]:off[k + 1]].decode() for k in range(nres.value)]
+    n = npair.value
+    return int(total.value), {(names[a], names[b]): int(c) for a, b, c in zip(r1[:n].tolist(), r2[:n].tolist(), cnt[:n].tolist())}
+
+
 def counts_to_table(residue_label, counts: np.ndarray):
     """Device count table (upper triangle incl. diagonal, index = lo*R - lo*(lo-1)/2 + (hi-lo)) -> {(res1, res2): n}.
     ``residue_label`` is sorted as Python strings, so rank order is label order and res1 <= res2."""

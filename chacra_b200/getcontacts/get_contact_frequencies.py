@@ -45,6 +45,15 @@ def main(argv=None):
     reduce_ = fq.shipped_counts if args.semantics == "shipped" else fq.intended_counts_tsv
     per_input = []
     for fh in args.input_files:
+        name = getattr(fh, "name", None)
+        fast = None
+        if labels is None and isinstance(name, str) and os.path.isfile(name):
+            # a file on disk and no relabelling: the library's threaded reader (same table; None = not a file in frame order)
+            fast = fq.native_counts(name, itypes, shipped=args.semantics == "shipped")
+        if fast is not None:
+            fh.close()
+            per_input.append(fast)
+            continue
         frames, sets = reduce_(fh, itypes, as_sets=True)
         fh.close()
         if labels is not None:

@@ -245,6 +245,21 @@ int64_t chc_write_contacts_tsv(int fd, chc_contact* rec, int64_t n, const char* 
 /* printf("%.3f") of a float32 distance as the writer formats it (exposed for tests); returns the length */
 int chc_format_fixed3(float value, char* out32);
 
+/* Contact-list TSV -> residue-pair frame counts (host code; replaces the line loop of get_contact_frequencies.py:58-134 /
+ * contact_calc/transformations.py:70-150, 262-304, 446-470).  itypes_csv: comma-separated interaction types to count
+ * (NULL or "" = all lines).  shipped != 0 reproduces the reference reader's behaviour (first line of every new frame
+ * dropped, last frame never flushed); 0 counts every line.  Returns CHC_OK and a result handle, or
+ * CHC_E_IO (cannot read), CHC_E_INVALID (malformed line; chc_tsv_counts_error gives the reference's message), or
+ * CHC_E_ORDER (frame numbers not strictly increasing: not a file get_dynamic_contacts wrote; use a line-by-line reader). */
+typedef struct chc_tsv_counts chc_tsv_counts;
+int  chc_count_tsv(const char* path, const char* itypes_csv, int32_t shipped, int32_t n_threads, chc_tsv_counts** out);
+/* sizes: residues, pairs, bytes of all residue names together, total_frames of the header */
+void chc_tsv_counts_sizes(const chc_tsv_counts* r, int64_t* n_residues, int64_t* n_pairs, int64_t* name_bytes, int64_t* total_frames);
+/* name_text[name_off[k] .. name_off[k+1]) = residue k; pair p joins res1[p] <= res2[p] (string order), count[p] frames */
+void chc_tsv_counts_get(const chc_tsv_counts* r, char* name_text, int64_t* name_off, int32_t* res1, int32_t* res2, int64_t* count);
+const char* chc_tsv_counts_error(const chc_tsv_counts* r);
+void chc_tsv_counts_free(chc_tsv_counts* r);
+
 /* Raw DCD frames -> interleaved coordinates (replaces VMD's dcd molfile plugin behind load_traj,
  * contact_calc/contact_utils.py:89-116).  d_raw: DEVICE copy of file bytes; the x record payload of frame k starts at
  * d_raw + first_x_offset + k*frame_pitch (4-byte aligned), y and z follow at +(4*n_atoms+8) bytes each, as in the file.

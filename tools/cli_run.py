@@ -37,6 +37,21 @@ def main():
     dt = time.perf_counter() - t0
     size = os.path.getsize(out)
     lines = sum(1 for _ in open(out)) - 2
+    # second script of the flow: the frequency table from that file (threaded reader), and the same table from the device counts
+    from chacra_b200 import frequencies as fq
+    t0 = time.perf_counter()
+    total, shipped = fq.native_counts(out, fq.ALL_FREQ_ITYPES, shipped=True)
+    t_freq = time.perf_counter() - t0
+    _, intended = fq.native_counts(out, fq.ALL_FREQ_ITYPES, shipped=False)
+    sample = []
+    with open(out) as fh:
+        for k, line in enumerate(fh):
+            sample.append(line)
+            if k >= 400000:
+                break
+    t0 = time.perf_counter()
+    fq.shipped_counts(sample, fq.ALL_FREQ_ITYPES)
+    t_py = (time.perf_counter() - t0) / len(sample)
     # the Python line loop this writer replaced, on the records of 20 frames
     import tsv_oracle
     from chacra_b200 import compile_topology
@@ -45,12 +60,20 @@ def main():
     eng.submit(DCDFile(dcd).read_device(0, 19), 0, 0)
     eng.synchronize()
     rec = eng.drain_contacts()
+    # the count table the kernels accumulated for ALL frames == the table read back from the text they emitted
+    full = ContactEngine(compile_topology(atoms), bench.ITYPES, n_states=1)
+    full.submit(DCDFile(dcd).read_device(), 0, 0)
+    full.synchronize()
+    table = fq.counts_to_table(compile_topology(atoms).residue_label, full.counts(0))
+    assert table == intended and total == a.frames, (len(table), len(intended), total)
     t0 = time.perf_counter()
     tsv_oracle.ContactWriterPy(io.StringIO(), atoms.atom_labels(), 0, 1, True).write(rec)
     py = (time.perf_counter() - t0) / 20
     print("cli: %d frames x %d atoms -> %d lines, %.1f MB in %.2f s = %.0f frames/s (%.0f lines/frame, %.2f GB/s of text) | "
-          "Python line loop: %.1f ms per frame = %.0f frames/s" % (a.frames, atoms.n, lines, size / 1e6, dt, a.frames / dt, lines / a.frames,
-                                                                   size / dt / 1e9, py * 1e3, 1.0 / py))
+          "Python line loop: %.1f ms per frame = %.0f frames/s | frequency table from the file: %.2f s = %.1f M lines/s (Python reader: "
+          "%.2f M lines/s), %d pairs, equal to the device count table" % (
+              a.frames, atoms.n, lines, size / 1e6, dt, a.frames / dt, lines / a.frames, size / dt / 1e9, py * 1e3, 1.0 / py,
+              t_freq, lines / t_freq / 1e6, 1e-6 / t_py, len(shipped)))
     os.unlink(dcd); os.unlink(out)
 
 
