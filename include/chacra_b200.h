@@ -15,6 +15,12 @@
  *                            (external/getcontacts/contact_calc/transformations.py:70-150, :446-470;
  *                            driver external/getcontacts/get_contact_frequencies.py:58-134)
  *   chc_drain_near_cutoff <- new: the "within 1e-4 A / 1e-3 deg of a cutoff" side channel
+ *   chc_write_contacts_tsv <- contact_consumer()'s text (compute_contacts.py:306-359), host threads
+ *   chc_count_tsv         <- the contact-file reader of the frequency step (transformations.py:70-150), host threads
+ *   chc_submit_frames_indexed, chc_dcd_unpack, chc_xtc_decode, chc_permuted_pca
+ *                         <- the rows SURVEY 8(f) ranks next: replica -> state demultiplexing
+ *                            (chacra/trajectories/process_hremd.py:184-307), trajectory input (VMD molfile plugins behind
+ *                            contact_utils.py:89-116), ContactPCA's permutation test (chacra/ContactFrequencies.py:631-656)
  *
  * Conventions: plain C types only; 0 = success, negative = error (chc_last_error gives the text);
  * nothing throws or exits; the caller owns every buffer it passes in; the library owns what it
