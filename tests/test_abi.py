@@ -74,3 +74,14 @@ def test_device_entry_points_fail_loudly_without_a_gpu():
         run_permuted_pca(np.zeros((3, 4)), 2, seed=1)
     with pytest.raises(_lib.ChacraLibraryError):
         DCDFile(os.path.join(GOLDEN, "5xnd_trajectory.dcd")).read_device()
+
+
+def test_plain_c_client_links_and_runs(tmp_path):
+    """The header compiles as C99 and a C program drives the host-only entry points through the shared library."""
+    import subprocess
+    lib_dir = os.path.dirname(_lib.build())
+    exe = str(tmp_path / "abi_host")
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), os.path.join(ROOT, "tests", "c", "abi_host.c"),
+                    "-o", exe, "-L", lib_dir, "-lchacra_b200", "-Wl,-rpath," + lib_dir], check=True)
+    out = subprocess.run([exe, str(tmp_path / "scratch.tsv")], capture_output=True, text=True)
+    assert out.returncode == 0 and "abi_host ok" in out.stdout, out.stderr
