@@ -83,3 +83,59 @@ def demux_contacts(engine, replicas, replica_to_state_idx, save_interval: int = 
     for s in (range(n_rep) if states is None else states):
         engine.submit_indexed(pool, d_flat[s], state=int(s), first_index=first_index)
     return src
+
+
+def load_state_table(source, save_interval: int = 1, traj_len: int | None = None) -> np.ndarray:
+    """``replica_to_state_idx`` restricted to the saved cycles, from a femto ``samples.arrow`` stream file
+    (``load_femto_data``, process_hremd.py:24-36), a ``.npy`` table [cycles][replicas], or anything ``state_sources``
+    takes."""
+    if isinstance(source, (str, bytes)) or hasattr(source, "__fspath__"):
+        path = str(source)
+        if path.endswith(".npy"):
+            source = list(np.load(path))
+        else:
+            import pyarrow
+            with pyarrow.OSFile(path, "rb") as fh:
+                with pyarrow.RecordBatchStreamReader(fh) as reader:
+                    source = reader.read_all().to_pandas()
+    return _state_table(source, save_interval, traj_len)
+
+
+def demux_contacts_from_files(engine, replica_paths, replica_to_state_idx, save_interval: int = 1, window: int = 2000,
+                              fragment: int = 100):
+    """Contacts of every state straight off the replica trajectory files ``r0.dcd, r1.dcd, ...`` (replica order): no
+    state trajectory is written or held.  Frames are taken in windows of ``window`` frames (a multiple of the 100-frame
+    fragment, so the per-fragment hydrophobic sets see the same first frames as a whole-trajectory run); a window holds
+    R x window frames on the device.  Returns (n_frames, source table [S][F])."""
+    import torch
+    from .trajectory import open_trajectory
+    readers = [open_trajectory(p) for p in replica_paths]
+    n_rep = len(readers)
+    n_frames = min(r.n_frames for r in readers)
+    for r in readers:
+        if hasattr(r, "device"):
+            r.device = engine.device
+        if r.n_atoms != engine.topo.n_atoms:
+            raise ValueError("%s has %d atoms, the topology %d" % (getattr(r, "path", "trajectory"), r.n_atoms, engine.topo.n_atoms))
+    src = state_sources(replica_to_state_idx, save_interval, n_frames)
+    if src.shape[0] != n_rep:
+        raise ValueError("state table has %d states, %d replica files were given" % (src.shape[0], n_rep))
+    n_frames = src.shape[1]
+    window = max(fragment, window // fragment * fragment)
+    dev = torch.device("cuda", engine.device)
+    for f0 in range(0, n_frames, window):
+        f1 = min(f0 + window, n_frames)
+        w = f1 - f0
+        pool = torch.empty((n_rep, w, engine.topo.n_atoms, 3), dtype=torch.float32, device=dev)
+        for r, reader in enumerate(readers):
+            read = getattr(reader, "read_device", None)
+            if read is not None:
+                pool[r] = read(f0, f1 - 1)
+            else:
+                pool[r] = torch.from_numpy(np.ascontiguousarray(reader.read(f0, f1 - 1))).to(dev)
+        flat = torch.from_numpy(src[:, f0:f1] * w + np.arange(w, dtype=np.int64)[None, :]).to(dev)
+        flat_pool = pool.view(n_rep * w, engine.topo.n_atoms, 3)
+        for s in range(n_rep):
+            engine.submit_indexed(flat_pool, flat[s], state=s, first_index=f0)
+        engine.synchronize()                              # the pool is released before the next window is read
+    return n_frames, src

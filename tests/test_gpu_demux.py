@@ -1,6 +1,8 @@
 """Device-side replica -> state demultiplexing: reading frames through a source index gives exactly the
 counts of gathering the same frames first (what get_state_coordinates_from_replica does, process_hremd.py:184-230) --
 for the bulk-copy binning kernel, the register and gather variants, and the in-place pair path."""
+import os
+
 import numpy as np
 import pytest
 
@@ -76,3 +78,41 @@ def test_indexed_submission_validates(replicas):
     eng.synchronize()
     assert np.array_equal(three, 3 * eng.counts(0))
     eng.close()
+
+
+def test_replica_files_to_frequency_tables(tmp_path, replicas):
+    """r{j}.dcd + state table -> freqs_state_{i}.tsv (the extension script), against state trajectories gathered on the
+    host and pushed through the ordinary path; windows that cut the run at fragment boundaries change nothing."""
+    import torch
+    from test_gpu_dcd import write_dcd
+    from chacra_b200.demux import state_sources
+    from chacra_b200.frequencies import counts_to_table
+    from chacra_b200.getcontacts import get_replica_frequencies
+    import bench
+    topo, reps, table = replicas
+    n_rep, n_frames = reps.shape[:2]
+    host = reps.cpu().numpy()
+    paths = []
+    for r in range(n_rep):
+        paths.append(str(tmp_path / ("r%d.dcd" % r)))
+        write_dcd(paths[-1], host[r], "<", r % 2 == 0)
+    np.save(str(tmp_path / "states.npy"), np.repeat(table, 2, axis=0))          # two cycles per saved frame
+    top, _ = bench.make_topology(1)
+    out = str(tmp_path / "freqs")
+    get_replica_frequencies.main(argv=["--topology", top, "--replicas"] + paths + ["--state_data", str(tmp_path / "states.npy"),
+                                       "--save_interval", "2", "--output_dir", out, "--window", "100"])
+    src = state_sources(list(table))
+    ref = _engine(topo, n_rep)
+    for s in range(n_rep):
+        ref.submit(np.ascontiguousarray(host[src[s], np.arange(n_frames)]), s, 0)
+    ref.synchronize()
+    for s in range(n_rep):
+        want = counts_to_table(topo.residue_label, ref.counts(s))
+        rows = [l.rstrip("\n").split("\t") for l in open(os.path.join(out, "freqs_state_%d.tsv" % s)).read().splitlines()[2:]]
+        got = {(a, b): f for a, b, f in rows}
+        assert len(got) == len(want) > 50
+        for k, c in want.items():
+            assert got[k] == "%.3f" % (c / n_frames)
+    head = open(os.path.join(out, "freqs_state_0.tsv")).readline()
+    assert head.startswith("#\ttotal_frames:%d\t" % n_frames)
+    ref.close()
