@@ -62,7 +62,8 @@ __device__ __forceinline__ unsigned long long xtc_reorder(unsigned long long W, 
 
 // three mixed-radix digits (radices sz[1], sz[2] < 2^24 matter) from `nbits` bits (xdrfile receiveints); inv1, inv2 =
 // 1.0 / sz[1], 1.0 / sz[2]
-__device__ __forceinline__ void xtc_ints(XtcBits& B, int nbits, const unsigned sz[3], double inv1, double inv2, int out[3]) {
+__device__ __forceinline__ void xtc_ints(XtcBits& B, int nbits, unsigned sz1, unsigned sz2, double inv1, double inv2, int out[3]) {
+    const unsigned sz[3] = {0u, sz1, sz2};
     if (nbits <= 64) {
         unsigned long long W;
         if (nbits <= 32) W = B.get(nbits);
@@ -117,69 +118,86 @@ xtc_decode_kernel(const unsigned* __restrict__ blob, const XtcFrameMeta* __restr
         if (smallidx < XTC_FIRSTIDX || smallidx > XTC_LASTIDX) { atomicOr(status, 1u); continue; }
         int smaller = xtc_magicints[max(XTC_FIRSTIDX, smallidx - 1)] / 2;
         int smallnum = xtc_magicints[smallidx] / 2;
-        unsigned sizesmall[3];
-        sizesmall[0] = sizesmall[1] = sizesmall[2] = (unsigned)xtc_magicints[smallidx];
         const double inv1 = 1.0 / (double)sizeint[1], inv2 = 1.0 / (double)sizeint[2];
         double invs = inv_magic[smallidx];
         XtcBits B{src, 0ull, 0};
         const unsigned* end = src + ((m.nbytes + 3) >> 2) + 2;
-        int i = 0, run = 0;
+        // One atom per loop iteration, whichever kind it is (a "large" atom or one small difference of a run), so that the
+        // 32 frames of a warp, each somewhere else in its own stream, stay on the same instructions.
+        int i = 0, run = 0;            // atoms written; length of the last announced run (in integers, a multiple of 3)
+        int remaining = 0, pend = 0;   // small atoms still to come in this run; radix step to apply when it ends
+        bool first_small = false;      // the next small atom is the first of its run (stored swapped with the large one)
+        int prev[3] = {0, 0, 0};
+        unsigned ssmall = (unsigned)xtc_magicints[smallidx];
         bool bad = false;
         while (i < n_atoms) {
-            int cur[3];
-            if (m.bitsize == 0) {
+            const bool small = remaining > 0;
+            int v[3];
+            if (!small && m.bitsize == 0) {
 #pragma unroll
-                for (int k = 0; k < 3; ++k) cur[k] = (int)B.get(m.bitsizeint[k]);
+                for (int k = 0; k < 3; ++k) v[k] = (int)B.get(m.bitsizeint[k]);
             } else {
-                xtc_ints(B, m.bitsize, sizeint, inv1, inv2, cur);
+                xtc_ints(B, small ? smallidx : m.bitsize, small ? ssmall : sizeint[1], small ? ssmall : sizeint[2],
+                         small ? invs : inv1, small ? invs : inv2, v);
             }
+            bool step = false;         // a run (or a lone large atom) has just ended: the small radix may move
+            if (small) {
 #pragma unroll
-            for (int k = 0; k < 3; ++k) cur[k] += m.minint[k];
-            ++i;
-            int is_smaller = 0;
-            if (B.get(1)) {
-                run = (int)B.get(5);
-                is_smaller = run % 3;
-                run -= is_smaller;
-                --is_smaller;
-            }
-            if (i + run / 3 > n_atoms || B.w > end) { bad = true; break; }
-            if (run > 0) {
-                int prev[3] = {cur[0], cur[1], cur[2]};
-                for (int k = 0; k < run; k += 3) {
-                    int d[3];
-                    xtc_ints(B, smallidx, sizesmall, invs, invs, d);
+                for (int c = 0; c < 3; ++c) v[c] += prev[c] - smallnum;
+                if (first_small) {     // the first two atoms of a run are stored in swapped order (water: H O H)
 #pragma unroll
-                    for (int c = 0; c < 3; ++c) d[c] += prev[c] - smallnum;
-                    ++i;
-                    if (k == 0) {       // the first two atoms of a run are stored in swapped order (water: H O H)
-#pragma unroll
-                        for (int c = 0; c < 3; ++c) {
-                            out[3 * (i - 2) + c] = ((float)d[c] * inv) * 10.0f;
-                            out[3 * (i - 1) + c] = ((float)prev[c] * inv) * 10.0f;
-                        }
-                    } else {
-#pragma unroll
-                        for (int c = 0; c < 3; ++c) out[3 * (i - 1) + c] = ((float)d[c] * inv) * 10.0f;
+                    for (int c = 0; c < 3; ++c) {
+                        out[3 * i + c] = ((float)v[c] * inv) * 10.0f;
+                        out[3 * (i + 1) + c] = ((float)prev[c] * inv) * 10.0f;
                     }
+                    i += 2;
+                    first_small = false;
+                } else {
 #pragma unroll
-                    for (int c = 0; c < 3; ++c) prev[c] = d[c];
+                    for (int c = 0; c < 3; ++c) out[3 * i + c] = ((float)v[c] * inv) * 10.0f;
+                    ++i;
                 }
+#pragma unroll
+                for (int c = 0; c < 3; ++c) prev[c] = v[c];
+                step = --remaining == 0;
             } else {
 #pragma unroll
-                for (int c = 0; c < 3; ++c) out[3 * (i - 1) + c] = ((float)cur[c] * inv) * 10.0f;
+                for (int k = 0; k < 3; ++k) v[k] += m.minint[k];
+                int is_smaller = 0;
+                if (B.get(1)) {
+                    run = (int)B.get(5);
+                    is_smaller = run % 3;
+                    run -= is_smaller;
+                    --is_smaller;
+                }
+                if (i + 1 + run / 3 > n_atoms || B.w > end) { bad = true; break; }
+                pend = is_smaller;
+                if (run > 0) {
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) prev[c] = v[c];
+                    remaining = run / 3;
+                    first_small = true;
+                } else {
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) out[3 * i + c] = ((float)v[c] * inv) * 10.0f;
+                    ++i;
+                    step = true;
+                }
             }
-            smallidx += is_smaller;
-            if (smallidx < XTC_FIRSTIDX || smallidx > XTC_LASTIDX) { bad = true; break; }
-            if (is_smaller < 0) {
-                smallnum = smaller;
-                smaller = smallidx > XTC_FIRSTIDX ? xtc_magicints[smallidx - 1] / 2 : 0;
-            } else if (is_smaller > 0) {
-                smaller = smallnum;
-                smallnum = xtc_magicints[smallidx] / 2;
+            if (step && pend != 0) {
+                smallidx += pend;
+                if (smallidx < XTC_FIRSTIDX || smallidx > XTC_LASTIDX) { bad = true; break; }
+                if (pend < 0) {
+                    smallnum = smaller;
+                    smaller = smallidx > XTC_FIRSTIDX ? xtc_magicints[smallidx - 1] / 2 : 0;
+                } else {
+                    smaller = smallnum;
+                    smallnum = xtc_magicints[smallidx] / 2;
+                }
+                ssmall = (unsigned)xtc_magicints[smallidx];
+                invs = inv_magic[smallidx];
+                pend = 0;
             }
-            sizesmall[0] = sizesmall[1] = sizesmall[2] = (unsigned)xtc_magicints[smallidx];
-            invs = inv_magic[smallidx];
         }
         if (bad) atomicOr(status, 1u);
     }
