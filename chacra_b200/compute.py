@@ -24,7 +24,8 @@ _RECORD_CAPACITY = 1 << 23
 
 
 def compute_contacts(top, traj, output, itypes, geom_criterion_values, cores, beg, end, stride, distout,
-                     ligand_sele, solv_sele, lipid_sele, sele1, sele2, device=0, frequency_output=None):
+                     ligand_sele, solv_sele, lipid_sele, sele1, sele2, device=0, frequency_output=None,
+                     count_output=None):
     """Compute the contact list of ``traj`` and write it to ``output`` (contact-list TSV).
 
     ``cores`` is accepted for interface compatibility (the reference uses it as the number of VMD worker
@@ -91,10 +92,14 @@ def compute_contacts(top, traj, output, itypes, geom_criterion_values, cores, be
             done += len(frames)
     if os.environ.get("CHACRA_TIMING"):
         print("stages: trajectory input %.3f s, contacts + drain %.3f s, TSV text %.3f s" % tuple(stage), file=sys.stderr)
-    if frequency_output:
-        from .frequencies import ALL_FREQ_ITYPES, counts_to_table, write_frequency_table
+    if frequency_output or count_output:
+        from .frequencies import ALL_FREQ_ITYPES, counts_to_table, write_count_table, write_frequency_table
         table = counts_to_table(topo.residue_label, eng.counts(0))
-        with open(frequency_output, "w") as fd:
-            write_frequency_table(fd, total_frames, ALL_FREQ_ITYPES,
-                                  {k: (c, float(c) / total_frames) for k, c in table.items()})
+        if frequency_output:
+            with open(frequency_output, "w") as fd:
+                write_frequency_table(fd, total_frames, ALL_FREQ_ITYPES,
+                                      {k: (c, float(c) / total_frames) for k, c in table.items()})
+        if count_output:
+            with open(count_output, "w") as fd:
+                write_count_table(fd, total_frames, ALL_FREQ_ITYPES, table)
     eng.close()

@@ -193,3 +193,15 @@ def write_frequency_table(fd, total_frames: int, itypes, freqs, order=None):
     keys = order if order is not None else sorted(freqs)
     for r1, r2 in keys:
         fd.write("\t".join([r1, r2, "%.3f" % freqs[(r1, r2)][1]]) + "\n")
+
+
+def write_count_table(fd, total_frames: int, itypes, counts, order=None):
+    """Integer sidecar of the frequency table: ``res1 <TAB> res2 <TAB> frame_count``.  The reference
+    only keeps ``count / total_frames`` printed with three decimals, which loses the counts when runs are merged or
+    frame-weighted afterwards (chacra/scripts/process_hremd_output.py:205-222); with the counts the merge is exact."""
+    fd.write("#\ttotal_frames:%d\tinteraction_types:%s\n" % (total_frames, ",".join(itypes)))
+    fd.write("#\tColumns:\tresidue_1,\tresidue_2\tframe_count\n")
+    keys = order if order is not None else sorted(counts)
+    for r1, r2 in keys:
+        fd.write("%s\t%s\t%d\n" % (r1, r2, counts[(r1, r2)]))
+

@@ -59,6 +59,8 @@ def build_getcontact_parser(program_description, trajectory):
     opt.add_argument("--device", type=int, metavar="INT", default=0, help="CUDA device ordinal (extension) [default = 0]")
     opt.add_argument("--frequency_output", type=str, metavar="PATH", default=None,
                      help="also write the residue-pair frequency table from the device count table (extension)")
+    opt.add_argument("--count_output", type=str, metavar="PATH", default=None,
+                     help="also write the integer residue-pair frame counts behind that table (extension)")
     geo = p.add_argument_group("Geometric criteria")
     for flag, typ, default, text in _GEOMETRY:
         geo.add_argument(flag, type=typ, metavar="FLOAT", default=default, help=text)

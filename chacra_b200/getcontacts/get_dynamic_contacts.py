@@ -48,7 +48,7 @@ def main(argv=None):
     tic = datetime.datetime.now()
     compute_contacts(args.topology, args.trajectory, args.output, itypes, process_geometric_criterion_args(args),
                      args.cores, args.beg, end, args.stride, args.distout, args.ligand, args.solv, args.lipid,
-                     args.sele, sele2, device=args.device, frequency_output=args.frequency_output)
+                     args.sele, sele2, device=args.device, frequency_output=args.frequency_output, count_output=args.count_output)
     print("\nTotal computation time:", (datetime.datetime.now() - tic).total_seconds(), "seconds")
     for k, v in (("topology", args.topology), ("trajectory", args.trajectory), ("output", args.output),
                  ("cores", args.cores), ("solv", args.solv), ("sele", args.sele), ("sele2", sele2), ("stride", args.stride)):

@@ -28,12 +28,13 @@ def main(argv=None):
     ap.add_argument("--sele2", default=None)
     ap.add_argument("--itypes", nargs="+", default=["all"])
     ap.add_argument("--device", type=int, default=0)
+    ap.add_argument("--counts", action="store_true", help="also write counts_state_{i}.tsv (integer frame counts)")
     ap.add_argument("--window", type=int, default=2000, help="frames per replica held on the device at a time")
     args = ap.parse_args(argv)
     from chacra_b200 import compile_topology, read_pdb
     from chacra_b200.demux import demux_contacts_from_files, load_state_table
     from chacra_b200.engine import COMPUTE_ORDER, ContactEngine
-    from chacra_b200.frequencies import ALL_FREQ_ITYPES, counts_to_table, write_frequency_table
+    from chacra_b200.frequencies import ALL_FREQ_ITYPES, counts_to_table, write_count_table, write_frequency_table
     from chacra_b200.trajectory import open_trajectory
     itypes = COMPUTE_ORDER if "all" in args.itypes else [t for t in COMPUTE_ORDER if t in args.itypes]
     atoms = read_pdb(args.topology)
@@ -50,6 +51,9 @@ def main(argv=None):
         pairs = counts_to_table(topo.residue_label, eng.counts(s))
         with open(os.path.join(args.output_dir, "freqs_state_%d.tsv" % s), "w") as fd:
             write_frequency_table(fd, n_frames, ALL_FREQ_ITYPES, {k: (c, float(c) / n_frames) for k, c in pairs.items()})
+        if args.counts:
+            with open(os.path.join(args.output_dir, "counts_state_%d.tsv" % s), "w") as fd:
+                write_count_table(fd, n_frames, ALL_FREQ_ITYPES, pairs)
     eng.close()
     print("wrote %d frequency tables (%d frames per state) to %s" % (len(args.replicas), n_frames, args.output_dir))
 

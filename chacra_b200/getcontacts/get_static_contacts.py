@@ -31,7 +31,7 @@ def main(argv=None):
     tic = datetime.datetime.now()
     compute_contacts(args.structure, args.structure, args.output, itypes, process_geometric_criterion_args(args), 1, 0, 0, 1,
                      args.distout, args.ligand, args.solv, args.lipid, args.sele, sele2, device=args.device,
-                     frequency_output=args.frequency_output)
+                     frequency_output=args.frequency_output, count_output=args.count_output)
     print("\nTotal computation time: " + str((datetime.datetime.now() - tic).total_seconds()) + " seconds")
     for k, v in (("topology", args.structure), ("trajectory", args.structure), ("output", args.output), ("solv", args.solv),
                  ("sele", args.sele), ("sele2", sele2)):

@@ -62,9 +62,10 @@ def test_dynamic_contacts_all_itypes(tmp_path):
 
 def test_dynamic_contacts_distout_and_device_frequencies(tmp_path):
     dyn, _ = _cli()
-    out, fout = tmp_path / "cont.tsv", tmp_path / "freqs_dev.tsv"
+    out, fout, cout = tmp_path / "cont.tsv", tmp_path / "freqs_dev.tsv", tmp_path / "counts_dev.tsv"
     dyn.main(["--topology", TOP, "--trajectory", TRJ, "--output", str(out), "--itypes", "all", "--distout",
-              "--sele", "protein", "--sele2", "protein", "--cores", "4", "--frequency_output", str(fout)])     # ChACRA's call
+              "--sele", "protein", "--sele2", "protein", "--cores", "4", "--frequency_output", str(fout),
+              "--count_output", str(cout)])                                                                 # ChACRA's call + extensions
     lines = _lines(out)
     assert lines[1].endswith(", distance_1-2") and len(lines) == 22589
     import getcontacts_oracle as o
@@ -76,6 +77,13 @@ def test_dynamic_contacts_distout_and_device_frequencies(tmp_path):
         assert f == "%.3f" % float(np.sqrt(o._d2(a, b), dtype=np.float32))
     rows = [ln.split("\t") for ln in _lines(fout)[2:]]
     assert len(rows) == 398 and sum(round(float(r[2]) * 20) for r in rows) == 5831
+    # the integer sidecar: the counts behind that table, and the ones the threaded reader finds in the emitted text
+    crow = [ln.split("\t") for ln in _lines(cout)[2:]]
+    assert _lines(cout)[0].startswith("#\ttotal_frames:20\t") and [r[:2] for r in crow] == [r[:2] for r in rows]
+    assert all("%.3f" % (int(c[2]) / 20) == r[2] for c, r in zip(crow, rows)) and sum(int(c[2]) for c in crow) == 5831
+    from chacra_b200 import frequencies as fq
+    total, from_text = fq.native_counts(str(out), fq.ALL_FREQ_ITYPES, shipped=False)
+    assert total == 20 and from_text == {(c[0], c[1]): int(c[2]) for c in crow}
 
 
 def test_dynamic_contacts_salt_bridges_asp_lys(tmp_path):
