@@ -10,6 +10,7 @@
 //   block is undefined).
 #pragma once
 #include <algorithm>
+#include <chrono>
 #include <cerrno>
 #include <cstdint>
 #include <cstdio>
@@ -171,6 +172,9 @@ inline int64_t write_contacts(int fd, Rec* rec, int64_t n, const Tables& T, int 
         fn(0);
         for (auto& th : pool) th.join();
     };
+    const bool timing = getenv("CHACRA_TIMING") != nullptr;
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto t_start = now();
     // pass 1 (blocks of records): validate, order atom_1 / atom_2 by label, frame range
     const int nb = (int)std::min<int64_t>(nt, (n + 65535) / 65536);
     std::vector<int32_t> bmin((size_t)nb), bmax((size_t)nb);
@@ -238,7 +242,9 @@ inline int64_t write_contacts(int fd, Rec* rec, int64_t n, const Tables& T, int 
             lines[(size_t)t] += got;
         }
     };
+    auto t_sorted = now();
     run(nt, work);
+    auto t_text = now();
     int64_t total = 0;
     for (int t = 0; t < nt; ++t) { if (lines[(size_t)t] < 0) return -3; total += lines[(size_t)t]; }
     // a regular file takes the threads' texts in parallel at their final offsets (one thread copying into the page cache
@@ -261,6 +267,11 @@ inline int64_t write_contacts(int fd, Rec* rec, int64_t n, const Tables& T, int 
     } else {
         for (int t = 0; t < nt; ++t)
             if (!write_all(fd, text[(size_t)t].data(), text[(size_t)t].size())) return -2;
+    }
+    if (timing) {
+        auto sec = [](auto a, auto b) { return std::chrono::duration<double>(b - a).count(); };
+        fprintf(stderr, "tsv: %lld records, %d threads: by frame %.3f s, sort + text %.3f s, write %.3f s\n", (long long)n, nt,
+                sec(t_start, t_sorted), sec(t_sorted, t_text), sec(t_text, now()));
     }
     return total;
 }
