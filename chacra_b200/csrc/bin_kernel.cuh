@@ -89,14 +89,7 @@ bin_frames_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__
             float ext[3];
 #pragma unroll
             for (int d = 0; d < 3; ++d) { org[d] = ord2f(M.bb_min[d]); ext[d] = ord2f(M.bb_max[d]) - org[d]; }
-            float cell = P.cell;
-            for (;;) {                    // the cell edge only ever grows: every pair within the cutoff stays in adjacent cells
-                inv = 1.0f / cell;
-#pragma unroll
-                for (int d = 0; d < 3; ++d) nc[d] = (int)(ext[d] * inv) + 1;
-                if ((long long)(nc[0] + 2) * (nc[1] + 2) * (nc[2] + 2) * (gridb ? 2 : 1) + 1 <= B.max_cells) break;
-                cell *= 1.25f;
-            }
+            grid_dims(ext, P.cell, B.max_cells, gridb, inv, nc);
         }
         const int px = nc[0] + 2, pxy = px * (nc[1] + 2), ncell = pxy * (nc[2] + 2);
         const int nkey = gridb ? 2 * ncell : ncell;

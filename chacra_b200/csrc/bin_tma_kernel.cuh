@@ -41,9 +41,6 @@ struct BinTmaShared {
     unsigned long long full[2];
 };
 
-// unclamped grid coordinate: pair atoms lie inside the bounding box the grid was sized from, so (x - origin) * inv
-// is already in [0, n - 1]; same value as cell_of
-__device__ __forceinline__ int cell_in(float x, float origin, float inv) { return (int)((x - origin) * inv); }
 
 template <int THREADS, int APT, int NBUF>
 __global__ void __launch_bounds__(THREADS, NBUF == 1 ? 2 : 1)
@@ -156,14 +153,7 @@ bin_frames_tma_kernel(DevTopo T, DevParams P, BinLayout B, BinTmaLayout Y, const
             float ext[3];
 #pragma unroll
             for (int d = 0; d < 3; ++d) { org[d] = ord2f(M.bb_min[bi][d]); ext[d] = ord2f(M.bb_max[bi][d]) - org[d]; }
-            float cell = P.cell;
-            for (;;) {                    // the cell edge only ever grows: every pair within the cutoff stays in adjacent cells
-                inv = 1.0f / cell;
-#pragma unroll
-                for (int d = 0; d < 3; ++d) nc[d] = (int)(ext[d] * inv) + 1;
-                if ((long long)(nc[0] + 2) * (nc[1] + 2) * (nc[2] + 2) * (gridb ? 2 : 1) + 1 <= Y.max_cells) break;
-                cell *= 1.25f;
-            }
+            grid_dims(ext, P.cell, Y.max_cells, gridb, inv, nc);
         }
         const int px = nc[0] + 2, pxy = px * (nc[1] + 2), ncell = pxy * (nc[2] + 2);
         const int nkey = gridb ? 2 * ncell : ncell;
@@ -174,7 +164,7 @@ bin_frames_tma_kernel(DevTopo T, DevParams P, BinLayout B, BinTmaLayout Y, const
 #pragma unroll
         for (int k = 0; k < APT; ++k) {
             const int p = tid + k * THREADS;
-            int c = (cell_in(rz[k], org[2], inv) + 1) * pxy + (cell_in(ry[k], org[1], inv) + 1) * px + cell_in(rx[k], org[0], inv) + 1;
+            int c = (cell_of(rz[k], org[2], inv, nc[2]) + 1) * pxy + (cell_of(ry[k], org[1], inv, nc[1]) + 1) * px + cell_of(rx[k], org[0], inv, nc[0]) + 1;
             r_cr[k] = (unsigned)(p < NP ? c : dummy);
         }
         if (gridb) {                      // unselected solvent sorts into the second set of cells

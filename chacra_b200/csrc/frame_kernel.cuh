@@ -36,6 +36,23 @@ __device__ __forceinline__ const float* frame_ptr(const float* xyz, const long l
     return xyz + (size_t)(src ? __ldg(src + f) : f) * (size_t)frame_stride;
 }
 
+// Grid over a frame's bounding box: the cell edge starts at the cutoff and only ever grows (every pair within the cutoff
+// stays in adjacent cells) until the padded grid fits `max_cells` counters.  Safe for any input: a NaN or infinite extent
+// counts as zero (such atoms are clamped into the border cells by cell_of), per-axis counts are capped before they are
+// multiplied, so nothing overflows and the loop ends (at most ~400 steps for an extent of 3e38).
+__device__ __forceinline__ void grid_dims(const float ext_in[3], float cell, long long max_cells, bool gridb, float& inv, int nc[3]) {
+    float ext[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) ext[d] = (ext_in[d] >= 0.f && ext_in[d] <= 3.0e38f) ? ext_in[d] : 0.f;
+    for (;;) {
+        inv = 1.0f / cell;
+#pragma unroll
+        for (int d = 0; d < 3; ++d) nc[d] = (int)fminf(ext[d] * inv, 1.0e6f) + 1;
+        if ((long long)(nc[0] + 2) * (nc[1] + 2) * (nc[2] + 2) * (gridb ? 2 : 1) + 1 <= max_cells) break;
+        cell *= 1.25f;
+    }
+}
+
 __device__ __forceinline__ int cell_of(float x, float origin, float inv, int n) {
     int c = (int)((x - origin) * inv);
     return min(max(c, 0), n - 1);

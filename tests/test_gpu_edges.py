@@ -89,3 +89,34 @@ def test_empty_single_and_invalid_submissions(c2):
     eng.synchronize()
     assert np.array_equal(eng.counts(0), _counts(topo, [(x[:260], 0, 0)])[0])
     eng.close()
+
+
+def test_degenerate_frames_do_not_disturb_their_neighbours():
+    """Frames are independent: NaN, infinite, absurdly large or fully collapsed coordinates in some frames of one fragment
+    leave the counts of the other fragments exactly as they are (and nothing hangs or faults)."""
+    import torch
+    import bench
+    from chacra_b200 import compile_topology
+    from chacra_b200.synthetic import FrameGenerator
+    path, atoms = bench.make_topology(1)
+    topo = compile_topology(atoms)
+    x = FrameGenerator(atoms.xyz, 77, amplitude=1.0, device="cuda").frames(300)
+    clean = _counts(topo, [(x[:100], 0, 0), (x[200:], 0, 200)])[0]
+    bad = x.clone()
+    bad[120, 5] = float("nan")
+    bad[121, ::7] = float("inf")
+    bad[122] *= 1e30
+    bad[123] = bad[123, 0]                                    # every atom on one point
+    bad[124, :, 2] = 0.0                                      # flattened into a plane
+    for env in ({}, {"CHACRA_BIN_VARIANT": "0"}, {"CHACRA_BIN_VARIANT": "4"}, {"CHACRA_FORCE_LARGE": "1"}):
+        os.environ.update(env)
+        try:
+            a = _counts(topo, [(bad[:100], 0, 0), (bad[200:], 0, 200)])[0]
+            whole = _counts(topo, [(bad, 0, 0)])[0]
+            middle = _counts(topo, [(bad[100:200], 0, 100)])[0]
+        finally:
+            for k in env:
+                os.environ.pop(k, None)
+        assert np.array_equal(a, clean)
+        assert np.array_equal(whole, clean + middle)          # still additive over fragments
+        assert middle.max() <= 100
