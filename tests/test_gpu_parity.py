@@ -132,3 +132,52 @@ def test_binning_kernel_variants_agree(oracle_5xnd, monkeypatch):
     # the first 20 frames are the fixture itself
     want, _ = _oracle_sets(oracle_5xnd)
     assert {c for c in runs["3"]["contacts"] if c[0] < 20} == want
+
+
+@pytest.mark.parametrize("first,last", [(0, 1), (0, 2), (3, 6), (0, 12), (40, 75), (100, 112)])
+def test_tiny_and_odd_sized_systems(tmp_path, oracle_5xnd, first, last):
+    """Cut-outs of the 5xnd fixture (residues first..last-1: from one residue to a few dozen; fewer pair atoms than a
+    warp, a handful of cells, possibly no ring / ion / hydrogen-bond partner at all) against the oracle, on both pair
+    paths and two binning variants."""
+    import getcontacts_oracle as o
+    src = os.path.join(GOLDEN, "5xnd_topology.pdb")
+    keep, lines, seen = [], [], []
+    k = 0
+    for ln in open(src):
+        if ln.startswith(("ATOM  ", "HETATM")):
+            key = (ln[21], ln[22:27])
+            if key not in seen:
+                seen.append(key)
+            if first <= seen.index(key) < last:
+                keep.append(k)
+                lines.append(ln)
+            k += 1
+    top = str(tmp_path / "cut.pdb")
+    open(top, "w").write("".join(lines) + "END\n")
+    frames = np.ascontiguousarray(oracle_5xnd["frames"][:, keep, :])
+    res = o.run(top, top, ALL, frames=frames, collect_near=True)
+    want, want_near = _oracle_sets(res)
+    for env in ({}, {"CHACRA_FORCE_LARGE": "1"}, {"CHACRA_BIN_VARIANT": "0"}, {"CHACRA_BIN_VARIANT": "4"}):
+        os.environ.update(env)
+        try:
+            run = _engine_run(top, frames, ALL)
+        finally:
+            for name in env:
+                os.environ.pop(name, None)
+        assert run["contacts"] == want, (env, sorted(want - run["contacts"])[:3], sorted(run["contacts"] - want)[:3])
+        assert run["near"] == want_near
+        _check_counts(run, res)
+
+
+def test_far_from_the_origin_coarse_float_grid(oracle_5xnd):
+    """The same frames shifted by thousands of Angstrom: float32 coordinates then sit on a 5e-4 A grid, exact distance
+    ties and near-cutoff events become common -- the float32 recipes must still agree bit for bit."""
+    import getcontacts_oracle as o
+    top = os.path.join(GOLDEN, "5xnd_topology.pdb")
+    frames = (oracle_5xnd["frames"][:8].astype(np.float64) + np.array([4000.0, -7000.0, 9000.0])).astype(np.float32)
+    res = o.run(top, top, ALL, frames=frames, collect_near=True)
+    want, want_near = _oracle_sets(res)
+    run = _engine_run(top, frames, ALL)
+    assert run["contacts"] == want, (sorted(want - run["contacts"])[:3], sorted(run["contacts"] - want)[:3])
+    assert run["near"] == want_near and len(want_near) > 0
+    _check_counts(run, res)
