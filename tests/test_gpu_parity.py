@@ -181,3 +181,30 @@ def test_far_from_the_origin_coarse_float_grid(oracle_5xnd):
     assert run["contacts"] == want, (sorted(want - run["contacts"])[:3], sorted(run["contacts"] - want)[:3])
     assert run["near"] == want_near and len(want_near) > 0
     _check_counts(run, res)
+
+
+@pytest.mark.parametrize("change", [
+    {"SALT_BRIDGE_CUTOFF_DISTANCE": 8.0, "HBOND_CUTOFF_DISTANCE": 5.0, "VDW_EPSILON": 2.0},          # wide: larger cells
+    {"SALT_BRIDGE_CUTOFF_DISTANCE": 2.5, "HBOND_CUTOFF_DISTANCE": 2.8, "VDW_EPSILON": 0.0, "HBOND_CUTOFF_ANGLE": 20},
+    {"HBOND_CUTOFF_ANGLE": 180, "PI_CATION_CUTOFF_ANGLE": 90, "PI_STACK_CUTOFF_ANGLE": 90, "T_STACK_CUTOFF_ANGLE": 90,
+     "PI_STACK_PSI_ANGLE": 90, "T_STACK_PSI_ANGLE": 90, "PI_CATION_CUTOFF_DISTANCE": 9.5, "PI_STACK_CUTOFF_DISTANCE": 9.5,
+     "T_STACK_CUTOFF_DISTANCE": 6.0},
+    {"HBOND_RES_DIFF": 0, "VDW_RES_DIFF": 0},
+    {"HBOND_RES_DIFF": 4, "VDW_RES_DIFF": 6, "HBOND_CUTOFF_ANGLE": 0},
+])
+def test_non_default_geometric_criteria(oracle_5xnd, change):
+    """Every --*_cutoff_* / --*_res_diff flag of the reference's parser (argparsers.py:80-125) away from its default."""
+    import getcontacts_oracle as o
+    top = os.path.join(GOLDEN, "5xnd_topology.pdb")
+    frames = np.ascontiguousarray(oracle_5xnd["frames"][:5])
+    geom = dict(o.DEFAULT_GEOM)
+    geom.update(change)
+    res = o.run(top, top, ALL, geom=geom, frames=frames, collect_near=True)
+    want, want_near = _oracle_sets(res)
+    run = _engine_run(top, frames, ALL, geometry=geom)
+    for it in sorted({c[1] for c in want | run["contacts"]}):
+        w = {c for c in want if c[1] == it}
+        g = {c for c in run["contacts"] if c[1] == it}
+        assert g == w, "%s: missing %s extra %s" % (it, sorted(w - g)[:5], sorted(g - w)[:5])
+    assert run["near"] == want_near
+    _check_counts(run, res)
