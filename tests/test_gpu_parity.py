@@ -208,3 +208,29 @@ def test_non_default_geometric_criteria(oracle_5xnd, change):
         assert g == w, "%s: missing %s extra %s" % (it, sorted(w - g)[:5], sorted(g - w)[:5])
     assert run["near"] == want_near
     _check_counts(run, res)
+
+
+def test_unequal_overlapping_selections_over_two_fragments(oracle_5xnd):
+    """--sele and --sele2 different and overlapping, 130 frames = two fragments: the stand-alone hydrophobic-query kernel
+    (subset rule for sele1, equality rule for sele2, hydrophobics.py:24,39) and both directions of every pair rule."""
+    import getcontacts_oracle as o
+    top = os.path.join(GOLDEN, "5xnd_topology.pdb")
+    base = oracle_5xnd["frames"]
+    frames = np.ascontiguousarray(base[(np.arange(130) * 3) % 20])
+    frames[100:] = base[(np.arange(30) + 11) % 20]
+    s1, s2 = "protein and resid 1 to 60", "protein and resid 45 to 112"
+    res = o.run(top, top, ALL, frames=frames, sele1=s1, sele2=s2, collect_near=True)
+    want, want_near = _oracle_sets(res)
+    for env in ({}, {"CHACRA_FORCE_LARGE": "1"}):
+        os.environ.update(env)
+        try:
+            run = _engine_run(top, frames, ALL, s1, s2)
+        finally:
+            for name in env:
+                os.environ.pop(name, None)
+        for it in sorted({c[1] for c in want | run["contacts"]}):
+            w = {c for c in want if c[1] == it}
+            g = {c for c in run["contacts"] if c[1] == it}
+            assert g == w, "%s %s: missing %s extra %s" % (env, it, sorted(w - g)[:5], sorted(g - w)[:5])
+        assert run["near"] == want_near
+        _check_counts(run, res)
