@@ -22,6 +22,7 @@ from . import _lib
 from ._hostio import FileStager
 
 XTC_MAGIC = 1995
+_SLACK = 128                      # zero bytes after the last stream of a transfer: a corrupt run may read this far past its end
 _HEADER = 52                      # magic, natoms, step, time, box[9]
 META_DTYPE = np.dtype([("offset", "<i8"), ("nbytes", "<i4"), ("precision", "<f4"), ("minint", "<i4", 3),
                        ("maxint", "<i4", 3), ("smallidx", "<i4"), ("raw", "<i4"), ("bitsize", "<i4"),
@@ -130,7 +131,7 @@ class XTCFile(FileStager):
         metas, off, t_host = [], 0, 0.0
         if len(cuts) == 2:
             meta, used = self._stage(idx, 0)
-            d_blob = self._stage_bufs[0][:used + 8].to(dev, non_blocking=True)
+            d_blob = self._stage_bufs[0][:used + _SLACK].to(dev, non_blocking=True)
             metas.append(meta)
             t_host = time.perf_counter() - t0
         else:
@@ -142,11 +143,11 @@ class XTCFile(FileStager):
                     t1 = time.perf_counter()
                     meta, used = pending.result()
                     t_host += time.perf_counter() - t1          # time the device side had to wait for the file
-                    if off + used + 8 > d_blob.numel():         # spans carry the frame headers too; grow if the estimate was short
-                        bigger = torch.empty(off + used + 8 + (d_blob.numel() >> 2), dtype=torch.uint8, device=dev)
+                    if off + used + _SLACK > d_blob.numel():         # spans carry the frame headers too; grow if the estimate was short
+                        bigger = torch.empty(off + used + _SLACK + (d_blob.numel() >> 2), dtype=torch.uint8, device=dev)
                         bigger[:off].copy_(d_blob[:off])
                         d_blob = bigger
-                    d_blob[off:off + used + 8].copy_(self._stage_bufs[c & 1][:used + 8], non_blocking=True)
+                    d_blob[off:off + used + _SLACK].copy_(self._stage_bufs[c & 1][:used + _SLACK], non_blocking=True)
                     done[c & 1].record()
                     meta["offset"] += off
                     metas.append(meta)
@@ -172,19 +173,19 @@ class XTCFile(FileStager):
         sizes = (meta["nbytes"].astype(np.int64) + 3) & ~3
         lo, hi = int(meta["offset"][0]), int(meta["offset"][-1] + sizes[-1])
         if hi - lo <= 1.25 * sizes.sum() + 4096:        # (nearly) consecutive frames: one span, headers and all
-            host = self._pinned(hi - lo + 8, which)
+            host = self._pinned(hi - lo + _SLACK, which)
             self._pread(memoryview(host.numpy())[:hi - lo], lo)        # straight from the file into pinned memory
             meta["offset"] -= lo                        # file offsets are multiples of 4 (XDR), so these are too
             used = hi - lo
         else:
             starts = np.concatenate([[0], np.cumsum(sizes)[:-1]])
             used = int(sizes.sum())
-            host = self._pinned(used + 8, which)
+            host = self._pinned(used + _SLACK, which)
             view = host.numpy()
             for src, n, dst in zip(meta["offset"], sizes, starts):
                 view[dst:dst + n] = self._mm[src:src + n]
             meta["offset"] = starts
-        host.numpy()[used:used + 8] = 0
+        host.numpy()[used:used + _SLACK] = 0
         return meta, used
 
     def read(self, beg: int = 0, end: int | None = None, stride: int = 1) -> np.ndarray:

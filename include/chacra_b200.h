@@ -230,7 +230,7 @@ typedef struct chc_xtc_frame {
     int32_t bitsizeint[3];
 } chc_xtc_frame;
 
-/* d_blob: DEVICE bytes (4-byte aligned, 8 bytes of slack after the last stream); d_meta: DEVICE array of n_frames
+/* d_blob: DEVICE bytes (4-byte aligned, 128 readable bytes after the last stream); d_meta: DEVICE array of n_frames
  * entries; d_xyz: DEVICE float32 [n_frames][frame_stride] (frame_stride 0 = 3*n_atoms), Angstrom.  Synchronises the
  * stream; CHC_E_INVALID when a bit stream is inconsistent with n_atoms. */
 int chc_xtc_decode(const void* d_blob, const chc_xtc_frame* d_meta, int64_t n_frames, int32_t n_atoms, float* d_xyz,
