@@ -27,7 +27,7 @@ WORKLOAD = "1tnf solvated HREMD synthetic: 20 states x 10k frames, ~7k protein a
 METRIC = "contact frames/sec (all itypes)"
 # dram__bytes_read.sum + dram__bytes_write.sum per frame of this workload, from the committed ncu --set full capture
 # (profiles/r01_v4_ncu_summary.txt, 11 840 frames per launch): pair kernel 0.923 GB + 5 MB, streaming kernel 0.931 GB + 0.862 GB
-NCU_DRAM_BYTES_PER_FRAME = {"pair_frames_kernel": (922.934528e6 + 5.139968e6) / 11840, "bin_frames_kernel": (931.195136e6 + 862.322432e6) / 11840}
+NCU_DRAM_BYTES_PER_FRAME = {"pair_frames_kernel": (923.036672e6 + 5.214208e6) / 11840, "bin_frames_kernel": (931.569408e6 + 859.877888e6) / 11840}
 
 
 def make_topology(copies=4):
