@@ -205,3 +205,29 @@ def write_count_table(fd, total_frames: int, itypes, counts, order=None):
     for r1, r2 in keys:
         fd.write("%s\t%s\t%d\n" % (r1, r2, counts[(r1, r2)]))
 
+
+
+def read_count_table(path: str):
+    """(total_frames, {(res1, res2): count}) from a file written by ``write_count_table``."""
+    total, table = 0, {}
+    with open(path) as fh:
+        for line in fh:
+            if line.startswith("#"):
+                if "total_frames:" in line:
+                    total = int(line.split("total_frames:")[1].split()[0])
+                continue
+            tok = line.rstrip("\n").split("\t")
+            if len(tok) == 3:
+                table[(tok[0], tok[1])] = int(tok[2])
+    return total, table
+
+
+def merge_runs_exact(count_files, output_file, itypes=None):
+    """Frequency table of several runs of one state from their integer sidecars: sum of counts over sum of frames.
+    The reference combines runs from the three-decimal frequency files weighted by frame counts
+    (chacra/scripts/process_hremd_output.py:205-222), which keeps a rounding error of up to 5e-4 per run; this is exact."""
+    per_input = [read_count_table(p) for p in count_files]
+    total, freqs = merge_counts(per_input)
+    with open(output_file, "w") as fd:
+        write_frequency_table(fd, total, itypes or ALL_FREQ_ITYPES, freqs)
+    return total, {k: c for k, (c, _) in freqs.items()}

@@ -100,3 +100,25 @@ def test_dynamic_cli_flag_errors():
     with pytest.raises(SystemExit) as e:
         cli.main(["--topology", "a.pdb", "--trajectory", "a.dcd", "--output", "o.tsv", "--itypes", "nonsense"])
     assert e.value.code == 2
+
+
+def test_count_sidecar_round_trip_and_exact_merge_of_runs(tmp_path):
+    from chacra_b200 import frequencies as fq
+    runs = [(700, {("A:ALA:1", "A:ARG:2"): 333, ("A:ALA:1", "A:GLY:9"): 1}),
+            (1300, {("A:ALA:1", "A:ARG:2"): 1001, ("A:ARG:2", "A:GLY:9"): 650})]
+    files = []
+    for k, (frames, table) in enumerate(runs):
+        p = str(tmp_path / ("counts_%d.tsv" % k))
+        with open(p, "w") as fd:
+            fq.write_count_table(fd, frames, fq.ALL_FREQ_ITYPES, table)
+        assert fq.read_count_table(p) == (frames, table)
+        files.append(p)
+    out = str(tmp_path / "freqs_state_0.tsv")
+    total, merged = fq.merge_runs_exact(files, out)
+    assert total == 2000 and merged == {("A:ALA:1", "A:ARG:2"): 1334, ("A:ALA:1", "A:GLY:9"): 1, ("A:ARG:2", "A:GLY:9"): 650}
+    rows = [ln.split("\t") for ln in open(out).read().splitlines()]
+    assert rows[0][:2] == ["#", "total_frames:2000"]
+    assert rows[2:] == [["A:ALA:1", "A:ARG:2", "0.667"], ["A:ALA:1", "A:GLY:9", "0.001"], ["A:ARG:2", "A:GLY:9", "0.325"]]
+    # the reference's way (frame-weighted three-decimal frequencies) is off in the last digit here: 0.476*0.35 + 0.770*0.65 = 0.6671 vs 1334/2000 = 0.667
+    weighted = round(333 / 700, 3) * 0.35 + round(1001 / 1300, 3) * 0.65
+    assert abs(weighted - 1334 / 2000) > 5e-5
