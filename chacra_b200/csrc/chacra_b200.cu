@@ -15,7 +15,9 @@
 #include "tsv_writer.h"
 #include "tsv_counts.h"
 
+#ifndef PAIR_THREADS
 #define PAIR_THREADS 1024
+#endif
 #define SMEM_LIMIT (227 * 1024)
 
 struct chc_ctx {

@@ -18,9 +18,20 @@
 #include "frame_phases.cuh"
 #include "water_phase.cuh"
 
-#define Q1_CAP 96           // (i, j) survivors per warp (>= 64: see the flush in E1)
+#ifndef Q1_CAP
+#define Q1_CAP 128          // (i, j) survivors per warp (>= 64: see the flush in E1; 128 measured 1.2 % faster than 96, 160+ no better)
+#endif
+#ifndef QF_CAP
 #define QF_CAP 64           // survivors that passed the cheap filter, per warp
+#endif
+#ifndef Q2_CAP
 #define Q2_CAP 64           // classified pairs per warp and queue (plain, polar)
+#endif
+#ifndef E1_UNROLL
+#define E1_UNROLL 2
+#endif
+#define CHC_PRAGMA(x) _Pragma(#x)
+#define CHC_UNROLL(n) CHC_PRAGMA(unroll n)
 
 struct PairLayout {         // shared-memory plan of the pair kernel (bytes)
     int off_rec;            // SMALL: header | spos | aux  (B.fixed_bytes)
@@ -206,7 +217,7 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                 mbase = beg + k0;
                 const float4* pj = spos + mbase;
                 unsigned m = 0u;
-#pragma unroll 2
+CHC_UNROLL(E1_UNROLL)
                 for (int k4 = 0; k4 < n; k4 += 4) {
                     const float4 a = pj[k4], b = pj[k4 + 1], c = pj[k4 + 2], d = pj[k4 + 3];
                     const unsigned nib = (dist2_fused(ix, iy, iz, a.x, a.y, a.z) <= cut2p ? 1u : 0u) |
