@@ -27,6 +27,10 @@
 #ifndef Q2_CAP
 #define Q2_CAP 64           // classified pairs per warp and queue (plain, polar)
 #endif
+#ifndef E1_TARGET
+#define E1_TARGET 32        // E1 runs until this many survivors are queued (one F batch)
+#endif
+static_assert(Q1_CAP - E1_TARGET >= 32 && E1_TARGET >= 32, "a lane's 32 pending hits must fit behind E1_TARGET queued survivors");
 #ifndef E1_UNROLL
 #define E1_UNROLL 2
 #endif
@@ -102,11 +106,13 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                 bulk_g2s(smem + L.off_rec, rec, (unsigned)B.fixed_bytes, &M->bar);
                 bulk_g2s(smem + L.off_cells, rec + B.off_cells, cbytes, &M->bar);
                 // the record this CTA needs next: on its way to L2 while this frame is enumerated (large chunks spill to HBM)
+#ifndef NO_L2_PREFETCH
                 if (f + (int)gridDim.x < n_frames) {
                     const unsigned char* nxt = rec + (size_t)gridDim.x * B.stride;
                     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(nxt), "r"((unsigned)B.fixed_bytes) : "memory");
                     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(nxt + B.off_cells), "r"(cbytes) : "memory");
                 }
+#endif
                 M->cursor = 0; M->ring_cursor = 0; M->nmark = 0;
             }
             for (int w = tid; w < L.bits_words; w += THREADS) bits[w] = 0u;
@@ -151,7 +157,7 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
         bool exhausted = false;
         for (;;) {
             // ---- E1 ----
-            while (q1n < 32 && !exhausted) {
+            while (q1n < E1_TARGET && !exhausted) {
                 if (__any_sync(FULL, mask != 0u)) {
                     // queue the pending hits, whole lanes at a time, as far as the queue has room (q1n < 32 here and a
                     // lane holds at most 32 hits, so the first pending lane always fits: Q1_CAP - 32 >= 32)
