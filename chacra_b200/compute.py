@@ -14,7 +14,7 @@ import sys
 
 import numpy as np
 
-from .engine import ContactEngine, ChacraError, COMPUTE_ORDER, TRAJ_FRAG_SIZE
+from .engine import ContactEngine, ChacraError, COMPUTE_ORDER, NEAR_KINDS, TRAJ_FRAG_SIZE
 from .topology import read_pdb, compile_topology
 from .trajectory import open_trajectory
 from .tsv import ContactWriter, header_lines
@@ -25,12 +25,14 @@ _RECORD_CAPACITY = 1 << 23
 
 def compute_contacts(top, traj, output, itypes, geom_criterion_values, cores, beg, end, stride, distout,
                      ligand_sele, solv_sele, lipid_sele, sele1, sele2, device=0, frequency_output=None,
-                     count_output=None):
+                     count_output=None, near_output=None, write_contacts=True):
     """Compute the contact list of ``traj`` and write it to ``output`` (contact-list TSV).
 
     ``cores`` is accepted for interface compatibility (the reference uses it as the number of VMD worker
-    processes, :267); one GPU replaces them.  ``frequency_output`` (extension): also write the residue-pair
-    frequency table straight from the device count table (intended counts, SURVEY A.12 level L2).
+    processes, :267); one GPU replaces them.  Extensions: ``frequency_output`` / ``count_output`` write the
+    residue-pair frequency table / integer frame counts straight from the device count table (intended counts,
+    SURVEY A.12 level L2); ``near_output`` lists every pair within 1e-4 A / 1e-3 degree of a cutoff;
+    ``write_contacts=False`` skips the contact list altogether (no records leave the device, no text is written).
     """
     geom = dict(geom_criterion_values or {})
     itypes = list(itypes)
@@ -55,41 +57,84 @@ def compute_contacts(top, traj, output, itypes, geom_criterion_values, cores, be
     beg = max(min(beg, sim_length - 1), 0)                # :247-249
     end = min(max(end, beg), sim_length - 1)
     stride = max(1, stride)
-    total_frames = math.ceil((end - beg + 1) / stride)
+    total_frames = math.ceil((end - beg + 1) / stride)    # what the header says (:309)
     num_fragments = math.ceil((end - beg + 1) / (TRAJ_FRAG_SIZE * stride))
+    # The reference's fragments are never clamped to --end (:253-254): the last one runs to its own end or to the end of
+    # the trajectory, so frames past --end are computed and written too.  Reproduced (the oracle does the same).
+    last = min(beg + num_fragments * TRAJ_FRAG_SIZE * stride - 1, sim_length - 1)
+    n_proc = len(range(beg, last + 1, stride))
     print("Processing %s (frame %d to %d with stride of %d) as %d fragments\n" % (traj, beg, end, stride, num_fragments))
 
     kernel_itypes = [t for t in COMPUTE_ORDER if t in itypes]
-    eng = ContactEngine(topo, kernel_itypes, geom, n_states=1, emit_contacts=True, contact_capacity=_RECORD_CAPACITY,
-                        device=device)
+    track_near = near_output is not None
+    eng = ContactEngine(topo, kernel_itypes, geom, n_states=1, emit_contacts=bool(write_contacts),
+                        contact_capacity=_RECORD_CAPACITY, track_near=track_near, near_capacity=1 << 20, device=device)
     labels = atoms.atom_labels()
-    with open(output, "w") as fd:
-        fd.write(header_lines(total_frames, beg, end, stride, itypes, distout))
-        writer = ContactWriter(fd, labels, beg, stride, distout, TRAJ_FRAG_SIZE)
-        done = 0                                         # selected frames processed so far
-        stage = [0.0, 0.0, 0.0]                          # seconds: trajectory input, contacts + drain, TSV text
-        per_frame = None                                 # measured records per frame
-        while done < total_frames:
-            if per_frame is None:
-                n = min(TRAJ_FRAG_SIZE, total_frames - done)
-            else:
-                room = int(0.5 * _RECORD_CAPACITY / max(per_frame, 1.0))
-                n = min(max(TRAJ_FRAG_SIZE, room // TRAJ_FRAG_SIZE * TRAJ_FRAG_SIZE), total_frames - done)
+    near_fd = None
+    if track_near:
+        near_fd = open(near_output, "w")
+        near_fd.write("# near-cutoff observations: |value - cutoff| < 1e-4 A (distances) or 1e-3 degree (angles); these pairs sit on the\n"
+                      "# float32 boundary of a reference criterion and are listed apart from the contact list\n"
+                      "# Columns: frame, criterion, atom_1, atom_2, value_minus_cutoff\n")
+    near_total = 0
+
+    def drain_near():
+        nonlocal near_total
+        rec, total = eng.drain_near()
+        if total > len(rec):
+            raise ChacraError("near-cutoff buffer overflow (%d observations)" % total)
+        near_total += len(rec)
+        order = np.lexsort((rec["atom2"], rec["atom1"], rec["kind"], rec["frame"]))
+        for r in rec[order]:
+            near_fd.write("%d\t%s\t%s\t%s\t%.3e\n" % (beg + int(r["frame"]) * stride, NEAR_KINDS[r["kind"]], labels[r["atom1"]],
+                                                       labels[r["atom2"]], r["delta"]))
+
+    reader = getattr(trj, "read_device", trj.read)       # DCD and XTC frames are unpacked on the device and stay there
+    stage = [0.0, 0.0, 0.0]                              # seconds: trajectory input, contacts + drain, TSV text
+    done = 0                                             # selected frames processed so far
+    if write_contacts:
+        with open(output, "w") as fd:
+            fd.write(header_lines(total_frames, beg, end, stride, itypes, distout))
+            writer = ContactWriter(fd, labels, beg, stride, distout, TRAJ_FRAG_SIZE)
+            per_frame = None                             # measured records per frame
+            while done < n_proc:
+                if per_frame is None:
+                    n = min(TRAJ_FRAG_SIZE, n_proc - done)
+                else:
+                    room = int(0.5 * _RECORD_CAPACITY / max(per_frame, 1.0))
+                    n = min(max(TRAJ_FRAG_SIZE, room // TRAJ_FRAG_SIZE * TRAJ_FRAG_SIZE), n_proc - done)
+                first = beg + done * stride
+                t0 = time.perf_counter()
+                frames = reader(first, min(first + (n - 1) * stride, last), stride)
+                t1 = time.perf_counter()
+                eng.submit(frames, 0, done)
+                eng.synchronize()
+                rec = eng.drain_contacts(copy=False)      # reordered in place by the writer, gone before the next drain
+                t2 = time.perf_counter()
+                writer.write(rec)
+                if track_near:
+                    drain_near()
+                t3 = time.perf_counter()
+                stage[0] += t1 - t0; stage[1] += t2 - t1; stage[2] += t3 - t2
+                per_frame = max(per_frame or 0.0, len(rec) / float(len(frames)))
+                done += len(frames)
+    else:
+        # counts only: whole fragments in chunks of about 1 GiB of coordinates, nothing but the count table comes back
+        per = max(TRAJ_FRAG_SIZE, (1 << 30) // (12 * atoms.n) // TRAJ_FRAG_SIZE * TRAJ_FRAG_SIZE)
+        while done < n_proc:
+            n = min(per, n_proc - done)
             first = beg + done * stride
-            # DCD and XTC frames are unpacked on the device and stay there; other readers hand host arrays to the staging path
-            reader = getattr(trj, "read_device", trj.read)
             t0 = time.perf_counter()
-            frames = reader(first, min(first + (n - 1) * stride, end), stride)
+            frames = reader(first, min(first + (n - 1) * stride, last), stride)
             t1 = time.perf_counter()
             eng.submit(frames, 0, done)
             eng.synchronize()
-            rec = eng.drain_contacts(copy=False)          # reordered in place by the writer, gone before the next drain
-            t2 = time.perf_counter()
-            writer.write(rec)
-            t3 = time.perf_counter()
-            stage[0] += t1 - t0; stage[1] += t2 - t1; stage[2] += t3 - t2
-            per_frame = max(per_frame or 0.0, len(rec) / float(len(frames)))
+            if track_near:
+                drain_near()
+            stage[0] += t1 - t0; stage[1] += time.perf_counter() - t1
             done += len(frames)
+    if near_fd is not None:
+        near_fd.close()
     if os.environ.get("CHACRA_TIMING"):
         print("stages: trajectory input %.3f s, contacts + drain %.3f s, TSV text %.3f s" % tuple(stage), file=sys.stderr)
     if frequency_output or count_output:
@@ -103,3 +148,4 @@ def compute_contacts(top, traj, output, itypes, geom_criterion_values, cores, be
             with open(count_output, "w") as fd:
                 write_count_table(fd, total_frames, ALL_FREQ_ITYPES, table)
     eng.close()
+    return None

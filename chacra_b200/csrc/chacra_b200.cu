@@ -95,6 +95,11 @@ static const void* bin_kernel_fn(int variant, int apt, int* threads) {
     }
 }
 
+static const void* pair_kernel_fn(bool small, bool near) {
+    if (small) return near ? (const void*)pair_frames_kernel<PAIR_THREADS, true, true> : (const void*)pair_frames_kernel<PAIR_THREADS, true, false>;
+    return near ? (const void*)pair_frames_kernel<PAIR_THREADS, false, true> : (const void*)pair_frames_kernel<PAIR_THREADS, false, false>;
+}
+
 static size_t al16(size_t v) { return (v + 15) & ~size_t(15); }
 
 // Decide where a frame lives while its pairs are enumerated (shared memory or in place in global memory) and lay
@@ -245,6 +250,10 @@ extern "C" int chc_create(chc_ctx** out, const chc_topology* t, const chc_params
     if (p->itype_mask & CHC_IT_HP) P.pre2 = std::max(P.pre2, P.hp2);
     if (p->itype_mask & CHC_IT_SB) P.pre2 = std::max(P.pre2, P.sb2);
     if (p->itype_mask & CHC_IT_HB) P.pre2 = std::max(P.pre2, P.hb2);
+    if (p->track_near) {                  // the near-cutoff band just ABOVE a distance cutoff must survive the prefilter too
+        const double band = 4.0 * std::max(p->near_dist_tol, 0.0);
+        P.pre2 = std::max(P.pre2, sq(cmax + band));
+    }
     P.hb_angle = (float)p->hb_angle;
     P.hb_fast = P.hb_angle < 89.0f && P.hb_angle > 1.0f;
     if (P.hb_fast) {
@@ -256,6 +265,7 @@ extern "C" int chc_create(chc_ctx** out, const chc_topology* t, const chc_params
     double rmax = std::max(p->pc_dist, std::max(p->ps_dist, p->ts_dist)) + 0.05;
     P.ring_pre2 = (float)(rmax * rmax);
     P.pc_soft2 = sq(10.0); P.ps_soft2 = sq(10.0); P.ts_soft2 = sq(6.0);   // pi_cation.py:22, aromatics.py:26-27
+    P.pc_soft = 10.0; P.ps_soft = 10.0; P.ts_soft = 6.0;
     P.pc_dist = p->pc_dist; P.pc_angle = p->pc_angle; P.ps_dist = p->ps_dist; P.ps_angle = p->ps_angle; P.ps_psi = p->ps_psi;
     P.ts_dist = p->ts_dist; P.ts_angle = p->ts_angle; P.ts_psi = p->ts_psi;
     P.sb_dist = p->sb_dist; P.hb_dist = p->hb_dist; P.hp_dist = p->hp_dist; P.soft = p->vdw_soft_cutoff;
@@ -264,8 +274,7 @@ extern "C" int chc_create(chc_ctx** out, const chc_topology* t, const chc_params
     ctx->n_pairs = (int64_t)T.R * (T.R + 1) / 2;
     rc = plan(ctx);
     if (rc != CHC_OK) return fail(ctx, rc, "topology with %d pair atoms / %d residues does not fit any kernel path", T.n_pair, T.R);
-    if (ctx->small_path) CK(cudaFuncSetAttribute(pair_frames_kernel<PAIR_THREADS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->L.total));
-    else CK(cudaFuncSetAttribute(pair_frames_kernel<PAIR_THREADS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->L.total));
+    CK(cudaFuncSetAttribute(pair_kernel_fn(ctx->small_path, p->track_near != 0), cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->L.total));
     // binning kernel variant: registers hold the frame's pair atoms when they fit (one HBM pass), else three gather passes
     ctx->bin_variant = T.n_pair <= 512 * 8 ? 1 : (T.n_pair <= 1024 * 8 ? 2 : 0);
     // frames that fit in shared memory stream through bulk async copies (bin_tma_kernel.cuh)
@@ -351,6 +360,7 @@ extern "C" int chc_create(chc_ctx** out, const chc_topology* t, const chc_params
     ctx->st.path = ctx->small_path ? 1 : 2; ctx->st.smem_bytes = ctx->L.total; ctx->st.threads = PAIR_THREADS;
     ctx->st.grid = ctx->pair_grid; ctx->st.bin_smem_bytes = ctx->bin_smem; ctx->st.bin_grid = ctx->bin_grid;
     ctx->st.chunk_frames = ctx->chunk_frames; ctx->st.record_bytes = ctx->B.stride;
+    ctx->st.bin_variant = ctx->bin_variant; ctx->st.bin_apt = ctx->bin_tma ? ctx->tma_apt : 0;
     return CHC_OK;
 }
 
@@ -419,12 +429,14 @@ static int submit_impl(chc_ctx* ctx, int state, const float* d_xyz, const long l
     const bool continues = (first_index % F) != 0;
     if (continues && !(ctx->last_state == state && ctx->next_index == first_index))
         return fail(ctx, CHC_E_ORDER, "submit_frames: chunk starts at %lld, inside a %d-frame fragment it does not continue", (long long)first_index, F);
+    if (continues && ctx->hp_last_slot > 0) {
+        // the fragment being continued was computed into slot hp_last_slot by the previous call; it moves to slot 0 BEFORE the
+        // mask buffer may grow (ensure_hpmask carries slot 0 over into a fresh buffer)
+        CK(cudaMemcpyAsync(ctx->hpmask, ctx->hpmask + (size_t)ctx->hp_last_slot * ctx->T.n_pair, ctx->T.n_pair, cudaMemcpyDeviceToDevice, stream));
+        ctx->hp_last_slot = 0;
+    }
     int rc = ensure_hpmask(ctx, frag1 - frag0 + 1);
     if (rc != CHC_OK) return rc;
-    if (continues && ctx->hp_last_slot > 0) {
-        // the fragment being continued was computed into slot hp_last_slot by the previous call
-        CK(cudaMemcpyAsync(ctx->hpmask, ctx->hpmask + (size_t)ctx->hp_last_slot * ctx->T.n_pair, ctx->T.n_pair, cudaMemcpyDeviceToDevice, stream));
-    }
     ctx->hp_last_slot = (int)(frag1 - frag0);
     DevOut O;
     O.counts = ctx->counts + (size_t)state * ctx->n_pairs; O.n_pairs = ctx->n_pairs;
@@ -470,12 +482,12 @@ static int submit_impl(chc_ctx* ctx, int state, const float* d_xyz, const long l
             }
         }
         const int grid = std::min(n, ctx->pair_grid);
-        if (ctx->small_path)
-            pair_frames_kernel<PAIR_THREADS, true><<<grid, PAIR_THREADS, ctx->L.total, stream>>>(
-                ctx->T, ctx->P, O, ctx->L, ctx->B, ctx->binned, n, first_index + c0, F, frag0, ctx->hpmask, nullptr, nullptr, ctx->wscratch);
-        else
-            pair_frames_kernel<PAIR_THREADS, false><<<grid, PAIR_THREADS, ctx->L.total, stream>>>(
-                ctx->T, ctx->P, O, ctx->L, ctx->B, ctx->binned, n, first_index + c0, F, frag0, ctx->hpmask, ctx->gstamp, ctx->gstate, ctx->wscratch);
+        {
+            int nn = n; long long fi = first_index + c0, fr0 = frag0; int ff = F;
+            unsigned* gs = ctx->small_path ? nullptr : ctx->gstamp; unsigned* gt = ctx->small_path ? nullptr : ctx->gstate;
+            void* args[] = {&ctx->T, &ctx->P, &O, &ctx->L, &ctx->B, &ctx->binned, &nn, &fi, &ff, &fr0, &ctx->hpmask, &gs, &gt, &ctx->wscratch};
+            CK(cudaLaunchKernel(pair_kernel_fn(ctx->small_path, ctx->P.track_near != 0), dim3(grid), dim3(PAIR_THREADS), args, ctx->L.total, stream));
+        }
         CK(cudaGetLastError());
         if (ctx->timing) { CK(cudaEventRecord(ev.c, stream)); ctx->ev_pending.push_back(ev); }
         ctx->st.kernel_launches += 2;

@@ -36,6 +36,8 @@
 #define C_NEARV 16u   // within near_dist_tol of the vdW cutoff
 #define C_NEARH 32u   // ... of the hydrophobic (same) cutoff
 #define C_HBW   64u   // hydrogen-bond candidate between a non-solvent atom and a solvent atom (water-bridge edge)
+#define C_NEARS 128u  // ion pair within near_dist_tol of the salt-bridge cutoff
+#define C_NEARB 256u  // donor / acceptor heavy pair (or water edge) within near_dist_tol of the hydrogen-bond distance cutoff
 
 struct DevTopo {
     int n_atoms, n_pair, n_aux, n_h, n_rings, n_cat, n_dis, K, R, n_hp_base, same;
@@ -66,6 +68,7 @@ struct DevParams {
     float hb_tan_lo, hb_tan_hi; int hb_fast;   // tangent bracket of the cutoff (frame_phases.cuh hb_direction)
     float ring_pre2;       // conservative centroid prefilter for pc/ps/ts
     float ps_soft2, ts_soft2, pc_soft2;
+    double ps_soft, ts_soft, pc_soft;
     double pc_dist, pc_angle, ps_dist, ps_angle, ps_psi, ts_dist, ts_angle, ts_psi;
     double sb_dist, hb_dist, hp_dist, soft;
     double near_d, near_a;

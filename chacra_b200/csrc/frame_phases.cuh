@@ -16,6 +16,7 @@ struct FrameCtx {            // per-CTA view of the current frame (shared memory
 };
 
 // ---- R: pi-cation ----------------------------------------------------------------------------------
+template <bool TN>
 __device__ __forceinline__ void ring_pc_task(const DevTopo& T, const DevParams& P, const DevOut& O, const FrameCtx& F,
                                              int c, int r) {
     const int* pa = T.ring_pc_aux + 3 * r;
@@ -30,6 +31,8 @@ __device__ __forceinline__ void ring_pc_task(const DevTopo& T, const DevParams& 
     // measure contacts 10.0: every ring atom must be selected against the cation, within the soft cutoff, unbonded
     unsigned cf = T.cat_flags[c];
     int catom = T.cat_atom[c];
+    bool soft_fail = false;              // some ring atom lies just above the soft cutoff (inside the near band)
+    int near_atom[3]; double near_dl[3]; int n_near = 0;
     for (int k = 0; k < 3; ++k) {
         // ring_pc_aux is a permutation of ring_sel_aux; find the matching selection flags / atom index
         int slot = pa[k], q = 0;
@@ -39,17 +42,25 @@ __device__ __forceinline__ void ring_pc_task(const DevTopo& T, const DevParams& 
         bool dir = ((cf & 1u) && (rf & 2u)) || (!T.same && (cf & 2u) && (rf & 1u));
         if (!dir || ratom == catom) return;
         const float* pr = F.aux + 3 * slot;
-        if (dist2_exact(xc[0], xc[1], xc[2], pr[0], pr[1], pr[2]) > P.pc_soft2) return;
+        const float d2k = dist2_exact(xc[0], xc[1], xc[2], pr[0], pr[1], pr[2]);
+        if (TN) {
+            const double dl = (double)sqrtf(d2k) - P.pc_soft;
+            if (fabs(dl) < P.near_d) { near_atom[n_near] = ratom; near_dl[n_near] = dl; ++n_near; }
+            if (d2k > P.pc_soft2) { if (!(dl < P.near_d)) return; soft_fail = true; }
+        } else if (d2k > P.pc_soft2) return;
     }
     D3 a = d3(p1), b = d3(p2), cc = d3(p3), x = d3(xc);
     D3 cen = centroid3(a, b, cc);
     D3 v = sub3(x, cen);
     double d = sqrt(dot3(v, v));
     int rep = T.ring_rep[r];
-    if (P.track_near && fabs(d - P.pc_dist) < P.near_d) emit_near(O, F.frame, CHC_NEAR_PC_DIST, catom, rep, d - P.pc_dist);
+    if (n_near > 0 && d - P.pc_dist < P.near_d)       // the soft 10 A search decides this group (pi_cation.py:22,70,98)
+        for (int k = 0; k < n_near; ++k) emit_near(O, F.frame, CHC_NEAR_PC_SOFT, catom, near_atom[k], near_dl[k]);
+    if (soft_fail) return;
+    if (TN && fabs(d - P.pc_dist) < P.near_d) emit_near(O, F.frame, CHC_NEAR_PC_DIST, catom, rep, d - P.pc_dist);
     if (d > P.pc_dist) return;
     double t = fold180(angle_deg(normal3(a, b, cc), v));
-    if (P.track_near && fabs(t - P.pc_angle) < P.near_a) emit_near(O, F.frame, CHC_NEAR_PC_ANGLE, catom, rep, t - P.pc_angle);
+    if (TN && fabs(t - P.pc_angle) < P.near_a) emit_near(O, F.frame, CHC_NEAR_PC_ANGLE, catom, rep, t - P.pc_angle);
     if (t > P.pc_angle) return;
     count_pair(O, F.bits, F.gen, T.cat_res[c], T.ring_res[r], T.R);
     if (P.emit) {
@@ -59,6 +70,7 @@ __device__ __forceinline__ void ring_pc_task(const DevTopo& T, const DevParams& 
 }
 
 // ---- R: pi-stacking and T-stacking ---------------------------------------------------------------------
+template <bool TN>
 __device__ __forceinline__ void ring_stack_task(const DevTopo& T, const DevParams& P, const DevOut& O, const FrameCtx& F,
                                                 int r1, int r2) {
     if (T.ring_res[r1] == T.ring_res[r2]) return;
@@ -82,7 +94,15 @@ __device__ __forceinline__ void ring_stack_task(const DevTopo& T, const DevParam
     }
     hit_ps = (P.itypes & CHC_IT_PS) && best <= P.ps_soft2;
     hit_ts = (P.itypes & CHC_IT_TS) && best <= P.ts_soft2;
-    if (!(hit_ps || hit_ts) || t1[0] < 0 || t2[0] < 0) return;
+    // the closest selected ring-atom pair within the near band of a soft search cutoff (aromatics.py:26-27,166)
+    double soft_ps = 1.0, soft_ts = 1.0;
+    if (TN && best < 3.0e38f) {
+        const double db = (double)sqrtf(best);
+        if (P.itypes & CHC_IT_PS) soft_ps = db - P.ps_soft;
+        if (P.itypes & CHC_IT_TS) soft_ts = db - P.ts_soft;
+    }
+    const bool near_ps = fabs(soft_ps) < P.near_d, near_ts = fabs(soft_ts) < P.near_d;
+    if (!(hit_ps || hit_ts || near_ps || near_ts) || t1[0] < 0 || t2[0] < 0) return;
     D3 a1 = d3(F.aux + 3 * t1[0]), a2 = d3(F.aux + 3 * t1[1]), a3 = d3(F.aux + 3 * t1[2]);
     D3 b1 = d3(F.aux + 3 * t2[0]), b2 = d3(F.aux + 3 * t2[1]), b3 = d3(F.aux + 3 * t2[2]);
     D3 c1 = centroid3(a1, a2, a3), c2 = centroid3(b1, b2, b3);
@@ -94,10 +114,12 @@ __device__ __forceinline__ void ring_stack_task(const DevTopo& T, const DevParam
     bool have_ang = false;
     for (int which = 0; which < 2; ++which) {
         bool on = which == 0 ? hit_ps : hit_ts;
-        if (!on) continue;
         double dcut = which == 0 ? P.ps_dist : P.ts_dist, acut = which == 0 ? P.ps_angle : P.ts_angle,
                pcut = which == 0 ? P.ps_psi : P.ts_psi;
-        if (P.track_near && fabs(d - dcut) < P.near_d)
+        if ((which == 0 ? near_ps : near_ts) && d - dcut < P.near_d)
+            emit_near(O, F.frame, which == 0 ? CHC_NEAR_PS_SOFT : CHC_NEAR_TS_SOFT, rep1, rep2, which == 0 ? soft_ps : soft_ts);
+        if (!on) continue;
+        if (TN && fabs(d - dcut) < P.near_d)
             emit_near(O, F.frame, which == 0 ? CHC_NEAR_PS_DIST : CHC_NEAR_TS_DIST, rep1, rep2, d - dcut);
         if (d > dcut) continue;
         if (!have_ang) {
@@ -106,10 +128,10 @@ __device__ __forceinline__ void ring_stack_task(const DevTopo& T, const DevParam
             have_ang = true;
         }
         double v = which == 0 ? fold180(ang) : fabs(ang - 90.0);
-        if (P.track_near && fabs(v - acut) < P.near_a)
+        if (TN && fabs(v - acut) < P.near_a)
             emit_near(O, F.frame, which == 0 ? CHC_NEAR_PS_ANGLE : CHC_NEAR_TS_ANGLE, rep1, rep2, v - acut);
         if (v > acut) continue;
-        if (P.track_near && fabs(psi - pcut) < P.near_a)
+        if (TN && fabs(psi - pcut) < P.near_a)
             emit_near(O, F.frame, which == 0 ? CHC_NEAR_PS_PSI : CHC_NEAR_TS_PSI, rep1, rep2, psi - pcut);
         if (psi > pcut) continue;
         count_pair(O, F.bits, F.gen, T.ring_res[r1], T.ring_res[r2], T.R);
@@ -133,6 +155,7 @@ __device__ __forceinline__ bool e2_may_classify(const DevParams& P, const FrameC
 }
 
 // ---- E2: exact float32 d2 and class tests for one prefilter survivor ---------------------------------------
+template <bool TN>
 __device__ __forceinline__ unsigned e2_classify(const DevTopo& T, const DevParams& P, const FrameCtx& F, float4 a, float4 b,
                                                 float& d2_out) {
     float d2 = dist2_exact(a.x, a.y, a.z, b.x, b.y, b.z);
@@ -141,17 +164,25 @@ __device__ __forceinline__ unsigned e2_classify(const DevTopo& T, const DevParam
     bool dual = ((wi & I_S1) && (wj & I_S2)) || ((wi & I_S2) && (wj & I_S1));
     // water-bridge edge: exactly one solvent atom, the other in the hydrogen-bond selection U; needs no dual selection
     // (hbonds.py:78-80) and is dropped only inside one residue (:131)
-    const bool edge = (P.itypes & CHC_IT_HB) && ((wi ^ wj) & I_SOLV) && (((wi & I_SOLV) ? wj : wi) & I_HBU) &&
-                      ((wi | wj) & I_HASH) && d2 <= P.hb2;
-    if (!dual && !edge) return 0u;
+    const bool edge_pre = (P.itypes & CHC_IT_HB) && ((wi ^ wj) & I_SOLV) && (((wi & I_SOLV) ? wj : wi) & I_HBU) &&
+                          ((wi | wj) & I_HASH);
+    const bool edge = edge_pre && d2 <= P.hb2;
+    // near-cutoff bands of the two plain distance cutoffs (salt_bridges.py:76-80, hbonds.py:64-82)
+    bool band_sb = false, band_hb = false;
+    if (TN) {
+        const double dd = (double)sqrtf(d2);
+        band_sb = fabs(dd - P.sb_dist) < P.near_d; band_hb = fabs(dd - P.hb_dist) < P.near_d;
+    }
+    const bool edge_near = edge_pre && band_hb;
+    if (!dual && !edge && !edge_near) return 0u;
     int dl = abs(F.lkey[wi >> I_PIDX_SHIFT] - F.lkey[wj >> I_PIDX_SHIFT]);
-    if (!dual) return (edge && dl != 0) ? C_HBW : 0u;
+    if (!dual) return dl != 0 ? ((edge ? C_HBW : 0u) | (edge_near ? C_NEARB : 0u)) : 0u;
     int e = (wi & I_ELEM) * T.K + (wj & I_ELEM);
     unsigned cls = 0;
     if (dl >= P.vdw_rd) {
         if ((P.itypes & CHC_IT_VDW) && (wi & wj & I_VDW)) {
             if (d2 <= F.tv[e]) cls |= C_VDW;
-            if (P.track_near && d2 <= P.soft2 && fabs((double)sqrtf(d2) - T.vcut[e]) < P.near_d) cls |= C_NEARV;
+            if (TN && d2 <= P.soft2 && fabs((double)sqrtf(d2) - T.vcut[e]) < P.near_d) cls |= C_NEARV;
         }
         if ((P.itypes & CHC_IT_HP) && d2 <= P.hp2) {
             // static base-carbon bits first, then this fragment's membership (hydrophobics.py:8-41)
@@ -164,15 +195,20 @@ __device__ __forceinline__ unsigned e2_classify(const DevTopo& T, const DevParam
                                     ((wj & I_HP1) && (hj & 1u) && (wi & I_HP2) && (hi & 2u)));
                 if (hp) {
                     if (d2 <= F.th[e]) cls |= C_HP;
-                    if (P.track_near && fabs((double)sqrtf(d2) - T.vcut[e]) < P.near_d) cls |= C_NEARH;
+                    if (TN && fabs((double)sqrtf(d2) - T.vcut[e]) < P.near_d) cls |= C_NEARH;
                 }
             }
         }
     }
-    if ((P.itypes & CHC_IT_SB) && d2 <= P.sb2 &&
-        (((wi & I_ANION) && (wj & I_CATION)) || ((wj & I_ANION) && (wi & I_CATION)))) cls |= C_SB;
-    if ((P.itypes & CHC_IT_HB) && d2 <= P.hb2 && (wi & wj & I_HBU) && ((wi | wj) & I_HASH) && dl >= P.hb_rd) cls |= C_HB;
-    if (edge && dl != 0) cls |= C_HBW;
+    if ((P.itypes & CHC_IT_SB) && (((wi & I_ANION) && (wj & I_CATION)) || ((wj & I_ANION) && (wi & I_CATION)))) {
+        if (d2 <= P.sb2) cls |= C_SB;
+        if (band_sb) cls |= C_NEARS;
+    }
+    if ((P.itypes & CHC_IT_HB) && (wi & wj & I_HBU) && ((wi | wj) & I_HASH) && dl >= P.hb_rd) {
+        if (d2 <= P.hb2) cls |= C_HB;
+        if (band_hb) cls |= C_NEARB;
+    }
+    if (dl != 0) cls |= (edge ? C_HBW : 0u) | (edge_near ? C_NEARB : 0u);
     return cls;
 }
 
@@ -181,6 +217,7 @@ __device__ __forceinline__ unsigned e2_classify(const DevTopo& T, const DevParam
 // monotone in |u x v| / (u.v), so away from the cutoff the decision follows from one multiply: P.hb_tan_lo / hb_tan_hi
 // bracket tan(cutoff) by a relative 4e-4 (~7e-3 degree at 70 degrees, far above every rounding step of the exact recipe
 // and above the 1e-3 degree near-cutoff band); only inside the bracket is the exact double-precision atan2 evaluated.
+template <bool TN>
 __device__ __forceinline__ bool hb_direction(const DevTopo& T, const DevParams& P, const DevOut& O, const FrameCtx& F,
                                              float4 d, float4 a, int pd, int atom_d, int atom_a, bool report = true) {
     bool ok = false;
@@ -198,7 +235,7 @@ __device__ __forceinline__ bool hb_direction(const DevTopo& T, const DevParams& 
             if (pcos <= 0.f || psin > pcos * P.hb_tan_hi) continue;                    // surely above it
         }
         float ang = 57.2958f * (float)atan2((double)psin, (double)pcos);
-        if (report && P.track_near && fabs((double)ang - (double)P.hb_angle) < P.near_a)
+        if (report && TN && fabs((double)ang - (double)P.hb_angle) < P.near_a)
             emit_near(O, F.frame, CHC_NEAR_HB_ANGLE, atom_d, atom_a, (double)ang - (double)P.hb_angle);
         ok |= ang < P.hb_angle;
     }
@@ -206,6 +243,7 @@ __device__ __forceinline__ bool hb_direction(const DevTopo& T, const DevParams& 
 }
 
 // ---- E3: everything that needs the global tables, for one classified pair ---------------------------------------
+template <bool TN>
 __device__ __forceinline__ void e3_finish(const DevTopo& T, const DevParams& P, const DevOut& O, const FrameCtx& F,
                                           int i, int j, unsigned cls) {
     float4 a = F.spos[i], b = F.spos[j];
@@ -215,10 +253,12 @@ __device__ __forceinline__ void e3_finish(const DevTopo& T, const DevParams& P, 
     int ai = T.pair_atom[pi], aj = T.pair_atom[pj];
     const unsigned si = T.pair_info[pi], sj = T.pair_info[pj];       // static-only bits: ligand, backbone, CYS, xbond
     // directly bonded pairs are excluded by measure contacts / measure hbonds (Appendix A.4, A.5)
-    bool need_bond = (cls & (C_SB | C_HB | C_HBW)) || ((si & I_XBOND) && (sj & I_XBOND));
+    bool need_bond = (cls & (C_SB | C_HB | C_HBW | C_NEARS | C_NEARB)) || ((si & I_XBOND) && (sj & I_XBOND));
     if (need_bond && is_bonded(T, pi, aj)) return;
     int ri = T.pair_res[pi], rj = T.pair_res[pj];
     float dist = sqrtf(d2);
+    if (cls & C_NEARS) emit_near(O, F.frame, CHC_NEAR_SB_DIST, ai, aj, (double)dist - P.sb_dist);
+    if (cls & C_NEARB) emit_near(O, F.frame, CHC_NEAR_HB_DIST, ai, aj, (double)dist - P.hb_dist);
     if (cls & (C_VDW | C_HP | C_NEARV | C_NEARH)) {
         bool ss = (si & I_CYS) && (sj & I_CYS) && is_disulfide(T, T.pair_resid[pi], T.pair_resid[pj]);
         if (!ss) {
@@ -242,7 +282,12 @@ __device__ __forceinline__ void e3_finish(const DevTopo& T, const DevParams& P, 
         int aa = ij ? ai : aj, ac = ij ? aj : ai;
         bool al = wa & I_LIG, cl = wc & I_LIG;
         if (!(al && cl)) count_pair(O, F.bits, F.gen, ri, rj, T.R);
-        if (P.emit) emit_contact(O, F.frame, al ? (cl ? CHC_SBLL : CHC_SBLP) : (cl ? CHC_SBPL : CHC_SB), aa, ac, dist);
+        if (P.emit) {
+            emit_contact(O, F.frame, al ? (cl ? CHC_SBLL : CHC_SBLP) : (cl ? CHC_SBPL : CHC_SB), aa, ac, dist);
+            // the reference's if / if / if-else also appends a plain `sb` line behind an `sblp` or `sbpl` one (salt_bridges.py:90-97):
+            // it is the line get_contact_frequencies counts
+            if (al != cl) emit_contact(O, F.frame, CHC_SB, aa, ac, dist);
+        }
     }
     if (cls & (C_HB | C_HBW)) {
         bool ok = false;
@@ -251,7 +296,7 @@ __device__ __forceinline__ void e3_finish(const DevTopo& T, const DevParams& P, 
             const unsigned wd = dir ? wj : wi;
             if (!(wd & I_HASH)) continue;
             const float4 xd = dir ? b : a, xa = dir ? a : b;
-            ok |= hb_direction(T, P, O, F, xd, xa, dir ? pj : pi, dir ? aj : ai, dir ? ai : aj, (cls & C_HB) != 0);
+            ok |= hb_direction<TN>(T, P, O, F, xd, xa, dir ? pj : pi, dir ? aj : ai, dir ? ai : aj, (cls & C_HB) != 0);
         }
         if (ok && (cls & C_HBW)) {
             // record the edge with the solvent atom: neighbour = sorted slot of the non-solvent atom (hbonds.py:126-142)

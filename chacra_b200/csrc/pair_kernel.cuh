@@ -54,7 +54,8 @@ struct PairMisc {
     int nmark;                  // waters with at least one hydrogen bond to a non-solvent atom (this frame)
 };
 
-template <int THREADS, bool SMALL>
+// TN: the near-cutoff side channel is compiled in (chc_params.track_near); the counts-only production path carries none of it
+template <int THREADS, bool SMALL, bool TN>
 __global__ void __launch_bounds__(THREADS, 1)
 pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, const unsigned char* __restrict__ binned,
                    int n_frames, long long first_index, int frag_frames, long long frag0,
@@ -264,9 +265,9 @@ CHC_UNROLL(E1_UNROLL)
                 unsigned cls = 0u; float d2 = 0.f; unsigned ei = 0u, ej = 0u;
                 if (lane < nb) {
                     qget(qf, QF_CAP, qfn + lane, ei, ej);
-                    cls = e2_classify(T, P, F, spos[ei], spos[ej], d2);
+                    cls = e2_classify<TN>(T, P, F, spos[ei], spos[ej], d2);
                 }
-                const bool polar = (cls & (C_SB | C_HB | C_HBW)) != 0u;
+                const bool polar = (cls & (C_SB | C_HB | C_HBW | C_NEARS | C_NEARB)) != 0u;
                 const unsigned balp = __ballot_sync(FULL, polar), balv = __ballot_sync(FULL, cls != 0u && !polar);
                 if (cls) {
                     const unsigned below = (1u << lane) - 1u;
@@ -288,7 +289,7 @@ CHC_UNROLL(E1_UNROLL)
                 if (lane < nb) {
                     unsigned ei, ej;
                     qget(q, Q2_CAP, qn + lane, ei, ej);
-                    e3_finish(T, P, O, F, (int)ei, (int)ej, q[QW * Q2_CAP + qn + lane]);
+                    e3_finish<TN>(T, P, O, F, (int)ei, (int)ej, q[QW * Q2_CAP + qn + lane]);
                 }
                 __syncwarp();
             }
@@ -306,14 +307,14 @@ CHC_UNROLL(E1_UNROLL)
                 if (u >= u_all) break;
                 if (u < u_pc) {
                     const int t = u * 32 + lane;
-                    if (t < n_pc) ring_pc_task(T, P, O, F, t / T.n_rings, t % T.n_rings);
+                    if (t < n_pc) ring_pc_task<TN>(T, P, O, F, t / T.n_rings, t % T.n_rings);
                 } else {
                     const int t = (u - u_pc) * 32 + lane;
                     if (t < n_st) {
                         int r2 = (int)((1.0f + sqrtf(1.0f + 8.0f * (float)t)) * 0.5f);
                         while (r2 * (r2 - 1) / 2 > t) --r2;
                         while ((r2 + 1) * r2 / 2 <= t) ++r2;
-                        ring_stack_task(T, P, O, F, t - r2 * (r2 - 1) / 2, r2);
+                        ring_stack_task<TN>(T, P, O, F, t - r2 * (r2 - 1) / 2, r2);
                     }
                 }
                 __syncwarp();
@@ -323,7 +324,7 @@ CHC_UNROLL(E1_UNROLL)
         // ---- W: water bridges from the (non-solvent, solvent) hydrogen bonds the pair phase recorded ----------------
         if (T.n_solv > 0 && (P.itypes & CHC_IT_HB)) {
             WaterScratch W = water_scratch(wscratch, blockIdx.x, T.n_solv);
-            water_bridges(T, P, O, F, W, cells, px, pxy, ncell, hdr, &M->nmark, tid, THREADS);
+            water_bridges<TN>(T, P, O, F, W, cells, px, pxy, ncell, hdr, &M->nmark, tid, THREADS);
             __syncthreads();
         }
     }

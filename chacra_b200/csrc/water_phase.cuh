@@ -28,7 +28,7 @@ __device__ __forceinline__ void bridge_emit(const DevTopo& T, const DevParams& P
                     sqrtf(dist2_exact(xa.x, xa.y, xa.z, xb.x, xb.y, xb.z)));
 }
 
-template <class cell_t>
+template <bool TN, class cell_t>
 __device__ __forceinline__ void water_bridges(const DevTopo& T, const DevParams& P, const DevOut& O, const FrameCtx& F,
                                               const WaterScratch& W, const cell_t* cells, int px, int pxy, int ncell,
                                               const BinHeader* hdr, const int* nmark, int tid, int nthreads) {
@@ -72,11 +72,15 @@ __device__ __forceinline__ void water_bridges(const DevTopo& T, const DevParams&
                     const int nj = min(W.cnt[ordj], WADJ);
                     if (nj == 0) continue;                                      // no non-solvent partner: cannot close a bridge
                     if (F.lkey[pw] == F.lkey[pj]) continue;                     // same residue (hbonds.py:131)
-                    if (dist2_exact(xw.x, xw.y, xw.z, xj.x, xj.y, xj.z) > P.hb2) continue;
+                    const float d2w = dist2_exact(xw.x, xw.y, xw.z, xj.x, xj.y, xj.z);
+                    const double dlw = TN ? (double)sqrtf(d2w) - P.hb_dist : 1.0;
+                    if (d2w > P.hb2 && !(fabs(dlw) < P.near_d)) continue;
                     if (!((ww | wj) & I_HASH) || is_bonded(T, pw, aj)) continue;
+                    if (fabs(dlw) < P.near_d) emit_near(O, F.frame, CHC_NEAR_HB_DIST, aw, aj, dlw);
+                    if (d2w > P.hb2) continue;
                     bool ok = false;
-                    if (ww & I_HASH) ok |= hb_direction(T, P, O, F, xw, xj, pw, aw, aj, false);
-                    if (!ok && (wj & I_HASH)) ok |= hb_direction(T, P, O, F, xj, xw, pj, aj, aw, false);
+                    if (ww & I_HASH) ok |= hb_direction<TN>(T, P, O, F, xw, xj, pw, aw, aj, false);
+                    if (!ok && (wj & I_HASH)) ok |= hb_direction<TN>(T, P, O, F, xj, xw, pj, aj, aw, false);
                     if (!ok) continue;
                     const int* Nj = W.adj + (size_t)ordj * WADJ;
                     for (int a = 0; a < nw; ++a)

@@ -26,7 +26,7 @@ COMPUTE_ORDER = ["sb", "pc", "ps", "ts", "vdw", "hb", "hp"]          # compute_c
 ITYPE_NAMES = ["sb", "sblp", "sbpl", "sbll", "pc", "ps", "ts", "vdw", "hbbb", "hbsb", "hbss", "hbll", "hblb", "hbls",
                "wb", "wb2", "lwb", "lwb2", "hp", "hplp", "hpll"]
 NEAR_KINDS = ["vdw_dist", "hp_dist", "hb_angle", "pc_dist", "pc_angle", "ps_dist", "ps_angle", "ps_psi", "ts_dist",
-              "ts_angle", "ts_psi", "sb_dist", "hb_dist"]
+              "ts_angle", "ts_psi", "sb_dist", "hb_dist", "pc_soft", "ps_soft", "ts_soft"]
 TRAJ_FRAG_SIZE = 100                                                  # compute_contacts.py:43
 
 CONTACT_DTYPE = np.dtype([("frame", "<i4"), ("itype", "<i4"), ("atom1", "<i4"), ("atom2", "<i4"), ("water1", "<i4"),
@@ -157,7 +157,11 @@ class ContactEngine:
                 raise ChacraError("host frames must have shape [F][%d][3]" % n)
             ptr, nf = xyz.ctypes.data, xyz.shape[0]
         self._check(self.lib.chc_submit_frames_host(self._ctx, state, ptr, nf, first_index, self._stream()))
-        self._keepalive = xyz
+        # asynchronous H2D copies read the caller's (pinned) buffer after this call returns: every submitted host
+        # array stays referenced until synchronize() / the next blocking read
+        self._keepalive = getattr(self, "_keepalive", [])
+        if not any(k is xyz for k in self._keepalive):
+            self._keepalive.append(xyz)
 
     def submit_indexed(self, pool, source_index, state: int = 0, first_index: int = 0):
         """Frame k of the submission is ``pool[source_index[k]]`` (replica -> state demultiplexing).
@@ -178,6 +182,7 @@ class ContactEngine:
 
     def synchronize(self):
         self._check(self.lib.chc_synchronize(self._ctx, self._stream()))
+        self._keepalive = []
 
     def counts(self, state: int = 0) -> np.ndarray:
         """int32 [P] residue-pair frame counts of one state (device -> host)."""

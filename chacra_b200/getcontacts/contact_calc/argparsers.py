@@ -37,7 +37,8 @@ def build_getcontact_parser(program_description, trajectory):
         req.add_argument("--trajectory", type=str, metavar="PATH", required=True, help="path to trajectory file")
     else:
         req.add_argument("--structure", type=str, metavar="PATH", required=True, help="path to structure file")
-    req.add_argument("--output", type=str, metavar="PATH", required=True, help="path to output file")
+    req.add_argument("--output", type=str, metavar="PATH", required=False, default=None,
+                     help="path to output file (required unless --no_contact_output is given)")
     req.add_argument("--itypes", type=str, nargs="+", required=True, metavar="STR",
                      help="Compute only these interaction types. Valid choices are:\n"
                           "* all, sb (salt-bridges), pc (pi-cation), ps (pi-stacking), ts (t-stacking),\n"
@@ -61,6 +62,10 @@ def build_getcontact_parser(program_description, trajectory):
                      help="also write the residue-pair frequency table from the device count table (extension)")
     opt.add_argument("--count_output", type=str, metavar="PATH", default=None,
                      help="also write the integer residue-pair frame counts behind that table (extension)")
+    opt.add_argument("--near_cutoff_output", type=str, metavar="PATH", default=None,
+                     help="list every pair within 1e-4 A / 1e-3 degree of a cutoff in this file (extension)")
+    opt.add_argument("--no_contact_output", default=False, action="store_true",
+                     help="skip the contact list: with --frequency_output / --count_output nothing but the count table leaves the GPU (extension)")
     geo = p.add_argument_group("Geometric criteria")
     for flag, typ, default, text in _GEOMETRY:
         geo.add_argument(flag, type=typ, metavar="FLOAT", default=default, help=text)

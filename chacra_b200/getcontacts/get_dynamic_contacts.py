@@ -36,6 +36,8 @@ def process_geometric_criterion_args(args):
 def main(argv=None):
     parser = ap.build_getcontact_parser(__doc__, True)
     args = parser.parse_args(argv)
+    if args.output is None and not args.no_contact_output:
+        parser.error("the following arguments are required: --output")
     sele2 = args.sele if args.sele2 is None else args.sele2
     end = args.end if args.end else sys.maxsize
     if "all" in args.itypes:
@@ -48,7 +50,8 @@ def main(argv=None):
     tic = datetime.datetime.now()
     compute_contacts(args.topology, args.trajectory, args.output, itypes, process_geometric_criterion_args(args),
                      args.cores, args.beg, end, args.stride, args.distout, args.ligand, args.solv, args.lipid,
-                     args.sele, sele2, device=args.device, frequency_output=args.frequency_output, count_output=args.count_output)
+                     args.sele, sele2, device=args.device, frequency_output=args.frequency_output, count_output=args.count_output,
+                     near_output=args.near_cutoff_output, write_contacts=not args.no_contact_output)
     print("\nTotal computation time:", (datetime.datetime.now() - tic).total_seconds(), "seconds")
     for k, v in (("topology", args.topology), ("trajectory", args.trajectory), ("output", args.output),
                  ("cores", args.cores), ("solv", args.solv), ("sele", args.sele), ("sele2", sele2), ("stride", args.stride)):

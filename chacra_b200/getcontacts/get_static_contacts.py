@@ -20,6 +20,8 @@ from get_dynamic_contacts import ALL_ITYPES, process_geometric_criterion_args  #
 def main(argv=None):
     parser = ap.build_getcontact_parser(__doc__, False)
     args = parser.parse_args(argv)
+    if args.output is None and not args.no_contact_output:
+        parser.error("the following arguments are required: --output")
     sele2 = args.sele if args.sele2 is None else args.sele2
     if "all" in args.itypes:
         itypes = ALL_ITYPES
@@ -31,7 +33,8 @@ def main(argv=None):
     tic = datetime.datetime.now()
     compute_contacts(args.structure, args.structure, args.output, itypes, process_geometric_criterion_args(args), 1, 0, 0, 1,
                      args.distout, args.ligand, args.solv, args.lipid, args.sele, sele2, device=args.device,
-                     frequency_output=args.frequency_output, count_output=args.count_output)
+                     frequency_output=args.frequency_output, count_output=args.count_output,
+                     near_output=args.near_cutoff_output, write_contacts=not args.no_contact_output)
     print("\nTotal computation time: " + str((datetime.datetime.now() - tic).total_seconds()) + " seconds")
     for k, v in (("topology", args.structure), ("trajectory", args.structure), ("output", args.output), ("solv", args.solv),
                  ("sele", args.sele), ("sele2", sele2)):

@@ -125,6 +125,10 @@ class DCDFile(FileStager):
                                         out[cuts[c]:].data_ptr(), 0, self.device, stream)
                 if rc != 0:
                     raise RuntimeError("chc_dcd_unpack failed (%d)" % rc)
+            # the pinned staging buffers belong to the reader: the next read_device call refills them straight away, so the
+            # copies out of them must have finished before this call returns (the unpack kernels may still be running)
+            for k in range(min(2, len(cuts) - 1)):
+                copied[k].synchronize()
         return out
 
 

@@ -59,7 +59,9 @@ enum chc_itype {
 enum chc_near_kind {
     CHC_NEAR_VDW_DIST = 0, CHC_NEAR_HP_DIST, CHC_NEAR_HB_ANGLE, CHC_NEAR_PC_DIST, CHC_NEAR_PC_ANGLE,
     CHC_NEAR_PS_DIST, CHC_NEAR_PS_ANGLE, CHC_NEAR_PS_PSI, CHC_NEAR_TS_DIST, CHC_NEAR_TS_ANGLE,
-    CHC_NEAR_TS_PSI, CHC_NEAR_SB_DIST, CHC_NEAR_HB_DIST
+    CHC_NEAR_TS_PSI, CHC_NEAR_SB_DIST, CHC_NEAR_HB_DIST,
+    /* soft `measure contacts` cutoffs of the ring detectors (pi_cation.py:22,70; aromatics.py:26-27,166) */
+    CHC_NEAR_PC_SOFT, CHC_NEAR_PS_SOFT, CHC_NEAR_TS_SOFT, CHC_N_NEAR_KINDS
 };
 
 /* error codes */
@@ -178,6 +180,8 @@ typedef struct chc_stats {
     double  pair_ms_total;        /* CUDA-event time of the pair kernels since chc_set_timing(1) */
     double  bin_ms_total;         /* ... of the binning kernels */
     int64_t timed_chunks;
+    int32_t bin_variant;          /* binning kernel: 3 / 4 = bulk-copy (two CTAs per SM / double buffered), 1 / 2 = registers, 0 = gather */
+    int32_t bin_apt;              /* pair atoms per thread of the bulk-copy binning kernel (template instantiation) */
 } chc_stats;
 
 typedef struct chc_ctx chc_ctx;

@@ -566,6 +566,29 @@ def measure_contacts(top: Topology, xyz, m1, m2, cutoff: float, one_selection=Fa
     return np.stack([a[keep], b[keep]], axis=1)
 
 
+NEAR_DIST_TOL = 1e-4     # Angstrom (north star: pairs within 1e-4 A / 1e-3 degree of a cutoff are listed separately)
+NEAR_ANGLE_TOL = 1e-3
+
+
+def contacts_band(top: Topology, xyz, m1, m2, cutoff: float, one_selection=False):
+    """Oracle-only companion of ``measure_contacts`` for the near-cutoff side channel (not reference behaviour):
+    every non-bonded pair (i in s1, j in s2, i != j) whose float32 ``sqrtf(d2)`` is below ``cutoff + 1e-4``, as
+    (i, j, delta) with delta = (double)sqrtf(d2) - cutoff.  |delta| < 1e-4 marks the pairs whose membership in
+    ``measure contacts cutoff`` rests on the weakly pinned <= / < at the float32 boundary."""
+    i1 = np.nonzero(m1)[0]
+    i2 = i1 if one_selection else np.nonzero(m2)[0]
+    p = _candidate_pairs(xyz[i1], xyz[i2], cutoff + 4 * NEAR_DIST_TOL, same=one_selection)
+    out = []
+    if len(p) == 0:
+        return out
+    a, b = i1[p[:, 0]], i2[p[:, 1]]
+    d = np.sqrt(_d2(xyz[a], xyz[b])).astype(F32).astype(np.float64) - float(cutoff)
+    for u, v, dl in zip(a.tolist(), b.tolist(), d.tolist()):
+        if u != v and dl < NEAR_DIST_TOL and not top.bonded(u, v):
+            out.append((u, v, dl))
+    return out
+
+
 def hbond_angle_f32(xd, xh, xa) -> np.float32:
     """Appendix A.5: 57.2958f * (float)atan2(|u x v|, u.v), u = h-d, v = a-h, float32 products."""
     u = (xh - xd).astype(F32)
@@ -641,9 +664,14 @@ class FragmentState(dict):
     """The per-fragment cache the reference keeps inside geom_criteria (Appendix A.8)."""
 
 
-def compute_salt_bridges(S: Setup, xyz, geom):
+def compute_salt_bridges(S: Setup, xyz, geom, near=None):
     top = S.top
     cut = geom['SALT_BRIDGE_CUTOFF_DISTANCE']
+    if near is not None:     # salt_bridges.py:76-80: the 4.0 A `measure contacts` boundary
+        band = contacts_band(top, xyz, S.anion & S.sele1, S.cation & S.sele2, cut)
+        if not S.same:
+            band += contacts_band(top, xyz, S.anion & S.sele2, S.cation & S.sele1, cut)
+        near += [("sb_dist", a, c, dl) for a, c, dl in band if abs(dl) < NEAR_DIST_TOL]
     p12 = measure_contacts(top, xyz, S.anion & S.sele1, S.cation & S.sele2, cut)
     pairs = set(map(tuple, p12.tolist()))
     if not S.same:
@@ -679,6 +707,23 @@ def compute_pi_cation(S: Setup, xyz, geom, near=None):
         groups[(c, top.reslabel(r))].add(r)
     out = []
     x64 = xyz.astype(np.float64)
+    if near is not None:
+        # pi_cation.py:22,70: the soft 10 A `measure contacts` decides whether a ring's three atoms all reach the group.
+        # Listed only where it can change the outcome: all three atoms inside 10 A + 1e-4 and the centroid within the
+        # hard distance cutoff (+ 1e-4).
+        band = contacts_band(top, xyz, S.prot_cation & S.sele1, S.ring & S.sele2, 10.0)
+        if not S.same:
+            band += contacts_band(top, xyz, S.prot_cation & S.sele2, S.ring & S.sele1, 10.0)
+        wide = defaultdict(dict)
+        for c, r, dl in band:
+            wide[(c, top.reslabel(r))][r] = dl
+        for (c, _), ring in wide.items():
+            if len(ring) != 3 or not any(abs(dl) < NEAR_DIST_TOL for dl in ring.values()):
+                continue
+            p = sorted(ring)
+            cen = _centroid(x64[p[0]], x64[p[1]], x64[p[2]])
+            if float(np.linalg.norm(x64[c] - cen)) - cd < NEAR_DIST_TOL:
+                near += [("pc_soft", c, r, dl) for r, dl in ring.items() if abs(dl) < NEAR_DIST_TOL]
     for (c, _), ring in sorted(groups.items(), key=lambda kv: (kv[0][0], min(kv[1]))):
         if len(ring) != 3:
             continue
@@ -730,6 +775,29 @@ def compute_aromatics(S: Setup, xyz, itype, soft, dist_cut, ang_cut, psi_cut, ne
             res_pairs.append((ra, rb))
     out = []
     x64 = xyz.astype(np.float64)
+    if near is not None:
+        # aromatics.py:26-27,166: the soft `measure contacts` (ps 10 A, ts 6 A) finds a residue pair through its CLOSEST
+        # selected ring-atom pair; listed when that closest distance is within 1e-4 A of the soft cutoff and the centroids
+        # are within the hard distance cutoff (+ 1e-4).
+        best = {}
+        for a, b, dl in contacts_band(top, xyz, sel, sel, soft, one_selection=True):
+            if not ((S.sele1[a] and S.sele2[b]) or (S.sele2[a] and S.sele1[b])):
+                continue
+            ra, rb = top.reslabel(a), top.reslabel(b)
+            if ra == rb:
+                continue
+            key = (min(ra, rb), max(ra, rb))
+            if key not in best or dl < best[key][0]:
+                best[key] = (dl, a, b)
+        for (ra, rb), (dl, a, b) in best.items():
+            if abs(dl) >= NEAR_DIST_TOL:
+                continue
+            t1, t2 = _aromatic_triplet(S, a), _aromatic_triplet(S, b)
+            if len(t1) != 3 or len(t2) != 3:
+                continue
+            c1, c2 = _centroid(*(x64[k] for k in t1)), _centroid(*(x64[k] for k in t2))
+            if float(np.linalg.norm(c1 - c2)) - dist_cut < NEAR_DIST_TOL:
+                near.append((itype + "_soft", _ring_rep(top, t1), _ring_rep(top, t2), dl))
     for ra, rb in res_pairs:
         t1, t2 = trip[ra], trip[rb]
         if len(t1) != 3 or len(t2) != 3:
@@ -860,6 +928,17 @@ def compute_hydrogen_bonds(S: Setup, xyz, geom, near=None):
     dual = lambda a, b: (S.sele1[a] and S.sele2[b]) or (S.sele2[a] and S.sele1[b])
     SS = measure_hbonds(top, xyz, U, U, cd, ca, one_selection=True, near=near,
                         near_filter=lambda d, a: dual(d, a) and not _local(top, d, a, rd))
+    has_h = getattr(top, "_has_h", None)
+    if has_h is None:
+        has_h = np.zeros(top.n, dtype=bool)
+        for i, nb in top.neigh.items():
+            if any(top.is_h[h] for h in nb):
+                has_h[i] = True
+        top._has_h = has_h
+    heavy = ~top.is_h
+    if near is not None:     # hbonds.py:75-82: the donor-acceptor distance of `measure hbonds` (heavy pairs with a hydrogen)
+        near += [("hb_dist", u, v, dl) for u, v, dl in contacts_band(top, xyz, U & heavy, U & heavy, cd, one_selection=True)
+                 if abs(dl) < NEAR_DIST_TOL and (has_h[u] or has_h[v]) and dual(u, v) and not _local(top, u, v, rd)]
     out = []
     for d, a in sorted(SS):
         if not dual(d, a):
@@ -881,6 +960,12 @@ def compute_hydrogen_bonds(S: Setup, xyz, geom, near=None):
         else:
             t = "hbsb"
         out.append((t, d, a))
+    if near is not None and S.solv.any():
+        # water edges (hbonds.py:64-80): a solvent heavy atom matters through its hydrogen bond to a selection atom; that
+        # bond's 3.5 A distance test is also what puts the water into the `within 3.5` shell, one float32 comparison.
+        same_res = lambda u, v: top.chain[u] == top.chain[v] and top.resid[u] == top.resid[v]
+        near += [("hb_dist", u, v, dl) for u, v, dl in contacts_band(top, xyz, U & heavy, S.solv & heavy, cd)
+                 if abs(dl) < NEAR_DIST_TOL and (has_h[u] or has_h[v]) and not same_res(u, v)]
     if not W.any():
         return out
     SW = measure_hbonds(top, xyz, U, W, cd, ca) | measure_hbonds(top, xyz, W, U, cd, ca)
@@ -893,6 +978,14 @@ def compute_hydrogen_bonds(S: Setup, xyz, geom, near=None):
             wd[d].add(a)
         if S.solv[a]:
             wd[a].add(d)
+    if near is not None:
+        # water-water bonds decide a two-water bridge only between waters that each hold a non-solvent partner
+        marked = np.zeros(top.n, dtype=bool)
+        for w, nb in wd.items():
+            if any(not S.solv[k] for k in nb):
+                marked[w] = True
+        near += [("hb_dist", u, v, dl) for u, v, dl in contacts_band(top, xyz, marked & heavy, marked & heavy, cd, one_selection=True)
+                 if abs(dl) < NEAR_DIST_TOL and (has_h[u] or has_h[v]) and not same_res(u, v)]
     for w in sorted(wd):
         for n1, n2 in product(sorted(wd[w]), repeat=2):
             s1, s2 = bool(S.solv[n1]), bool(S.solv[n2])
@@ -929,7 +1022,7 @@ def compute_frame_contacts(S: Setup, xyz, itypes, geom, frag: FragmentState, nea
         frag['xyz0'] = xyz
     out = []
     if "sb" in itypes:
-        out += compute_salt_bridges(S, xyz, geom)
+        out += compute_salt_bridges(S, xyz, geom, near)
     if "pc" in itypes:
         out += compute_pi_cation(S, xyz, geom, near)
     if "ps" in itypes:

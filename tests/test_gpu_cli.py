@@ -102,9 +102,35 @@ def test_beg_end_stride_and_empty_selection(tmp_path):
               "--stride", "4"])
     lines = _lines(out)
     assert lines[0].startswith("# total_frames:4 beg:3 end:15 stride:4 ")
-    assert {int(ln.split("\t")[0]) for ln in lines[2:]} == {3, 7, 11, 15}
-    gold = [t for t in read_golden_tsv(os.path.join(GOLDEN, "test_5xnd_expected.tsv.gz")) if t[1] == "vdw" and int(t[0]) in (3, 7, 11, 15)]
+    # the reference never clamps a fragment to --end (compute_contacts.py:253-254: end_frame = beg_frame + 100*stride - 1), so
+    # the last fragment also writes frame 19 although the header says total_frames:4
+    assert {int(ln.split("\t")[0]) for ln in lines[2:]} == {3, 7, 11, 15, 19}
+    gold = [t for t in read_golden_tsv(os.path.join(GOLDEN, "test_5xnd_expected.tsv.gz")) if t[1] == "vdw" and int(t[0]) in (3, 7, 11, 15, 19)]
     assert Counter(tuple(ln.split("\t")) for ln in lines[2:]) == Counter(tuple(t) for t in gold)
     with pytest.raises(SystemExit) as e:                         # compute_contacts.py:240-245
         dyn.main(["--topology", TOP, "--trajectory", TRJ, "--output", str(out), "--itypes", "sb", "--sele", "resname XYZ"])
     assert e.value.code == 1
+
+
+def test_counts_only_run_and_near_cutoff_file(tmp_path):
+    """Extensions of the drop-in script: --no_contact_output (nothing but the count table leaves the GPU; --output may be
+    omitted) gives the same frequency / count files as the run that also writes the contact list, and
+    --near_cutoff_output lists the oracle's near-cutoff observations with atom labels."""
+    import getcontacts_oracle as o
+    dyn, _ = _cli()
+    a = {k: str(tmp_path / k) for k in ("list.tsv", "f1.tsv", "c1.tsv", "n1.tsv", "f2.tsv", "c2.tsv", "n2.tsv")}
+    dyn.main(["--topology", TOP, "--trajectory", TRJ, "--output", a["list.tsv"], "--itypes", "all", "--distout",
+              "--frequency_output", a["f1.tsv"], "--count_output", a["c1.tsv"], "--near_cutoff_output", a["n1.tsv"]])
+    dyn.main(["--topology", TOP, "--trajectory", TRJ, "--itypes", "all", "--no_contact_output",
+              "--frequency_output", a["f2.tsv"], "--count_output", a["c2.tsv"], "--near_cutoff_output", a["n2.tsv"]])
+    for x, y in (("f1.tsv", "f2.tsv"), ("c1.tsv", "c2.tsv"), ("n1.tsv", "n2.tsv")):
+        assert open(a[x]).read() == open(a[y]).read()
+    res = o.run(TOP, TRJ, ["sb", "pc", "ps", "ts", "vdw", "hb", "hp"], collect_near=True)
+    top = res["top"]
+    want = sorted({(f, kind) + tuple(sorted((top.label(i), top.label(j)))) for f, kind, i, j, _ in res["near"]})
+    rows = [ln.rstrip("\n").split("\t") for ln in open(a["n1.tsv"]) if not ln.startswith("#")]
+    assert sorted({(int(r[0]), r[1]) + tuple(sorted((r[2], r[3]))) for r in rows}) == want and len(want) > 0
+    assert all(abs(float(r[4])) < 1e-3 for r in rows)
+    with pytest.raises(SystemExit) as e:                         # --output stays required when the list is written
+        dyn.main(["--topology", TOP, "--trajectory", TRJ, "--itypes", "all"])
+    assert e.value.code == 2

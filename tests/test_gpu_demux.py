@@ -116,3 +116,29 @@ def test_replica_files_to_frequency_tables(tmp_path, replicas):
     head = open(os.path.join(out, "freqs_state_0.tsv")).readline()
     assert head.startswith("#\ttotal_frames:%d\t" % n_frames)
     ref.close()
+
+
+def test_demultiplexed_counts_against_the_oracle(replicas):
+    """The device path against the ORACLE, not against itself: 3 replicas x 60 frames of one 5xnd tile; the state
+    trajectories are gathered on the host with the reference's index logic (sort_replica_trajectories, pinned in
+    tests/test_demux.py) and pushed through the numpy oracle; the indexed submission must give the same count tables."""
+    import bench
+    import getcontacts_oracle as o
+    from parallel import run_parallel
+    from chacra_b200.demux import demux_contacts, state_sources
+    topo, reps, table = replicas
+    reps, table = reps[:3, :60].contiguous(), np.argsort(np.argsort(table[:60, :3], axis=1), axis=1)   # permutations of 0..2
+    eng = _engine(topo, 3)
+    src = demux_contacts(eng, reps, list(table))
+    eng.synchronize()
+    assert np.array_equal(src, state_sources(list(table)))
+    host = reps.cpu().numpy()
+    top, _ = bench.make_topology(1)
+    rank = {lab: k for k, lab in enumerate(topo.residue_label)}
+    for s in range(3):
+        res = run_parallel(top, np.ascontiguousarray(host[src[s], np.arange(60)]), ALL)
+        want = np.zeros(eng.n_pairs, np.int64)
+        for (r1, r2), c in o.intended_counts(res).items():
+            want[int(eng.pair_index(np.array(rank[r1]), np.array(rank[r2])))] = c
+        assert want.sum() > 0 and np.array_equal(eng.counts(s).astype(np.int64), want), s
+    eng.close()

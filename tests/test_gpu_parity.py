@@ -234,3 +234,146 @@ def test_unequal_overlapping_selections_over_two_fragments(oracle_5xnd):
             assert g == w, "%s %s: missing %s extra %s" % (env, it, sorted(w - g)[:5], sorted(g - w)[:5])
         assert run["near"] == want_near
         _check_counts(run, res)
+
+
+def test_crafted_frames_on_every_plain_distance_cutoff(oracle_5xnd):
+    """Near-cutoff channel for the distance cutoffs whose <= / < direction SURVEY 8(c) calls weakly pinned: one atom of the
+    5xnd fixture is slid until a chosen pair sits 3e-5 A below / above the salt-bridge cutoff (salt_bridges.py:76-80, 4.0 A),
+    the hydrogen-bond distance (hbonds.py:75-82, 3.5 A) and the soft `measure contacts` radii of pc / ps / ts
+    (pi_cation.py:22,70; aromatics.py:26-27,166).  The kernel must list the same observations as the oracle and decide the
+    contacts the same way on both sides of every boundary."""
+    import itertools
+    import getcontacts_oracle as o
+    from conftest import tune_pair_distance
+    top = os.path.join(GOLDEN, "5xnd_topology.pdb")
+    x = oracle_5xnd["frames"][0]
+    T, S = oracle_5xnd["top"], oracle_5xnd["setup"]
+    an, ca, ring = np.nonzero(S.anion)[0], np.nonzero(S.cation)[0], np.nonzero(S.ring)[0]
+    d = np.linalg.norm(x[an][:, None] - x[ca][None], axis=-1)
+    k = np.argwhere((d > 3.2) & (d < 4.8))[0]
+    sb = (int(an[k[0]]), int(ca[k[1]]))
+    hb = next((c[2], c[3]) for c in oracle_5xnd["contacts"] if c[0] == 0 and c[1] == "hbbb")
+    pc = None
+    for c2 in np.nonzero(S.prot_cation)[0]:
+        for r in ring:
+            tri = o._aromatic_triplet(S, int(r))
+            if len(tri) != 3 or T.reslabel(int(c2)) == T.reslabel(int(r)):
+                continue
+            dd = [float(np.linalg.norm(x[c2] - x[t])) for t in tri]
+            cen = np.mean([x[t] for t in tri], axis=0)
+            if 9.0 < max(dd) < 9.9 and np.linalg.norm(x[c2] - cen) < 9.3:
+                pc = (int(c2), tri[int(np.argmax(dd))])
+                break
+        if pc:
+            break
+    closest = {}
+    for i, j in itertools.combinations([int(r) for r in ring], 2):
+        ri, rj = T.reslabel(i), T.reslabel(j)
+        if ri != rj:
+            dd = float(np.linalg.norm(x[i] - x[j]))
+            if (ri, rj) not in closest or dd < closest[(ri, rj)][0]:
+                closest[(ri, rj)] = (dd, i, j)
+    ps = next(v for v in closest.values() if 9.0 < v[0] < 9.8)
+    ts = next(v for v in closest.values() if 5.2 < v[0] < 5.9)
+    frames = []
+    for (i, j), target in ((sb, 4.0), (hb, 3.5), (pc, 10.0), (ps[1:], 10.0), (ts[1:], 6.0)):
+        frames += [tune_pair_distance(x, i, j, target, False), tune_pair_distance(x, i, j, target, True)]
+    frames = np.stack(frames)
+    geom = dict(o.DEFAULT_GEOM)
+    geom.update({"PI_CATION_CUTOFF_DISTANCE": 9.5, "PI_STACK_CUTOFF_DISTANCE": 12.0, "T_STACK_CUTOFF_DISTANCE": 9.0})
+    res = o.run(top, top, ALL, geom=geom, frames=frames, collect_near=True)
+    want, want_near = _oracle_sets(res)
+    kinds = {(n[0], n[1]) for n in want_near}
+    assert {(0, "sb_dist"), (1, "sb_dist"), (2, "hb_dist"), (3, "hb_dist"), (4, "pc_soft"), (5, "pc_soft"), (6, "ps_soft"),
+            (7, "ps_soft"), (8, "ts_soft"), (9, "ts_soft")} <= kinds
+    assert (0, "sb", min(sb), max(sb)) in want and (1, "sb", min(sb), max(sb)) not in want      # the boundary really decides
+    for env in ({}, {"CHACRA_FORCE_LARGE": "1"}):
+        os.environ.update(env)
+        try:
+            run = _engine_run(top, frames, ALL, geometry=geom)
+        finally:
+            for name in env:
+                os.environ.pop(name, None)
+        assert run["contacts"] == want, (env, sorted(want - run["contacts"])[:3], sorted(run["contacts"] - want)[:3])
+        assert run["near"] == want_near, (env, sorted(want_near - run["near"])[:5], sorted(run["near"] - want_near)[:5])
+        _check_counts(run, res)
+    # only the sb / hb types enabled: the prefilter radius is then the cutoff itself and must still cover the band above it
+    for its in (["sb"], ["hb"]):
+        r2 = o.run(top, top, its, geom=geom, frames=frames[:4], collect_near=True)
+        w2, n2 = _oracle_sets(r2)
+        run = _engine_run(top, frames[:4], its, geometry=geom)
+        assert run["contacts"] == w2 and run["near"] == n2 and len(n2) >= 2
+
+
+def _pdb_with_zinc(tmp_path, oracle_5xnd):
+    """The 5xnd fixture plus one HETATM zinc ion 2.1 A from an aspartate carboxylate oxygen: a charged ligand inside the
+    selection (contact_utils.py:605-665 makes metal-labelled ligand atoms cations)."""
+    x = oracle_5xnd["frames"]
+    T, S = oracle_5xnd["top"], oracle_5xnd["setup"]
+    od = next(int(i) for i in np.nonzero(S.anion)[0] if T.resname[i] == "ASP")
+    cg = next(int(i) for i in range(T.n) if T.residue[i] == T.residue[od] and T.name[i] == "CG")
+    u = x[0][od] - x[0][cg]
+    u /= np.linalg.norm(u)
+    zn0 = x[0][od] + 2.1 * u
+    lines = [ln for ln in open(os.path.join(GOLDEN, "5xnd_topology.pdb")) if ln.startswith(("ATOM  ", "HETATM"))]
+    lines.append("HETATM%5d ZN    ZN A 900    %8.3f%8.3f%8.3f  1.00  0.00          ZN\n" % (len(lines) + 1, zn0[0], zn0[1], zn0[2]))
+    top = str(tmp_path / "zn.pdb")
+    open(top, "w").write("".join(lines) + "END\n")
+    # the ion rides on the carboxylate oxygen in every frame
+    zn = x[:, od, :] + (zn0 - x[0][od])[None].astype(np.float32)
+    return top, np.ascontiguousarray(np.concatenate([x, zn[:, None, :]], axis=1), dtype=np.float32)
+
+
+def test_charged_ligand_salt_bridges_emit_the_plain_sb_line_too(tmp_path, oracle_5xnd):
+    """salt_bridges.py:90-97 (if / if / if-else): a protein-ligand salt bridge is written as `sbpl` (or `sblp`) AND as a plain
+    `sb` line -- the one get_contact_frequencies counts.  Contact list, count table and the text file against the oracle."""
+    import getcontacts_oracle as o
+    top, frames = _pdb_with_zinc(tmp_path, oracle_5xnd)
+    sel = "protein or resname ZN"
+    res = o.run(top, top, ["sb", "vdw", "hb"], frames=frames, sele1=sel, sele2=sel, collect_near=True)
+    want, want_near = _oracle_sets(res)
+    assert any(c[1] == "sbpl" for c in want) and sum(c[1] == "sb" for c in want) > sum(c[1] == "sbpl" for c in want)
+    for env in ({}, {"CHACRA_FORCE_LARGE": "1"}):
+        os.environ.update(env)
+        try:
+            run = _engine_run(top, frames, ["sb", "vdw", "hb"], sel, sel)
+        finally:
+            for name in env:
+                os.environ.pop(name, None)
+        for it in sorted({c[1] for c in want | run["contacts"]}):
+            w, g = {c for c in want if c[1] == it}, {c for c in run["contacts"] if c[1] == it}
+            assert g == w, "%s %s: missing %s extra %s" % (env, it, sorted(w - g)[:5], sorted(g - w)[:5])
+        assert run["near"] == want_near
+        _check_counts(run, res)
+
+
+def test_unaligned_growing_submissions_keep_the_hydrophobic_set(oracle_5xnd):
+    """chc_submit_frames may continue a fragment; the mask buffer then grows while slot 0 must keep the continued fragment's
+    hydrophobic set (250 frames at index 0, then 350 at index 250: the second call needs more fragment slots than the
+    first).  Device tensors, every binning variant with its own mask path; against one aligned submission."""
+    import torch
+    from chacra_b200 import read_pdb, compile_topology
+    from chacra_b200.engine import ContactEngine
+    base = oracle_5xnd["frames"]
+    frames = np.ascontiguousarray(base[(np.arange(600) * 7) % 20])
+    for k in range(6):                                   # every fragment opens on a different frame -> different hp sets
+        frames[100 * k] = base[(3 * k + 1) % 20]
+    x = torch.from_numpy(frames).cuda()
+    topo = compile_topology(read_pdb(os.path.join(GOLDEN, "5xnd_topology.pdb")), frames[0])
+    for variant in ("3", "0"):
+        os.environ["CHACRA_BIN_VARIANT"] = variant
+        try:
+            outs = []
+            for cuts in ([0, 600], [0, 250, 600], [0, 30, 130, 131, 460, 600]):
+                eng = ContactEngine(topo, ["hp", "vdw"], emit_contacts=True, contact_capacity=1 << 21)
+                for a, b in zip(cuts[:-1], cuts[1:]):
+                    eng.submit(x[a:b], 0, a)
+                eng.synchronize()
+                rec = eng.drain_contacts()
+                outs.append((eng.counts(0), np.sort(rec[["frame", "itype", "atom1", "atom2"]], order=["frame", "itype", "atom1", "atom2"])))
+                eng.close()
+            assert (outs[0][1]["itype"] == 18).sum() > 600 * 50          # hp records present in every fragment
+            for got in outs[1:]:
+                assert np.array_equal(got[0], outs[0][0]) and np.array_equal(got[1], outs[0][1]), variant
+        finally:
+            os.environ.pop("CHACRA_BIN_VARIANT", None)
