@@ -5,10 +5,13 @@ Workload (`config.workload`): "1tnf solvated HREMD synthetic: 20 states x 10k fr
 all itypes, 1 GPU" -> 4 tiled copies of the hydrogenated 5xnd fixture (6 516 atoms, 448 residues),
 20 states x 10 000 frames of float32 coordinates resident in HBM (15.6 GB >> 126 MB of L2).
 One "step" = one pass of the hot path over all 20 state trajectories (count tables reset first).
-With N > 1 every rank runs the same shape on its own frames (weak scaling) and the per-state count
-tables are merged with one NCCL all-reduce inside the step.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--states S] [--frames F]
+N > 1 (torchrun, one rank per GPU): STRONG scaling of the same job.  The 2 000 fragments of the 20 states are dealt
+out with chacra_b200.sharding.state_slices (what the product launcher get_state_frequencies.py does), every rank
+processes its share and the per-state int32 count tables are merged with one NCCL all-reduce inside the step
+(SURVEY.md 8(e)); value = the 200 000 frames / the slowest rank's device time.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--states S] [--frames F] [--no-extras]
 """
 import argparse
 import json
@@ -25,9 +28,7 @@ GOLDEN = os.path.join(ROOT, "tests", "golden")
 ITYPES = ["sb", "pc", "ps", "ts", "vdw", "hb", "hp"]
 WORKLOAD = "1tnf solvated HREMD synthetic: 20 states x 10k frames, ~7k protein atoms, all itypes, 1 GPU"
 METRIC = "contact frames/sec (all itypes)"
-# dram__bytes_read.sum + dram__bytes_write.sum per frame of this workload, from the committed ncu --set full capture
-# (profiles/r01_v4_ncu_summary.txt, 11 840 frames per launch): pair kernel 0.923 GB + 5 MB, streaming kernel 0.931 GB + 0.862 GB
-NCU_DRAM_BYTES_PER_FRAME = {"pair_frames_kernel": (923.036672e6 + 5.214208e6) / 11840, "bin_frames_kernel": (931.569408e6 + 859.877888e6) / 11840}
+TRAFFIC_JSON = os.path.join(ROOT, "profiles", "ncu_traffic.json")      # written by tools/ncu_traffic.py from a committed ncu capture
 
 
 def make_topology(copies=4):
@@ -76,59 +77,187 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(reasons), "samples": len(self.rows)}
 
 
-def oracle_frames_per_second(pdb_path, frames, procs):
-    """CPU restatement of the reference semantics (oracle/, numpy) on `frames`, `procs` worker processes."""
-    import multiprocessing as mp
-    chunks = [frames[k::procs] for k in range(procs) if len(frames[k::procs])]
+# ---- CPU baselines (the ONLY place bench.py touches oracle/) -----------------------------------------------------------
+def cpu_twin_rate(pdb_path, xyz0, frames, min_seconds=10.0, threads=None):
+    """C++/OpenMP twin of the reference semantics (oracle/getcontacts_cpu.cpp, pinned to the numpy oracle) on all host
+    cores: passes over `frames` (counts only, like the GPU arm) until `min_seconds` of CPU work."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import cpu_twin
+    tw = cpu_twin.Twin(pdb_path, xyz0=xyz0, itypes=ITYPES)
+    cores = threads or cpu_twin.load().gc_threads()
+    tw.run(frames[:max(1, min(len(frames), 4 * cores))], want_contacts=False, threads=cores)      # warm-up (page in, thread pool)
+    done, t0 = 0, time.perf_counter()
+    while True:
+        tw.run(frames, want_contacts=False, threads=cores)
+        done += len(frames)
+        dt = time.perf_counter() - t0
+        if dt >= min_seconds:
+            break
+    return done / dt, dt, done, cores
+
+
+def numpy_oracle_rate(pdb_path, frames, procs):
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    from parallel import run_parallel
+    import getcontacts_oracle as o
     t0 = time.perf_counter()
-    if len(chunks) == 1:
-        _oracle_worker((pdb_path, chunks[0]))
-    else:
-        with mp.get_context("fork").Pool(len(chunks)) as pool:
-            pool.map(_oracle_worker, [(pdb_path, c) for c in chunks])
+    res = run_parallel(pdb_path, frames, ITYPES, procs=procs)
+    o.intended_counts(res)
     dt = time.perf_counter() - t0
     return len(frames) / dt, dt
 
 
-def _oracle_worker(args):
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
-    import getcontacts_oracle as o
-    pdb_path, frames = args
-    res = o.run(pdb_path, pdb_path, ITYPES, frames=frames)
-    o.intended_counts(res)
-    return len(res["contacts"])
-
-
 def run_reference(args):
-    """--impl reference: the reference's CPU path.  vmd-python is not installable here (no network), so the
-    reference itself cannot run; the arm times the oracle port on all host cores (kind = "port")."""
+    """--impl reference: the reference's CPU path on the host cores.  getcontacts itself is Python driving VMD through
+    vmd-python 3.1.4, which is not installable here (no network) and has no source under /root/reference to compile, so the
+    arm times the C++/OpenMP restatement of the same semantics on ALL host cores (kind = "port-c++"; faster than real
+    getcontacts, which pays a Tcl round trip per candidate pair).  One step = a bounded sample of the workload."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    import numpy as np
     from chacra_b200.synthetic import FrameGenerator
     path, atoms = make_topology()
-    cores = os.cpu_count() or 1
-    per_step = max(cores, min(16 * cores, 512))
-    gen = FrameGenerator(atoms.xyz, 2000, amplitude=state_amplitude(0, args.states))
+    per_step = 4000                                   # frames of state 0 per step (the full job is 200 000)
+    gen = FrameGenerator(atoms.xyz, 2000, amplitude=state_amplitude(0, args.states), device="cpu")
     frames = gen.frames(per_step).numpy()
-    for _ in range(min(args.warmup, 1)):
-        oracle_frames_per_second(path, frames[:cores], cores)
+    warm = max(1, min(args.warmup, 3))
+    for _ in range(warm):
+        cpu_twin_rate(path, atoms.xyz, frames[:1000], min_seconds=0.0)
     t0 = time.perf_counter()
+    cores = 1
     for _ in range(args.steps):
-        oracle_frames_per_second(path, frames, cores)
+        _, _, _, cores = cpu_twin_rate(path, atoms.xyz, frames, min_seconds=0.0)
     dt = time.perf_counter() - t0
     fps = args.steps * per_step / dt
+    np_fps, np_dt = numpy_oracle_rate(path, frames[:4 * (os.cpu_count() or 1)], os.cpu_count() or 1)
     line = {"impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+            "warmup": warm, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "atoms": int(atoms.n), "itypes": ITYPES, "frames_per_step": per_step},
-            "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port",
-                             "sample": "%d frames per step of the config-2 shape, numpy oracle, %d processes; the reference "
-                                       "itself needs vmd-python (absent, no network)" % (per_step, cores)},
+            "config": {"workload": WORKLOAD, "atoms": int(atoms.n), "states": args.states, "frames_per_state": args.frames,
+                       "itypes": ITYPES, "frames_per_step": per_step,
+                       "sample": "each step = %d frames of state 0 of the same shape (a rate metric; the full job is %d frames)" % (
+                           per_step, args.states * args.frames)},
+            "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port-c++",
+                             "sample": "%d frames per step, C++/OpenMP twin of the reference semantics (oracle/getcontacts_cpu.cpp), %d threads, "
+                                       "counts only; the reference itself needs vmd-python (absent, no network)" % (per_step, cores),
+                             "numpy_oracle": {"value": np_fps, "unit": "frames/s", "cores": os.cpu_count() or 1, "seconds": np_dt}},
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
+
+
+# ---- measured DRAM traffic of the committed ncu capture ------------------------------------------------------------------
+def ncu_traffic(build_tag):
+    """dram__bytes_read.sum + dram__bytes_write.sum per frame from the committed `ncu --set full` capture -- only if that
+    capture was taken from THIS build of the kernels (chc_build_tag), else None with the reason."""
+    try:
+        t = json.load(open(TRAFFIC_JSON))
+    except Exception:
+        return None, "no committed ncu capture (profiles/ncu_traffic.json)"
+    if t.get("build_tag") != build_tag:
+        return None, "committed ncu capture is from build %s, library is %s" % (t.get("build_tag"), build_tag)
+    return t, "profiles/%s" % t.get("source", "ncu_traffic.json")
+
+
+# ---- the other BASELINE.json shapes: bounded samples + the real-size count exchange -------------------------------------
+def extra_config(name, copies, n_states, sample_frames, dev, world, dist, torch):
+    from chacra_b200 import compile_topology
+    from chacra_b200.engine import ContactEngine
+    from chacra_b200.sharding import merge_count_tables
+    from chacra_b200.synthetic import FrameGenerator
+    path, atoms = make_topology(copies)
+    topo = compile_topology(atoms)
+    eng = ContactEngine(topo, ITYPES, n_states=n_states, device=dev.index)
+    gen = FrameGenerator(atoms.xyz, 1000 * copies + int(os.environ.get("RANK", "0")), amplitude=0.8, device=dev)
+    step = max(1, min(sample_frames, (256 << 20) // (12 * atoms.n)))
+    x = torch.cat([gen.frames(min(step, sample_frames - b)) for b in range(0, sample_frames, step)])
+    eng.submit(x, 0, 0)
+    eng.synchronize()
+    eng.reset_counts()
+    eng.set_timing(True)
+    passes = 2
+    for _ in range(passes):
+        eng.submit(x, 0, 0)
+    eng.synchronize()
+    st = eng.stats()
+    ms = (st["pair_ms_total"] + st["bin_ms_total"]) / passes
+    t = torch.tensor([ms], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    out = {"atoms": int(atoms.n), "residues": int(topo.n_residues), "states_in_table": n_states, "sample_frames_per_rank": sample_frames,
+           "frames_per_s": world * sample_frames / (float(t.item()) * 1e-3), "pair_ms": st["pair_ms_total"] / passes, "bin_ms": st["bin_ms_total"] / passes,
+           "stream_gbs": 12.0 * atoms.n * sample_frames / (st["bin_ms_total"] / passes * 1e-3) / 1e9,
+           "how": "every rank times its own sample of one state (kernel events); aggregate = ranks x sample / slowest rank",
+           "table_bytes_dense": int(eng.counts_tensor.numel() * 4), "allreduce_ms_dense": None, "allreduce_ms_compact": None}
+    if world > 1:
+        counts = eng.counts_tensor
+        keep = counts.clone()
+        for mode in ("dense", "compact"):
+            best = None
+            for _ in range(3):
+                counts.copy_(keep)
+                dist.barrier()
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                info = {}
+                e0.record()
+                merge_count_tables(counts, compact=(mode == "compact"), info=info)
+                e1.record()
+                torch.cuda.synchronize()
+                tt = torch.tensor([e0.elapsed_time(e1)], device=dev)
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                best = float(tt.item()) if best is None else min(best, float(tt.item()))
+            out["allreduce_ms_" + mode] = best
+            if mode == "compact":
+                out["table_bytes_compact"] = info.get("compact_bytes")
+                out["pairs_nonzero"] = info.get("pairs_nonzero")
+        del keep
+    eng.close()
+    del x
+    torch.cuda.empty_cache()
+    return out
+
+
+def cli_rates(path, atoms, torch, dev):
+    """The path ChACRA really runs (process_hremd_output.py:139-175): state DCD -> contact-list TSV (--distout) -> frequency TSV
+    through the drop-in scripts, and the counts-only variant (--no_contact_output --frequency_output), on 2 000 frames."""
+    from chacra_b200.synthetic import FrameGenerator
+    from chacra_b200.getcontacts import get_contact_frequencies, get_dynamic_contacts
+    n = 2000
+    tmp = tempfile.mkdtemp(prefix="chacra_cli_")
+    x = FrameGenerator(atoms.xyz, 2000, amplitude=0.8, device=dev).frames(n).cpu().numpy()
+    dcd = os.path.join(tmp, "state_0.dcd")
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from test_gpu_dcd import write_dcd
+    write_dcd(dcd, x, "<", False)
+    out = {}
+    devnull = open(os.devnull, "w")
+    saved = os.dup(1)
+    try:
+        os.dup2(devnull.fileno(), 1)
+        for k in range(2):                                # first pass warms the page cache and the pinned buffers
+            t0 = time.perf_counter()
+            get_dynamic_contacts.main(["--topology", path, "--trajectory", dcd, "--output", os.path.join(tmp, "cont_state_0.tsv"), "--cores", "6",
+                                       "--itypes", "all", "--distout", "--sele", "protein", "--sele2", "protein"])
+            t1 = time.perf_counter()
+            get_contact_frequencies.main(["--input_files", os.path.join(tmp, "cont_state_0.tsv"), "--output_file", os.path.join(tmp, "freqs_state_0.tsv")])
+            t2 = time.perf_counter()
+            get_dynamic_contacts.main(["--topology", path, "--trajectory", dcd, "--itypes", "all", "--no_contact_output",
+                                       "--frequency_output", os.path.join(tmp, "freqs_direct_0.tsv")])
+            t3 = time.perf_counter()
+            out = {"frames": n, "value": n / (t2 - t0), "unit": "frames/s", "contacts_s": t1 - t0, "frequencies_s": t2 - t1,
+                   "tsv_bytes": os.path.getsize(os.path.join(tmp, "cont_state_0.tsv")),
+                   "what": "get_dynamic_contacts.py --itypes all --distout (DCD in, contact TSV out) + get_contact_frequencies.py, argv to files",
+                   "counts_only": {"value": n / (t3 - t2), "unit": "frames/s",
+                                   "what": "get_dynamic_contacts.py --no_contact_output --frequency_output (DCD in, frequency TSV out)"}}
+    finally:
+        os.dup2(saved, 1)
+        os.close(saved)
+        devnull.close()
+        for f in os.listdir(tmp):
+            os.remove(os.path.join(tmp, f))
+        os.rmdir(tmp)
+    return out
 
 
 def main():
@@ -140,6 +269,7 @@ def main():
     ap.add_argument("--states", type=int, default=20)
     ap.add_argument("--frames", type=int, default=10000, help="frames per state")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip config 3 / 4 samples, the CLI rate and the near-cutoff pass")
     ap.add_argument("--e2e-steps", type=int, default=2)
     args = ap.parse_args()
     if args.impl == "reference":
@@ -149,9 +279,9 @@ def main():
     import numpy as np
     import torch
     import torch.distributed as dist
-    from chacra_b200 import compile_topology
-    from chacra_b200.engine import ContactEngine
-    from chacra_b200.sharding import bind_to_gpu_numa_node, merge_count_tables
+    from chacra_b200 import compile_topology, _lib
+    from chacra_b200.engine import ContactEngine, NEAR_KINDS
+    from chacra_b200.sharding import bind_to_gpu_numa_node, merge_count_tables, state_slices
     from chacra_b200.synthetic import FrameGenerator
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -172,22 +302,27 @@ def main():
     path, atoms = make_topology()
     topo = compile_topology(atoms)
     eng = ContactEngine(topo, ITYPES, n_states=S, device=local)
+    build_tag = _lib.load().chc_build_tag().decode()
     N = atoms.n
-    # ---- synthetic state trajectories, generated straight into HBM ---------------------------------------
+    work = state_slices([F] * S, world, rank)           # [(state, first frame, count)]: this rank's share of the SAME 20 x 10k job
+    # ---- synthetic state trajectories, generated straight into HBM (the same frames whatever the rank count) ----------
     traj = []
-    for s in range(S):
-        gen = FrameGenerator(atoms.xyz, 1000 * 2 + s + 100 * rank, amplitude=state_amplitude(s, S), device=dev)
-        buf = torch.empty((F, N, 3), dtype=torch.float32, device=dev)
-        for b in range(0, F, 1000):
-            buf[b:b + 1000] = gen.frames(min(1000, F - b))
+    for s, first, cnt in work:
+        gen = FrameGenerator(atoms.xyz, 1000 * 2 + s, amplitude=state_amplitude(s, S), device=dev)
+        buf = torch.empty((cnt, N, 3), dtype=torch.float32, device=dev)
+        for b in range(0, first + cnt, 1000):
+            blk = gen.frames(min(1000, first + cnt - b))
+            lo, hi = max(b, first), min(b + len(blk), first + cnt)
+            if lo < hi:
+                buf[lo - first:hi - first] = blk[lo - b:hi - b]
         traj.append(buf)
-    del gen
     torch.cuda.synchronize()
+    my_frames = sum(c for _, _, c in work)
 
     def step():
         eng.reset_counts()
-        for s in range(S):
-            eng.submit(traj[s], s, 0)
+        for (s, first, cnt), buf in zip(work, traj):
+            eng.submit(buf, s, first)
         merge_count_tables(eng.counts_tensor)           # the path's one exchange step (int32 sum, order-free; no-op at N=1)
 
     def barrier():
@@ -218,18 +353,19 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     launches = st["kernel_launches"] - launches0 + (args.steps if world > 1 else 0)
-    frames_per_step = S * F * world
+    frames_per_step = S * F                              # whole job, all ranks
     value = args.steps * frames_per_step / (ms * 1e-3)
     counts_dev = eng.counts_tensor.clone()
 
     # ---- e2e: the same job through the host-buffer entry point (H2D + counts D2H inside the timed region) ----
-    host = torch.empty((F, N, 3), dtype=torch.float32, pin_memory=True)
-    host.copy_(traj[0])
+    longest = max(c for _, _, c in work)
+    host = torch.empty((longest, N, 3), dtype=torch.float32, pin_memory=True)
+    host.copy_(max(traj, key=len))
 
     def e2e_step():
         eng.reset_counts()
-        for s in range(S):
-            eng.submit(host, s, 0)
+        for s, first, cnt in work:
+            eng.submit(host[:cnt], s, first)
         merge_count_tables(eng.counts_tensor)
         return eng.counts_tensor.cpu()
 
@@ -245,9 +381,55 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
     e2e_value = args.e2e_steps * frames_per_step / e2e_s
-    # host path and device path must agree bit for bit on the state they share
-    if world == 1:
-        assert torch.equal(table[0], counts_dev[0].cpu()), "host-buffer path and device path disagree"
+    if world == 1 and len(work) and work[0][2] == longest:
+        # host path and device path must agree bit for bit on the state whose frames the host buffer holds
+        s_long = work[int(np.argmax([len(t_) for t_ in traj]))][0]
+        assert torch.equal(table[s_long], counts_dev[s_long].cpu()), "host-buffer path and device path disagree"
+
+    # ---- parity: first 100 frames of a CPU-generated state against the COMMITTED oracle count table (outside the timed region) ----
+    parity = {"checked": False}
+    gpath = os.path.join(GOLDEN, "bench_c2_100frames.npz")
+    if rank == 0 and os.path.exists(gpath) and N == 6516:
+        g = np.load(gpath)
+        xs = FrameGenerator(atoms.xyz, int(g["seed"]), amplitude=float(g["amplitude"]), device="cpu").frames(int(g["n_frames"]))
+        chk = ContactEngine(topo, ITYPES, n_states=1, device=local)
+        chk.submit(xs.to(dev), 0, 0)
+        chk.synchronize()
+        got = chk.counts(0).astype(np.int64)
+        want = np.zeros_like(got)
+        want[g["count_idx"]] = g["count_val"]
+        parity = {"checked": True, "equal": bool(np.array_equal(got, want)), "frames": int(g["n_frames"]), "pair_frames": int(want.sum()),
+                  "golden": "tests/golden/bench_c2_100frames.npz (numpy oracle, tests/golden/make_bench_golden.py)"}
+        chk.close()
+        assert parity["equal"], "count table differs from the committed oracle table"
+
+    # ---- near-cutoff channel: 1 000 frames of state 0 through the near-tracking instantiation (outside the timed region) ----
+    near = None
+    extras = {}
+    if rank == 0 and not args.no_extras:
+        ne = ContactEngine(topo, ITYPES, n_states=1, track_near=True, near_capacity=1 << 20, device=local)
+        xs = FrameGenerator(atoms.xyz, 2000, amplitude=state_amplitude(0, S), device=dev).frames(1000)
+        ne.submit(xs, 0, 0)
+        ne.synchronize()
+        rec, total = ne.drain_near()
+        kinds = np.bincount(rec["kind"], minlength=len(NEAR_KINDS))
+        near = {"frames": 1000, "near_total": int(total), "per_frame": total / 1000.0,
+                "by_kind": {NEAR_KINDS[k]: int(c) for k, c in enumerate(kinds) if c}}
+        ne.close()
+        del xs
+    if not args.no_extras:
+        del traj
+        torch.cuda.empty_cache()
+        try:
+            extras["config3"] = extra_config("config3", 10, 20, 1480, dev, world, dist, torch)
+            extras["config4"] = extra_config("config4", 61, 32, 296, dev, world, dist, torch)
+        except Exception as exc:                         # never lose the main line to an extra
+            extras["error"] = "%s: %s" % (type(exc).__name__, exc)
+        if rank == 0 and world == 1:
+            try:
+                extras["e2e_cli"] = cli_rates(path, atoms, torch, dev)
+            except Exception as exc:
+                extras["e2e_cli"] = {"error": "%s: %s" % (type(exc).__name__, exc)}
 
     if rank == 0:
         peaks = {}
@@ -257,52 +439,58 @@ def main():
             pass
         peak, which = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
         n_chunks = max(1, st["timed_chunks"])
-        frames_per_chunk = args.steps * S * F / n_chunks          # per rank
+        frames_per_chunk = args.steps * my_frames / n_chunks          # per launch, this rank
         pair_ms, bin_ms = st["pair_ms_total"] / n_chunks, st["bin_ms_total"] / n_chunks
         bytes_per_launch = 12.0 * N * frames_per_chunk         # algorithmic: every stored coordinate read once
         achieved = bytes_per_launch / (pair_ms * 1e-3) / 1e9
         stream_gbs = bytes_per_launch / (bin_ms * 1e-3) / 1e9
+        traffic, traffic_src = ncu_traffic(build_tag)
+        tp = traffic["pair_frames_kernel_bytes_per_frame"] * frames_per_chunk if traffic and N == 6516 else None
+        tb = traffic["bin_frames_kernel_bytes_per_frame"] * frames_per_chunk if traffic and N == 6516 else None
         line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic",
                 "config": {"workload": WORKLOAD, "atoms": int(N), "pair_atoms": int(len(topo.pair_atom)),
                            "residues": int(topo.n_residues), "states": S, "frames_per_state": F, "itypes": ITYPES,
-                           "l2": "inputs (%.1f GB per GPU) are larger than L2" % (S * F * N * 12 / 1e9),
+                           "l2": "inputs (%.1f GB per GPU) are larger than L2" % (my_frames * N * 12 / 1e9),
                            "outputs": "int32 residue-pair frame counts [states][pairs]",
-                           "parallelism": "frames sharded, %d rank(s), one int32 all-reduce" % world},
+                           "parallelism": "the job's %d fragments dealt out over %d rank(s) (sharding.state_slices: rank 0 holds %d frames of %d state(s)), "
+                                          "one int32 all-reduce" % (S * ((F + 99) // 100), world, my_frames, len(work))},
                 # dominant kernel = the pair kernel (fp32-issue / shared-memory bound by construction);
                 # its HBM fraction is reported as the contract asks, the streaming kernel's beside it
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": NCU_DRAM_BYTES_PER_FRAME["pair_frames_kernel"] * frames_per_chunk if N == 6516 else None,
-                             "kernel": "pair_frames_kernel", "peak_source": which,
+                             "traffic": tp, "traffic_source": traffic_src, "kernel": "pair_frames_kernel", "peak_source": which,
                              "avg_launch_ms": pair_ms, "launches_timed": n_chunks, "algorithmic_bytes_per_launch": bytes_per_launch,
                              "kernel_share_of_step": st["pair_ms_total"] / ms},
                 "roofline_stream": {"bound": "hbm", "achieved": stream_gbs, "peak": peak, "unit": "GB/s", "frac": stream_gbs / peak,
-                                    "traffic": NCU_DRAM_BYTES_PER_FRAME["bin_frames_kernel"] * frames_per_chunk if N == 6516 else None,
-                                    "traffic_note": "12 B/atom read once (no re-reads) + the binned record written once (83 KB per frame, 73 KB of it used)",
-                                    "kernel": "bin_frames_kernel", "avg_launch_ms": bin_ms,
+                                    "traffic": tb, "traffic_source": traffic_src, "kernel": "bin_frames_kernel", "avg_launch_ms": bin_ms,
                                     "algorithmic_bytes_per_launch": bytes_per_launch,
                                     "kernel_share_of_step": st["bin_ms_total"] / ms},
-                "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": int(S * F * N * 12) * world,
+                "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": int(S * F * N * 12),
                         "d2h_bytes_per_step": int(eng.counts_tensor.numel() * 4) * world, "steps": args.e2e_steps,
                         "host_numa": numa},
-                "gpu_launches": int(launches), "clocks": clocks,
-                "engine": {k: st[k] for k in ("path", "smem_bytes", "threads", "grid", "bin_smem_bytes", "bin_grid", "chunk_frames", "record_bytes")}}
+                "gpu_launches": int(launches), "clocks": clocks, "build_tag": build_tag, "parity": parity, "near": near,
+                "engine": {k: st[k] for k in ("path", "smem_bytes", "threads", "grid", "bin_smem_bytes", "bin_grid", "chunk_frames", "record_bytes",
+                                              "bin_variant", "bin_apt")}}
+        line.update(extras)
         if world == 1 and not args.no_cpu_baseline:
-            # the oracle port on ALL host cores, a bounded sample of the same workload (about 48 frames per core, 10-20 s)
-            cores = os.cpu_count() or 1
-            n_sample = max(16, min(48 * cores, 1536))
-            gen = FrameGenerator(atoms.xyz, 2000, amplitude=state_amplitude(0, S))
-            sample = gen.frames(n_sample).numpy()
-            fps, dt = oracle_frames_per_second(path, sample, cores)
-            line["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port",
-                                    "sample": "%d frames of the same shape (state 0), numpy oracle, %d worker processes, %.1f s; "
-                                              "the reference itself needs vmd-python (absent, no network)" % (n_sample, cores, dt)}
+            # the C++/OpenMP twin on ALL host cores, a bounded sample of the same workload (4 000 frames of state 0, >= 10 s)
+            gen = FrameGenerator(atoms.xyz, 2000, amplitude=state_amplitude(0, S), device="cpu")
+            sample = gen.frames(4000).numpy()
+            fps, dt, done, cores = cpu_twin_rate(path, atoms.xyz, sample, min_seconds=10.0)
+            procs = os.cpu_count() or 1
+            np_fps, np_dt = numpy_oracle_rate(path, sample[:4 * procs], procs)
+            line["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port-c++",
+                                    "sample": "%d frames (passes over 4 000 frames of state 0, same shape), C++/OpenMP twin of the reference semantics "
+                                              "(oracle/getcontacts_cpu.cpp), %d threads, counts only, %.1f s; the reference itself needs vmd-python "
+                                              "(absent, no network)" % (done, cores, dt),
+                                    "numpy_oracle": {"value": np_fps, "unit": "frames/s", "cores": procs, "frames": 4 * procs, "seconds": np_dt}}
         sys.stdout.flush()
         os.dup2(saved_stdout, 1)
         print(json.dumps(line), flush=True)
         os.dup2(2, 1)
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
 
 

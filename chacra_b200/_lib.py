@@ -79,6 +79,7 @@ class ChcStats(C.Structure):
 vp = C.c_void_p
 SYMBOLS = {
     "chc_abi_version": (C.c_int, []),
+    "chc_build_tag": (C.c_char_p, []),
     "chc_create": (C.c_int, [C.POINTER(vp), C.POINTER(ChcTopology), C.POINTER(ChcParams), C.c_int]),
     "chc_destroy": (None, [vp]),
     "chc_last_error": (C.c_char_p, [vp]),

@@ -84,10 +84,12 @@ def compute_contacts(top, traj, output, itypes, geom_criterion_values, cores, be
         if total > len(rec):
             raise ChacraError("near-cutoff buffer overflow (%d observations)" % total)
         near_total += len(rec)
-        order = np.lexsort((rec["atom2"], rec["atom1"], rec["kind"], rec["frame"]))
-        for r in rec[order]:
-            near_fd.write("%d\t%s\t%s\t%s\t%.3e\n" % (beg + int(r["frame"]) * stride, NEAR_KINDS[r["kind"]], labels[r["atom1"]],
-                                                       labels[r["atom2"]], r["delta"]))
+        rows = []
+        for r in rec:                                    # atom_1 / atom_2 ordered like a contact line (compute_contacts.py:343-348)
+            l1, l2 = labels[r["atom1"]], labels[r["atom2"]]
+            rows.append((int(r["frame"]), int(r["kind"]), min(l1, l2), max(l1, l2), float(r["delta"])))
+        for f, kind, l1, l2, delta in sorted(set(rows)):
+            near_fd.write("%d\t%s\t%s\t%s\t%.3e\n" % (beg + f * stride, NEAR_KINDS[kind], l1, l2, delta))
 
     reader = getattr(trj, "read_device", trj.read)       # DCD and XTC frames are unpacked on the device and stay there
     stage = [0.0, 0.0, 0.0]                              # seconds: trajectory input, contacts + drain, TSV text

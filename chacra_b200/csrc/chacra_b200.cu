@@ -162,7 +162,11 @@ static int plan(chc_ctx* ctx, size_t cells_cap = 49152) {
     return CHC_OK;
 }
 
+#ifndef CHC_BUILD_TAG
+#define CHC_BUILD_TAG "r02_v1"
+#endif
 extern "C" int chc_abi_version(void) { return CHC_ABI_VERSION; }
+extern "C" const char* chc_build_tag(void) { return CHC_BUILD_TAG; }
 extern "C" const char* chc_last_error(const chc_ctx* ctx) { return ctx ? ctx->err : "null context"; }
 extern "C" int64_t chc_n_pairs(const chc_ctx* ctx) { return ctx ? ctx->n_pairs : 0; }
 

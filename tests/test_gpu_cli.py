@@ -134,3 +134,31 @@ def test_counts_only_run_and_near_cutoff_file(tmp_path):
     with pytest.raises(SystemExit) as e:                         # --output stays required when the list is written
         dyn.main(["--topology", TOP, "--trajectory", TRJ, "--itypes", "all"])
     assert e.value.code == 2
+
+
+def test_all_states_launcher_single_rank(tmp_path):
+    """get_state_frequencies.py (the multi-GPU launcher) run as one process: per-state tables equal to what
+    get_dynamic_contacts --frequency_output writes for each state trajectory on its own; with --beg/--end/--stride too."""
+    import numpy as np
+    from test_gpu_dcd import write_dcd
+    from chacra_b200.trajectory import DCDFile
+    from chacra_b200.getcontacts import get_state_frequencies
+    dyn, _ = _cli()
+    x = DCDFile(TRJ).read()
+    states = []
+    for s in range(3):                                   # three "states": the fixture frames in different orders, 130 / 20 / 250 frames
+        n = (130, 20, 250)[s]
+        p = str(tmp_path / ("state_%d.dcd" % s))
+        write_dcd(p, np.ascontiguousarray(x[(np.arange(n) * (2 * s + 1) + s) % 20]), "<", False)
+        states.append(p)
+    for extra in ([], ["--beg", "5", "--end", "117", "--stride", "3"]):
+        out = tmp_path / ("all%d" % len(extra))
+        get_state_frequencies.main(["--topology", TOP, "--trajectories"] + states[::-1] + ["--output_dir", str(out), "--counts",
+                                    "--near_cutoff_output", str(out) + "_near.tsv"] + extra)
+        for s in range(3):
+            one = tmp_path / ("one%d_%d" % (s, len(extra)))
+            dyn.main(["--topology", TOP, "--trajectory", states[s], "--itypes", "all", "--no_contact_output",
+                      "--frequency_output", str(one) + "_f.tsv", "--count_output", str(one) + "_c.tsv"] + extra)
+            assert open(out / ("freqs_state_%d.tsv" % s)).read() == open(str(one) + "_f.tsv").read()
+            assert open(out / ("counts_state_%d.tsv" % s)).read() == open(str(one) + "_c.tsv").read()
+        assert sum(1 for ln in open(str(out) + "_near.tsv") if not ln.startswith("#")) > 0
