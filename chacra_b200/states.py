@@ -130,7 +130,7 @@ def gather_near(near, labels, sel, stride, path):
             s = int(r["reserved"])
             rows.add((s, sel[s][0] + int(r["frame"]) * stride, int(r["kind"]), min(l1, l2), max(l1, l2), float(r["delta"])))
     with open(path, "w") as fd:
-        fd.write("# near-cutoff observations: |value - cutoff| < 1e-4 A (distances) or 1e-3 degree (angles)\\n"
-                 "# Columns: state, frame, criterion, atom_1, atom_2, value_minus_cutoff\\n")
+        fd.write("# near-cutoff observations: |value - cutoff| < 1e-4 A (distances) or 1e-3 degree (angles)\n"
+                 "# Columns: state, frame, criterion, atom_1, atom_2, value_minus_cutoff\n")
         for s, f, kind, l1, l2, delta in sorted(rows):
-            fd.write("%d\\t%d\\t%s\\t%s\\t%s\\t%.3e\\n" % (s, f, NEAR_KINDS[kind], l1, l2, delta))
+            fd.write("%d\t%d\t%s\t%s\t%s\t%.3e\n" % (s, f, NEAR_KINDS[kind], l1, l2, delta))
