@@ -30,6 +30,7 @@ struct chc_ctx {
     BinLayout B{};
     BinTmaLayout Y{};
     bool small_path = true, bin_tma = false; int tma_apt = 8;
+    int lkey_max = 0;
     int bin_smem = 0, bin_grid = 0, pair_grid = 0, bin_threads = 256, bin_variant = 0;
     int64_t chunk_frames = 0;
     unsigned char* binned = nullptr;
@@ -116,7 +117,8 @@ static int plan(chc_ctx* ctx, size_t cells_cap = 49152) {
     B.off_cells = B.fixed_bytes;
     auto queue_bytes = [&](bool small, size_t* q1, size_t* qf, size_t* q2) {
         const size_t qw = small ? 1 : 2;
-        *q1 = al16(4 * qw * (size_t)warps * Q1_CAP); *qf = al16(4 * qw * (size_t)warps * QF_CAP);
+        // the shared-memory path filters its hits per lane and queues them straight into qf: no survivor queue q1
+        *q1 = small ? 0 : al16(4 * qw * (size_t)warps * Q1_CAP); *qf = al16(4 * qw * (size_t)warps * QF_CAP);
         *q2 = al16(8 * (qw + 1) * (size_t)warps * Q2_CAP);
         return *q1 + *qf + *q2;
     };
@@ -127,32 +129,52 @@ static int plan(chc_ctx* ctx, size_t cells_cap = 49152) {
     if (const char* e = getenv("CHACRA_MAX_CELLS")) cells_cap = std::min<size_t>(cells_cap, (size_t)std::max(2048, atoi(e)));   // test hook
     size_t want_cells = std::min<size_t>(cells_cap, std::max<size_t>(2048, 3 * (size_t)T.n_pair));
     const size_t plain_bits = al16(4 * (size_t)((ctx->n_pairs + 31) / 32));
+    // shared-memory path: the sorted atoms as slot pairs (x0 x1 y0 y1 | z0 z1) + flag word, filter key and residue rank per
+    // slot (padded); the queues live in the float4 image of the record once that has been converted (when they fit there)
+    const size_t e_pairs = ((size_t)T.n_pair + 1) / 2 + E1_PAD_PAIRS;
+    const size_t partner_bytes = al16(4 * (size_t)E1_PARTNER_SETS * ((((size_t)T.n_pair + 2 * E1_PAD_PAIRS + 31) >> 5) + 2));
+    const size_t e_bytes = 2 * al16(16 * e_pairs) + partner_bytes + al16(4 * 2 * e_pairs) + al16(2 * 2 * e_pairs);
+    const bool alias_queues = queues <= 16 * (size_t)T.n_pair;
     ctx->small_path = false;
     for (size_t cells = std::min<size_t>(want_cells, 16384); cells >= 2048 && cells >= (size_t)T.n_pair; cells -= 1024) {
-        size_t need = 128 + (size_t)B.fixed_bytes + al16(2 * cells) + al16(4 * (size_t)T.n_pair) + plain_bits + queues + tables;
+        size_t need = 256 + (size_t)B.fixed_bytes + al16(2 * cells) + plain_bits + (alias_queues ? 0 : queues) + tables + e_bytes;
         if (need <= SMEM_LIMIT) { ctx->small_path = true; want_cells = cells; break; }
     }
     if (getenv("CHACRA_FORCE_LARGE")) ctx->small_path = false;     // test hook: exercise the in-place path on small systems
+    if (ctx->lkey_max >= (1 << 24) || T.R > 65535) ctx->small_path = false;   // locality keys are exact floats, residue ranks 16 bit there
     B.max_cells = (int)want_cells;
     B.cell16 = ctx->small_path ? 1 : 0;     // n_pair < 65 536 there by a wide margin; the large path keeps 32-bit starts
     const size_t cell_bytes = B.cell16 ? 2 : 4;
     B.stride = (long long)((B.off_cells + al16(cell_bytes * (size_t)B.max_cells) + 127) & ~size_t(127));
     size_t off = 0;
+    queue_bytes(ctx->small_path, &q1b, &qfb, &q2b);
+    bool queues_placed = false;
     if (ctx->small_path) {
         L.off_rec = (int)off;   off += al16((size_t)B.fixed_bytes); off = (off + 127) & ~size_t(127);
         L.off_cells = (int)off; off += al16(cell_bytes * (size_t)B.max_cells);
-        L.off_lkey = (int)off;  off += al16(4 * (size_t)T.n_pair);
+        L.off_lkey = 0;
         L.off_bits = (int)off;  off += plain_bits;
         L.bits_words = (int)((ctx->n_pairs + 31) / 32);
+        L.off_exy = (int)off;   off += al16(16 * e_pairs);
+        L.off_ez = (int)off;    off += al16(16 * e_pairs);
+        L.off_ek = (int)off;    off += partner_bytes;
+        L.off_sw = (int)off;    off += al16(4 * 2 * e_pairs);
+        L.off_sres = (int)off;  off += al16(2 * 2 * e_pairs);
+        if (alias_queues) {
+            L.off_q1 = L.off_qf = L.off_rec + B.off_spos;
+            L.off_q2 = L.off_qf + (int)qfb;
+            queues_placed = true;
+        }
     } else {
-        L.off_rec = L.off_cells = L.off_lkey = L.off_bits = 0;
+        L.off_rec = L.off_cells = L.off_lkey = L.off_bits = L.off_exy = L.off_ez = L.off_ek = L.off_sw = L.off_sres = 0;
         if ((ctx->n_pairs + 23) / 24 > 0x7fffffff) return CHC_E_TOO_LARGE;
         L.bits_words = (int)((ctx->n_pairs + 23) / 24);
     }
-    queue_bytes(ctx->small_path, &q1b, &qfb, &q2b);
-    L.off_q1 = (int)off; off += q1b;
-    L.off_qf = (int)off; off += qfb;
-    L.off_q2 = (int)off; off += q2b;
+    if (!queues_placed) {
+        L.off_q1 = (int)off; off += q1b;
+        L.off_qf = (int)off; off += qfb;
+        L.off_q2 = (int)off; off += q2b;
+    }
     L.off_tv = (int)off; off += al16(4 * (size_t)T.K * T.K);
     L.off_th = (int)off; off += al16(4 * (size_t)T.K * T.K);
     L.off_misc = (int)off; off += al16(sizeof(PairMisc));
@@ -276,6 +298,7 @@ extern "C" int chc_create(chc_ctx** out, const chc_topology* t, const chc_params
     P.near_d = p->near_dist_tol; P.near_a = p->near_angle_tol;
 
     ctx->n_pairs = (int64_t)T.R * (T.R + 1) / 2;
+    for (size_t k = 0; k < NP; ++k) ctx->lkey_max = std::max(ctx->lkey_max, t->pair_lkey[k]);
     rc = plan(ctx);
     if (rc != CHC_OK) return fail(ctx, rc, "topology with %d pair atoms / %d residues does not fit any kernel path", T.n_pair, T.R);
     CK(cudaFuncSetAttribute(pair_kernel_fn(ctx->small_path, p->track_near != 0), cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->L.total));

@@ -2,9 +2,27 @@
 #pragma once
 #include "frame_kernel.cuh"
 
-struct FrameCtx {            // per-CTA view of the current frame (shared memory on the small path, global on the large one)
-    const float4* spos;      // cell-sorted pair atoms: x, y, z, (dynamic flags | pair_index << I_PIDX_SHIFT)
-    const int* lkey;         // locality key by pair index
+// Per-CTA view of the current frame.  SOA = the shared-memory path: the sorted atoms live as slot pairs (x0 x1 y0 y1 | z0 z1) plus
+// per-slot words (flags | pair index, filter key with the locality key, residue rank); otherwise the binned record is read in
+// place (float4 per slot) and the locality key / residue rank come from the global tables by pair index.
+template <bool SOA>
+struct FrameCtxT {
+    const float4* spos;      // !SOA: cell-sorted pair atoms: x, y, z, (dynamic flags | pair_index << I_PIDX_SHIFT)
+    const int* lkey;         // !SOA: locality key by pair index
+    const float4* exy; const float4* ezk; const unsigned* sw; const unsigned short* sres;   // SOA: x0 x1 y0 y1 | z0 z1 lkey0 lkey1 (floats)
+    __device__ __forceinline__ float4 at(int j) const {
+        if (SOA) {
+            const float4 a = exy[j >> 1]; const float4 b = ezk[j >> 1];
+            const float w = __uint_as_float(sw[j]);
+            return (j & 1) ? make_float4(a.y, a.w, b.y, w) : make_float4(a.x, a.z, b.x, w);
+        }
+        return spos[j];
+    }
+    __device__ __forceinline__ int lk(int j, unsigned w) const {
+        if (SOA) { const float4 b = ezk[j >> 1]; return (int)((j & 1) ? b.w : b.z); }      // exact: locality keys are below 2^24 here
+        return lkey[w >> I_PIDX_SHIFT];
+    }
+    __device__ __forceinline__ int res(const DevTopo& T, int j, int pidx) const { return SOA ? (int)sres[j] : T.pair_res[pidx]; }
     const float* aux;        // [NA][3] donor hydrogens, ring atoms, cations
     unsigned* bits;          // residue-pair set of this frame
     unsigned gen;            // 0: plain bitset; 1..255: generation of the stamped bitset
@@ -16,7 +34,7 @@ struct FrameCtx {            // per-CTA view of the current frame (shared memory
 };
 
 // ---- R: pi-cation ----------------------------------------------------------------------------------
-template <bool TN>
+template <bool TN, class FrameCtx>
 __device__ __forceinline__ void ring_pc_task(const DevTopo& T, const DevParams& P, const DevOut& O, const FrameCtx& F,
                                              int c, int r) {
     const int* pa = T.ring_pc_aux + 3 * r;
@@ -70,7 +88,7 @@ __device__ __forceinline__ void ring_pc_task(const DevTopo& T, const DevParams& 
 }
 
 // ---- R: pi-stacking and T-stacking ---------------------------------------------------------------------
-template <bool TN>
+template <bool TN, class FrameCtx>
 __device__ __forceinline__ void ring_stack_task(const DevTopo& T, const DevParams& P, const DevOut& O, const FrameCtx& F,
                                                 int r1, int r2) {
     if (T.ring_res[r1] == T.ring_res[r2]) return;
@@ -147,6 +165,7 @@ __device__ __forceinline__ void ring_stack_task(const DevTopo& T, const DevParam
 // one of the things tested here): vdW / hydrophobic / their near-cutoff reports need dl >= vdw_res_diff; a salt bridge
 // needs an anion and a cation; a hydrogen bond needs both atoms in the hydrogen-bond selection; a water edge needs
 // exactly one solvent atom.
+template <class FrameCtx>
 __device__ __forceinline__ bool e2_may_classify(const DevParams& P, const FrameCtx& F, unsigned wi, unsigned wj) {
     const bool polar = (((wi & I_ANION) && (wj & I_CATION)) || ((wj & I_ANION) && (wi & I_CATION))) || (wi & wj & I_HBU) ||
                        ((wi ^ wj) & I_SOLV);
@@ -155,9 +174,10 @@ __device__ __forceinline__ bool e2_may_classify(const DevParams& P, const FrameC
 }
 
 // ---- E2: exact float32 d2 and class tests for one prefilter survivor ---------------------------------------
-template <bool TN>
-__device__ __forceinline__ unsigned e2_classify(const DevTopo& T, const DevParams& P, const FrameCtx& F, float4 a, float4 b,
+template <bool TN, class FrameCtx>
+__device__ __forceinline__ unsigned e2_classify(const DevTopo& T, const DevParams& P, const FrameCtx& F, int si, int sj,
                                                 float& d2_out) {
+    const float4 a = F.at(si), b = F.at(sj);
     float d2 = dist2_exact(a.x, a.y, a.z, b.x, b.y, b.z);
     d2_out = d2;
     unsigned wi = __float_as_uint(a.w), wj = __float_as_uint(b.w);
@@ -175,7 +195,7 @@ __device__ __forceinline__ unsigned e2_classify(const DevTopo& T, const DevParam
     }
     const bool edge_near = edge_pre && band_hb;
     if (!dual && !edge && !edge_near) return 0u;
-    int dl = abs(F.lkey[wi >> I_PIDX_SHIFT] - F.lkey[wj >> I_PIDX_SHIFT]);
+    int dl = abs(F.lk(si, wi) - F.lk(sj, wj));
     if (!dual) return dl != 0 ? ((edge ? C_HBW : 0u) | (edge_near ? C_NEARB : 0u)) : 0u;
     int e = (wi & I_ELEM) * T.K + (wj & I_ELEM);
     unsigned cls = 0;
@@ -217,7 +237,7 @@ __device__ __forceinline__ unsigned e2_classify(const DevTopo& T, const DevParam
 // monotone in |u x v| / (u.v), so away from the cutoff the decision follows from one multiply: P.hb_tan_lo / hb_tan_hi
 // bracket tan(cutoff) by a relative 4e-4 (~7e-3 degree at 70 degrees, far above every rounding step of the exact recipe
 // and above the 1e-3 degree near-cutoff band); only inside the bracket is the exact double-precision atan2 evaluated.
-template <bool TN>
+template <bool TN, class FrameCtx>
 __device__ __forceinline__ bool hb_direction(const DevTopo& T, const DevParams& P, const DevOut& O, const FrameCtx& F,
                                              float4 d, float4 a, int pd, int atom_d, int atom_a, bool report = true) {
     bool ok = false;
@@ -243,10 +263,10 @@ __device__ __forceinline__ bool hb_direction(const DevTopo& T, const DevParams& 
 }
 
 // ---- E3: everything that needs the global tables, for one classified pair ---------------------------------------
-template <bool TN>
+template <bool TN, class FrameCtx>
 __device__ __forceinline__ void e3_finish(const DevTopo& T, const DevParams& P, const DevOut& O, const FrameCtx& F,
                                           int i, int j, unsigned cls) {
-    float4 a = F.spos[i], b = F.spos[j];
+    float4 a = F.at(i), b = F.at(j);
     const float d2 = dist2_exact(a.x, a.y, a.z, b.x, b.y, b.z);      // as in e2_classify (same operands, same order)
     unsigned wi = __float_as_uint(a.w), wj = __float_as_uint(b.w);
     int pi = wi >> I_PIDX_SHIFT, pj = wj >> I_PIDX_SHIFT;
@@ -255,7 +275,7 @@ __device__ __forceinline__ void e3_finish(const DevTopo& T, const DevParams& P, 
     // directly bonded pairs are excluded by measure contacts / measure hbonds (Appendix A.4, A.5)
     bool need_bond = (cls & (C_SB | C_HB | C_HBW | C_NEARS | C_NEARB)) || ((si & I_XBOND) && (sj & I_XBOND));
     if (need_bond && is_bonded(T, pi, aj)) return;
-    int ri = T.pair_res[pi], rj = T.pair_res[pj];
+    int ri = F.res(T, i, pi), rj = F.res(T, j, pj);
     float dist = sqrtf(d2);
     if (cls & C_NEARS) emit_near(O, F.frame, CHC_NEAR_SB_DIST, ai, aj, (double)dist - P.sb_dist);
     if (cls & C_NEARB) emit_near(O, F.frame, CHC_NEAR_HB_DIST, ai, aj, (double)dist - P.hb_dist);

@@ -22,7 +22,7 @@
 #define Q1_CAP 128          // (i, j) survivors per warp (>= 64: see the flush in E1; 128 measured 1.2 % faster than 96, 160+ no better)
 #endif
 #ifndef QF_CAP
-#define QF_CAP 64           // survivors that passed the cheap filter, per warp
+#define QF_CAP 128          // survivors that passed the cheap filter, per warp (>= E1_TARGET + 32: see the flush in E1)
 #endif
 #ifndef Q2_CAP
 #define Q2_CAP 64           // classified pairs per warp and queue (plain, polar)
@@ -30,7 +30,7 @@
 #ifndef E1_TARGET
 #define E1_TARGET 32        // E1 runs until this many survivors are queued (one F batch)
 #endif
-static_assert(Q1_CAP - E1_TARGET >= 32 && E1_TARGET >= 32, "a lane's 32 pending hits must fit behind E1_TARGET queued survivors");
+static_assert(Q1_CAP - E1_TARGET >= 32 && QF_CAP - E1_TARGET >= 32 && E1_TARGET >= 32, "a lane's 32 pending hits must fit behind E1_TARGET queued survivors");
 #ifndef E1_UNROLL
 #define E1_UNROLL 2
 #endif
@@ -43,15 +43,37 @@ struct PairLayout {         // shared-memory plan of the pair kernel (bytes)
     int off_lkey;           // SMALL: locality keys by pair index
     int off_bits;           // SMALL: residue-pair bitset
     int off_q1, off_qf, off_q2, off_tv, off_th, off_misc;
+    // SMALL: the sorted atoms as slot pairs (x0 x1 y0 y1 | z0 z1), and per slot the flag word, the filter key, the residue rank.
+    // The float4 image the bulk copy lands (inside off_rec) is dead once these are built: the queues live there.
+    int off_exy, off_ez, off_ek, off_sw, off_sres;      // off_ez: float4 z0 z1 lkey0 lkey1 per slot pair; off_ek: partner bit arrays
     int bits_words;         // words of the residue-pair set (plain: P/32, stamped: P/24)
     int total;
 };
+
+// ---- packed float32 pairs (Blackwell FADD2 / FMUL2 / FFMA2): two neighbour slots per instruction in the E1 prefilter ----
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float lo, float hi) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b) { f32x2 r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+
+// The cheap SUFFICIENT test for "no class" (most close pairs sit in the same or adjacent residues and only matter when both atoms
+// are polar; e2_may_classify in frame_phases.cuh states it for the in-place path) runs inside the E1 loop on the shared-memory
+// path: the locality key rides along as a float next to z, sign(dl^2 - (vdw_res_diff - 1/2)^2) marks a LOCAL neighbour, and
+// "polar partner" comes from a bit per slot: partner set c of a lane = (c & 1 ? hydrogen-bond selection : 0) | (c & 2 ? cations : 0)
+// | (c & 4 ? anions : 0) | solvent, set 8 = everything but solvent (for a solvent atom): 9 bit arrays over the sorted slots.
+#define E1_PAD_PAIRS 20        // slot pairs past the last atom that the unmasked E1 loads may touch
+#define E1_PARTNER_SETS 9
+__device__ __forceinline__ int e1_partner_set(unsigned w) {
+    return (w & I_SOLV) ? 8 : (int)(((w >> 6) & 1u) | (((w >> 8) & 1u) << 1) | (((w >> 9) & 1u) << 2));   // hbu | anion -> wants cations | cation -> wants anions
+}
 
 struct PairMisc {
     unsigned long long bar;     // mbarrier of the bulk copies
     int cursor;                 // next tile of 32 sorted atoms
     int ring_cursor;            // next unit of 32 ring tasks
     int nmark;                  // waters with at least one hydrogen bond to a non-solvent atom (this frame)
+    int qcur[32];               // SMALL: entries in every warp's E2 queue (lanes reserve room with one shared atomic each)
 };
 
 // TN: the near-cutoff side channel is compiled in (chc_params.track_near); the counts-only production path carries none of it
@@ -69,7 +91,7 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
     // queue entries: the pair (i, j) of sorted slots is one word on the shared-memory path (slots < 65 536), two otherwise
     constexpr int QW = SMALL ? 1 : 2;
     using cell_t = typename std::conditional<SMALL, unsigned short, int>::type;     // BinLayout::cell16 <=> SMALL
-    unsigned* q1 = reinterpret_cast<unsigned*>(smem + L.off_q1) + warp * (QW * Q1_CAP);            // survivors
+    unsigned* q1 = reinterpret_cast<unsigned*>(smem + L.off_q1) + (SMALL ? 0 : warp * (QW * Q1_CAP));   // survivors (in-place path only)
     unsigned* qf = reinterpret_cast<unsigned*>(smem + L.off_qf) + warp * (QW * QF_CAP);            // filtered survivors
     unsigned* q2 = reinterpret_cast<unsigned*>(smem + L.off_q2) + warp * (2 * (QW + 1) * Q2_CAP);  // plain | polar: pair, class
     auto qput = [](unsigned* q, int cap, int at, unsigned i, unsigned j) {
@@ -79,11 +101,9 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
         if (SMALL) { const unsigned w = q[at]; i = w & 0xffffu; j = w >> 16; } else { i = q[at]; j = q[cap + at]; }
     };
     for (int k = tid; k < T.K * T.K; k += THREADS) { tv[k] = T.tv[k]; th[k] = T.th[k]; }
-    int* s_lkey = reinterpret_cast<int*>(smem + L.off_lkey);
     unsigned* bits;
     unsigned gen = 0;
     if (SMALL) {
-        for (int k = tid; k < T.n_pair; k += THREADS) s_lkey[k] = T.pair_lkey[k];
         bits = reinterpret_cast<unsigned*>(smem + L.off_bits);
         if (tid == 0) { mbar_init(&M->bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
     } else {
@@ -136,10 +156,43 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
             cells = reinterpret_cast<const cell_t*>(rec + B.off_cells);
         }
         __syncthreads();
+        float4* exy = reinterpret_cast<float4*>(smem + L.off_exy);
+        float4* ezk = reinterpret_cast<float4*>(smem + L.off_ez);
+        unsigned* partner = reinterpret_cast<unsigned*>(smem + L.off_ek);      // [E1_PARTNER_SETS][pwords] bit per sorted slot
+        const int pwords = ((T.n_pair + 2 * E1_PAD_PAIRS + 31) >> 5) + 2;
+        unsigned* sw = reinterpret_cast<unsigned*>(smem + L.off_sw);
+        unsigned short* sres = reinterpret_cast<unsigned short*>(smem + L.off_sres);
+        if (SMALL) {
+            // The float4 image becomes slot PAIRS (E1 tests two neighbours per packed instruction): x0 x1 y0 y1 | z0 z1, plus
+            // per slot the flag word, the filter key (locality key from the L1/L2-resident table) and the residue rank.
+            const int NPs = T.n_pair, np2 = (NPs + 1) >> 1;
+            for (int q = tid; q < np2 + E1_PAD_PAIRS; q += THREADS) {
+                const int j0 = 2 * q, j1 = j0 + 1;
+                const float4 far = make_float4(3.0e18f, 3.0e18f, 3.0e18f, 0.f);
+                const float4 a = j0 < NPs ? spos[j0] : far, b = j1 < NPs ? spos[j1] : far;
+                exy[q] = make_float4(a.x, b.x, a.y, b.y);
+                const unsigned wa = __float_as_uint(a.w), wb = __float_as_uint(b.w);
+                const int pa = wa >> I_PIDX_SHIFT, pb = wb >> I_PIDX_SHIFT;
+                ezk[q] = make_float4(a.z, b.z, j0 < NPs ? (float)__ldg(&T.pair_lkey[pa]) : -3.0e7f, j1 < NPs ? (float)__ldg(&T.pair_lkey[pb]) : -3.0e7f);
+                sw[j0] = wa; sw[j1] = wb;
+                sres[j0] = j0 < NPs ? (unsigned short)__ldg(&T.pair_res[pa]) : (unsigned short)0;
+                sres[j1] = j1 < NPs ? (unsigned short)__ldg(&T.pair_res[pb]) : (unsigned short)0;
+            }
+            for (int wd = warp; wd < pwords; wd += THREADS / 32) {        // partner bits, one word of 32 slots per warp round
+                const int j = wd * 32 + lane;
+                const unsigned w = j < NPs ? __float_as_uint(spos[j].w) : 0u;
+                const unsigned hbu = __ballot_sync(FULL, (w & I_HBU) != 0u), cat = __ballot_sync(FULL, (w & I_CATION) != 0u),
+                               an = __ballot_sync(FULL, (w & I_ANION) != 0u), solv = __ballot_sync(FULL, (w & I_SOLV) != 0u);
+                if (lane < E1_PARTNER_SETS)
+                    partner[lane * pwords + wd] = lane == 8 ? ~solv : (((lane & 1) ? hbu : 0u) | ((lane & 2) ? cat : 0u) | ((lane & 4) ? an : 0u) | solv);
+            }
+            if (tid < 32) M->qcur[tid] = 0;
+            __syncthreads();               // from here on the float4 image is dead: its shared memory holds the (empty) queues
+        }
         const int px = hdr->nc[0] + 2, pxy = px * (hdr->nc[1] + 2), ncell = hdr->ncell;
-        FrameCtx F{spos, SMALL ? s_lkey : T.pair_lkey, aux, bits, gen, tv, th,
-                   hpmask + (size_t)(gidx / frag_frames - frag0) * T.n_pair, (int)gidx,
-                   water_scratch(wscratch, blockIdx.x, T.n_solv), &M->nmark};
+        FrameCtxT<SMALL> F{spos, T.pair_lkey, exy, ezk, sw, sres, aux, bits, gen, tv, th,
+                           hpmask + (size_t)(gidx / frag_frames - frag0) * T.n_pair, (int)gidx,
+                           water_scratch(wscratch, blockIdx.x, T.n_solv), &M->nmark};
         // ---- E: pair interactions ------------------------------------------------------------------------------
         const float cut2p = P.pre2 * 1.000002f;       // largest cutoff^2 of the enabled pair types, padded for the fused filter
         int q1n = 0, qfn = 0, q2n = 0, q3n = 0;
@@ -156,105 +209,214 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
         float ix = 0.f, iy = 0.f, iz = 0.f;
         unsigned mask = 0u; int mbase = 0;             // this lane's hits of the last chunk not yet queued: j = mbase + bit
         bool exhausted = false;
+        // SMALL: this lane's locality key (float) and partner bit array; lead = its range starts on an odd slot
+        float my_lk = 0.f; const unsigned* my_partner = partner; int lead = 0;
+        const float loc_thr = P.vdw_rd > 0 ? -((float)P.vdw_rd - 0.5f) * ((float)P.vdw_rd - 0.5f) : 1.0f;   // dl^2 + loc_thr < 0 <=> |dl| < vdw_res_diff
         for (;;) {
             // ---- E1 ----
-            while (q1n < E1_TARGET && !exhausted) {
-                if (__any_sync(FULL, mask != 0u)) {
-                    // queue the pending hits, whole lanes at a time, as far as the queue has room (q1n < 32 here and a
-                    // lane holds at most 32 hits, so the first pending lane always fits: Q1_CAP - 32 >= 32)
-                    const int cnt = __popc(mask);
-                    int incl = cnt;
-#pragma unroll
-                    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += t; }
-                    const bool ok = incl <= Q1_CAP - q1n;
-                    if (ok) {
-                        int at = q1n + incl - cnt;
-                        unsigned m = mask;
-                        while (m) {
-                            const int k = __ffs(m) - 1;
-                            m &= m - 1u;
-                            qput(q1, Q1_CAP, at, (unsigned)my_i, (unsigned)(mbase + k));
-                            ++at;
+            if (SMALL) {
+                // Slot pairs, packed float32 arithmetic; distance AND locality / polar-partner filter in one pass, survivors queued
+                // straight into the E2 queue.
+                while (qfn < E1_TARGET && !exhausted) {
+                    if (__any_sync(FULL, mask != 0u)) {
+                        // Queue the pending survivors: every lane reserves room with ONE shared atomic on the warp's cursor (no scan).
+                        // Reservations are served in some order; those past the capacity are taken back (all later ones are past it too,
+                        // so the cursor ends on the last entry written) and stay pending until E2 has drained a batch.  qfn < 32 here
+                        // and a lane holds at most 32, so somebody always gets in.
+                        const int cnt = __popc(mask);
+                        if (cnt) {
+                            int at = atomicAdd(&M->qcur[warp], cnt);
+                            if (at + cnt <= QF_CAP) {
+                                unsigned m = mask;
+                                while (m) {
+                                    const int k = __ffs(m) - 1;
+                                    m &= m - 1u;
+                                    qf[at++] = (unsigned)my_i | ((unsigned)(mbase + k) << 16);
+                                }
+                                mask = 0u;
+                            } else atomicSub(&M->qcur[warp], cnt);
                         }
-                        mask = 0u;
+                        __syncwarp();
+                        qfn = *reinterpret_cast<volatile int*>(&M->qcur[warp]);
+                        if (qfn >= E1_TARGET) break;
+                        if (__any_sync(FULL, mask != 0u)) break;     // the queue is full: let E2 run
+                        continue;
                     }
-                    q1n += __reduce_max_sync(FULL, ok ? incl : 0);
-                    continue;
-                }
-                k0 += 32;
-                if (k0 >= maxlen) {                    // next unit of work = (tile, range); fine grain keeps the frame's tail short
-                    int u = 0;
-                    if (lane == 0) u = atomicAdd(&M->cursor, 1);
-                    u = __shfl_sync(FULL, u, 0);
-                    if (u >= nunits) { exhausted = true; break; }
-                    const int t = (int)__umulhi((unsigned)u, nr_magic);         // u / nr (u < 2^16: exact with the rounded-up reciprocal)
-                    r = u - t * nr;
-                    if (t != tile) {
-                        tile = t;
-                        my_i = t * 32 + lane;
-                        if (my_i < nA) {
-                            const float4 p = spos[my_i];
-                            ix = p.x; iy = p.y; iz = p.z;
-                            my_c = (cell_of(iz, hdr->org[2], hdr->inv, hdr->nc[2]) + 1) * pxy +
-                                   (cell_of(iy, hdr->org[1], hdr->inv, hdr->nc[1]) + 1) * px +
-                                   cell_of(ix, hdr->org[0], hdr->inv, hdr->nc[0]) + 1;
-                        } else my_i = -1;
-                    }
-                    len = 0;
-                    if (my_i >= 0) {
-                        if (r == 0) { beg = my_i + 1; len = (int)cells[my_c + 2] - beg; }
-                        else {
-                            int base;
-                            if (r < 5) base = my_c + ((r == 1 || r == 4) - (r == 2)) * px + (r >= 2 ? pxy : 0);
-                            else { const int q = r - 5; base = my_c + ncell + (q % 3 - 1) * px + (q / 3 - 1) * pxy; }
-                            beg = (int)cells[base - 1];
-                            len = (int)cells[base + 2] - beg;
+                    k0 += 32;
+                    if (k0 >= maxlen) {                // next unit of work = (tile, range)
+                        int u = 0;
+                        if (lane == 0) u = atomicAdd(&M->cursor, 1);
+                        u = __shfl_sync(FULL, u, 0);
+                        if (u >= nunits) { exhausted = true; break; }
+                        const int t = (int)__umulhi((unsigned)u, nr_magic);
+                        r = u - t * nr;
+                        if (t != tile) {
+                            tile = t;
+                            my_i = t * 32 + lane;
+                            if (my_i < nA) {
+                                const float4 p = F.at(my_i);
+                                ix = p.x; iy = p.y; iz = p.z;
+                                my_lk = (float)F.lk(my_i, 0u);
+                                my_partner = partner + e1_partner_set(__float_as_uint(p.w)) * pwords;
+                                my_c = (cell_of(iz, hdr->org[2], hdr->inv, hdr->nc[2]) + 1) * pxy +
+                                       (cell_of(iy, hdr->org[1], hdr->inv, hdr->nc[1]) + 1) * px +
+                                       cell_of(ix, hdr->org[0], hdr->inv, hdr->nc[0]) + 1;
+                            } else my_i = -1;
                         }
+                        len = 0; lead = 0;
+                        if (my_i >= 0) {
+                            if (r == 0) { beg = my_i + 1; len = (int)cells[my_c + 2] - beg; }
+                            else {
+                                int base;
+                                if (r < 5) base = my_c + ((r == 1 || r == 4) - (r == 2)) * px + (r >= 2 ? pxy : 0);
+                                else { const int q = r - 5; base = my_c + ncell + (q % 3 - 1) * px + (q / 3 - 1) * pxy; }
+                                beg = (int)cells[base - 1];
+                                len = (int)cells[base + 2] - beg;
+                            }
+                            lead = beg & 1;            // ranges are walked from an even slot; the slot before an odd start is masked off
+                            len = len > 0 ? len + lead : 0;
+                            beg -= lead;
+                        }
+                        maxlen = __reduce_max_sync(FULL, len);
+                        k0 = 0;
+                        if (maxlen == 0) continue;
                     }
-                    maxlen = __reduce_max_sync(FULL, len);
-                    k0 = 0;
-                    if (maxlen == 0) continue;
-                }
-                // 32 candidate slots of every lane's range, four at a time: fused-multiply-add d2 against the padded largest cutoff
-                // (a superset filter: every class test in E2 compares the EXACT float32 d2 with its own cutoff).
-                // Slots past the lane's own range are computed too (they lie inside the record: at most 35 slots after
-                // the sorted atoms, where the aux atoms and the cell starts follow) and masked off afterwards.
-                const int n = min(32, maxlen - k0);
-                const int lim = len - k0;
-                mbase = beg + k0;
-                const float4* pj = spos + mbase;
-                unsigned m = 0u;
+                    // up to 16 slot pairs of every lane's range: fused-multiply-add d2 of two neighbours at a time against the padded
+                    // largest cutoff (a superset filter: every class test in E2 compares the EXACT float32 d2 with its own cutoff).
+                    // The sign bit of cut - d2 is shifted into the miss mask (first slot ends up highest).  Slots past the lane's own
+                    // range are computed too (inside the padded arrays) and masked off afterwards.
+                    const int npair = (min(32, maxlen - k0) + 1) >> 1;
+                    mbase = beg + k0;
+                    const float4* pxy2 = exy + (mbase >> 1);
+                    const float4* pzk2 = ezk + (mbase >> 1);
+                    const f32x2 X = pk2(ix, ix), Y = pk2(iy, iy), Z = pk2(iz, iz), C2 = pk2(cut2p, cut2p), LK = pk2(my_lk, my_lk),
+                                TH = pk2(loc_thr, loc_thr);
+                    unsigned miss = 0u, loc = 0u;
 CHC_UNROLL(E1_UNROLL)
-                for (int k4 = 0; k4 < n; k4 += 4) {
-                    const float4 a = pj[k4], b = pj[k4 + 1], c = pj[k4 + 2], d = pj[k4 + 3];
-                    const unsigned nib = (dist2_fused(ix, iy, iz, a.x, a.y, a.z) <= cut2p ? 1u : 0u) |
-                                         (dist2_fused(ix, iy, iz, b.x, b.y, b.z) <= cut2p ? 2u : 0u) |
-                                         (dist2_fused(ix, iy, iz, c.x, c.y, c.z) <= cut2p ? 4u : 0u) |
-                                         (dist2_fused(ix, iy, iz, d.x, d.y, d.z) <= cut2p ? 8u : 0u);
-                    m |= nib << k4;
+                    for (int q = 0; q < npair; ++q) {
+                        const float4 a = pxy2[q];
+                        const float4 b = pzk2[q];
+                        const f32x2 dx = sub2(X, pk2(a.x, a.y)), dy = sub2(Y, pk2(a.z, a.w)), dz = sub2(Z, pk2(b.x, b.y));
+                        const f32x2 sg = sub2(C2, fma2(dz, dz, fma2(dy, dy, mul2(dx, dx))));
+                        const f32x2 dl = sub2(LK, pk2(b.z, b.w));
+                        const f32x2 lc = fma2(dl, dl, TH);
+                        miss = __funnelshift_l((unsigned)sg, miss, 1);
+                        loc = __funnelshift_l((unsigned)lc, loc, 1);
+                        miss = __funnelshift_l((unsigned)(sg >> 32), miss, 1);
+                        loc = __funnelshift_l((unsigned)(lc >> 32), loc, 1);
+                    }
+                    // slot k of the chunk sits at bit 2 npair - 1 - k: bring it to bit k; a hit survives when it is not local or when
+                    // the neighbour is a polar partner of this lane's atom; keep [lead, len) of the lane's range
+                    const int sh = 32 - 2 * npair;
+                    const unsigned hits = ~__brev(miss << sh), local = __brev(loc << sh);
+                    const int wq = mbase >> 5, wr = mbase & 31;
+                    const unsigned part = __funnelshift_r(my_partner[wq], my_partner[wq + 1], wr);
+                    const int lo = max(lead - k0, 0), hi = min(len - k0, 32);
+                    const unsigned valid = hi > lo ? ((hi >= 32 ? 0xffffffffu : ((1u << hi) - 1u)) & ~((1u << lo) - 1u)) : 0u;
+                    mask = hits & (~local | part) & valid;
                 }
-                m = lim >= 32 ? m : (lim > 0 ? m & ((1u << lim) - 1u) : 0u);
-                mask = m;
-            }
-            if (q1n == 0 && qfn == 0 && q2n == 0 && q3n == 0) break;           // only reachable when exhausted
-            __syncwarp();
-            // ---- F: up to 32 survivors through the cheap sufficient test for "no class": most close pairs sit in the
-            //      same or adjacent residues and only matter when both atoms are polar ----
-            if (q1n > 0) {
-                const int nb = min(q1n, 32);
-                q1n -= nb;
-                bool keep = false; unsigned ei = 0u, ej = 0u;
-                if (lane < nb) {
-                    qget(q1, Q1_CAP, q1n + lane, ei, ej);
-                    keep = e2_may_classify(P, F, __float_as_uint(spos[ei].w), __float_as_uint(spos[ej].w));
-                }
-                const unsigned bal = __ballot_sync(FULL, keep);
-                if (keep) {
-                    const int at = qfn + __popc(bal & ((1u << lane) - 1u));
-                    qput(qf, QF_CAP, at, ei, ej);
-                }
-                qfn += __popc(bal);
+                if (exhausted) qfn = *reinterpret_cast<volatile int*>(&M->qcur[warp]);
+                if (qfn == 0 && q2n == 0 && q3n == 0) break;           // only reachable when exhausted
                 __syncwarp();
+            } else {
+                while (q1n < E1_TARGET && !exhausted) {
+                    if (__any_sync(FULL, mask != 0u)) {
+                        // queue the pending hits, whole lanes at a time, as far as the queue has room (q1n < 32 here and a
+                        // lane holds at most 32 hits, so the first pending lane always fits: Q1_CAP - 32 >= 32)
+                        const int cnt = __popc(mask);
+                        int incl = cnt;
+#pragma unroll
+                        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += t; }
+                        const bool ok = incl <= Q1_CAP - q1n;
+                        if (ok) {
+                            int at = q1n + incl - cnt;
+                            unsigned m = mask;
+                            while (m) {
+                                const int k = __ffs(m) - 1;
+                                m &= m - 1u;
+                                qput(q1, Q1_CAP, at, (unsigned)my_i, (unsigned)(mbase + k));
+                                ++at;
+                            }
+                            mask = 0u;
+                        }
+                        q1n += __reduce_max_sync(FULL, ok ? incl : 0);
+                        continue;
+                    }
+                    k0 += 32;
+                    if (k0 >= maxlen) {                    // next unit of work = (tile, range); fine grain keeps the frame's tail short
+                        int u = 0;
+                        if (lane == 0) u = atomicAdd(&M->cursor, 1);
+                        u = __shfl_sync(FULL, u, 0);
+                        if (u >= nunits) { exhausted = true; break; }
+                        const int t = (int)__umulhi((unsigned)u, nr_magic);         // u / nr (u < 2^16: exact with the rounded-up reciprocal)
+                        r = u - t * nr;
+                        if (t != tile) {
+                            tile = t;
+                            my_i = t * 32 + lane;
+                            if (my_i < nA) {
+                                const float4 p = spos[my_i];
+                                ix = p.x; iy = p.y; iz = p.z;
+                                my_c = (cell_of(iz, hdr->org[2], hdr->inv, hdr->nc[2]) + 1) * pxy +
+                                       (cell_of(iy, hdr->org[1], hdr->inv, hdr->nc[1]) + 1) * px +
+                                       cell_of(ix, hdr->org[0], hdr->inv, hdr->nc[0]) + 1;
+                            } else my_i = -1;
+                        }
+                        len = 0;
+                        if (my_i >= 0) {
+                            if (r == 0) { beg = my_i + 1; len = (int)cells[my_c + 2] - beg; }
+                            else {
+                                int base;
+                                if (r < 5) base = my_c + ((r == 1 || r == 4) - (r == 2)) * px + (r >= 2 ? pxy : 0);
+                                else { const int q = r - 5; base = my_c + ncell + (q % 3 - 1) * px + (q / 3 - 1) * pxy; }
+                                beg = (int)cells[base - 1];
+                                len = (int)cells[base + 2] - beg;
+                            }
+                        }
+                        maxlen = __reduce_max_sync(FULL, len);
+                        k0 = 0;
+                        if (maxlen == 0) continue;
+                    }
+                    // 32 candidate slots of every lane's range, four at a time: fused-multiply-add d2 against the padded largest cutoff
+                    // (a superset filter: every class test in E2 compares the EXACT float32 d2 with its own cutoff).
+                    // Slots past the lane's own range are computed too (they lie inside the record: at most 35 slots after
+                    // the sorted atoms, where the aux atoms and the cell starts follow) and masked off afterwards.
+                    const int n = min(32, maxlen - k0);
+                    const int lim = len - k0;
+                    mbase = beg + k0;
+                    const float4* pj = spos + mbase;
+                    unsigned m = 0u;
+CHC_UNROLL(E1_UNROLL)
+                    for (int k4 = 0; k4 < n; k4 += 4) {
+                        const float4 a = pj[k4], b = pj[k4 + 1], c = pj[k4 + 2], d = pj[k4 + 3];
+                        const unsigned nib = (dist2_fused(ix, iy, iz, a.x, a.y, a.z) <= cut2p ? 1u : 0u) |
+                                             (dist2_fused(ix, iy, iz, b.x, b.y, b.z) <= cut2p ? 2u : 0u) |
+                                             (dist2_fused(ix, iy, iz, c.x, c.y, c.z) <= cut2p ? 4u : 0u) |
+                                             (dist2_fused(ix, iy, iz, d.x, d.y, d.z) <= cut2p ? 8u : 0u);
+                        m |= nib << k4;
+                    }
+                    m = lim >= 32 ? m : (lim > 0 ? m & ((1u << lim) - 1u) : 0u);
+                    mask = m;
+                }
+                if (q1n == 0 && qfn == 0 && q2n == 0 && q3n == 0) break;           // only reachable when exhausted
+                __syncwarp();
+                // ---- F: up to 32 survivors through the cheap sufficient test for "no class": most close pairs sit in the
+                //      same or adjacent residues and only matter when both atoms are polar ----
+                if (q1n > 0) {
+                    const int nb = min(q1n, 32);
+                    q1n -= nb;
+                    bool keep = false; unsigned ei = 0u, ej = 0u;
+                    if (lane < nb) {
+                        qget(q1, Q1_CAP, q1n + lane, ei, ej);
+                        keep = e2_may_classify(P, F, __float_as_uint(spos[ei].w), __float_as_uint(spos[ej].w));
+                    }
+                    const unsigned bal = __ballot_sync(FULL, keep);
+                    if (keep) {
+                        const int at = qfn + __popc(bal & ((1u << lane) - 1u));
+                        qput(qf, QF_CAP, at, ei, ej);
+                    }
+                    qfn += __popc(bal);
+                    __syncwarp();
+                }
             }
             // ---- E2: 32 filtered survivors; classified pairs go to the plain queue (vdW / hydrophobic only) or to the
             //      polar queue (salt bridge, hydrogen bond, water edge), so that an E3 batch runs one kind of code ----
@@ -262,10 +424,11 @@ CHC_UNROLL(E1_UNROLL)
             if (qfn >= 32 || (drain1 && qfn > 0)) {
                 const int nb = min(qfn, 32);
                 qfn -= nb;
+                if (SMALL) { if (lane == 0) M->qcur[warp] = qfn; }     // the lanes' reservations start from here again
                 unsigned cls = 0u; float d2 = 0.f; unsigned ei = 0u, ej = 0u;
                 if (lane < nb) {
                     qget(qf, QF_CAP, qfn + lane, ei, ej);
-                    cls = e2_classify<TN>(T, P, F, spos[ei], spos[ej], d2);
+                    cls = e2_classify<TN>(T, P, F, (int)ei, (int)ej, d2);
                 }
                 const bool polar = (cls & (C_SB | C_HB | C_HBW | C_NEARS | C_NEARB)) != 0u;
                 const unsigned balp = __ballot_sync(FULL, polar), balv = __ballot_sync(FULL, cls != 0u && !polar);

@@ -13,13 +13,14 @@
 #include "frame_phases.cuh"
 #include "bin_kernel.cuh"
 
+template <class FrameCtx>
 __device__ __forceinline__ void bridge_emit(const DevTopo& T, const DevParams& P, const DevOut& O, const FrameCtx& F,
                                             int sa, int sb, int atom_w1, int atom_w2) {
-    const float4 xa = F.spos[sa], xb = F.spos[sb];
+    const float4 xa = F.at(sa), xb = F.at(sb);
     const unsigned wa = __float_as_uint(xa.w), wb = __float_as_uint(xb.w);
     if (!(((wa & I_S1) && (wb & I_S2)) || ((wa & I_S2) && (wb & I_S1)))) return;          // filter_dual_selection
     const int pa = wa >> I_PIDX_SHIFT, pb = wb >> I_PIDX_SHIFT;
-    if (abs(F.lkey[pa] - F.lkey[pb]) < P.hb_rd) return;                                   // same chain, |dresid| < res_diff
+    if (abs(F.lk(sa, wa) - F.lk(sb, wb)) < P.hb_rd) return;                                   // same chain, |dresid| < res_diff
     const bool lig = ((T.pair_info[pa] | T.pair_info[pb]) & I_LIG) != 0;
     const int itype = atom_w2 < 0 ? (lig ? CHC_LWB : CHC_WB) : (lig ? CHC_LWB2 : CHC_WB2);
     count_pair(O, F.bits, F.gen, T.pair_res[pa], T.pair_res[pb], T.R);
@@ -28,7 +29,7 @@ __device__ __forceinline__ void bridge_emit(const DevTopo& T, const DevParams& P
                     sqrtf(dist2_exact(xa.x, xa.y, xa.z, xb.x, xb.y, xb.z)));
 }
 
-template <bool TN, class cell_t>
+template <bool TN, class cell_t, class FrameCtx>
 __device__ __forceinline__ void water_bridges(const DevTopo& T, const DevParams& P, const DevOut& O, const FrameCtx& F,
                                               const WaterScratch& W, const cell_t* cells, int px, int pxy, int ncell,
                                               const BinHeader* hdr, const int* nmark, int tid, int nthreads) {
@@ -42,7 +43,7 @@ __device__ __forceinline__ void water_bridges(const DevTopo& T, const DevParams&
         const int sw = W.slot[ord];
         const int nw = min(W.cnt[ord], WADJ);
         const int* Nw = W.adj + (size_t)ord * WADJ;
-        const float4 xw = F.spos[sw];
+        const float4 xw = F.at(sw);
         const unsigned ww = __float_as_uint(xw.w);
         const int pw = ww >> I_PIDX_SHIFT;
         const int aw = T.pair_atom[pw];
@@ -62,7 +63,7 @@ __device__ __forceinline__ void water_bridges(const DevTopo& T, const DevParams&
                 const int base = c0 + g * ncell + (r % 3 - 1) * px + (r / 3 - 1) * pxy;
                 const int jb = (int)cells[base - 1], je = (int)cells[base + 2];
                 for (int j = jb + lane; j < je; j += 32) {
-                    const float4 xj = F.spos[j];
+                    const float4 xj = F.at(j);
                     const unsigned wj = __float_as_uint(xj.w);
                     if (!(wj & I_SOLV)) continue;
                     const int pj = wj >> I_PIDX_SHIFT;
@@ -71,7 +72,7 @@ __device__ __forceinline__ void water_bridges(const DevTopo& T, const DevParams&
                     const int ordj = T.pair_solv_ord[pj];
                     const int nj = min(W.cnt[ordj], WADJ);
                     if (nj == 0) continue;                                      // no non-solvent partner: cannot close a bridge
-                    if (F.lkey[pw] == F.lkey[pj]) continue;                     // same residue (hbonds.py:131)
+                    if (F.lk(sw, ww) == F.lk(j, wj)) continue;                     // same residue (hbonds.py:131)
                     const float d2w = dist2_exact(xw.x, xw.y, xw.z, xj.x, xj.y, xj.z);
                     const double dlw = TN ? (double)sqrtf(d2w) - P.hb_dist : 1.0;
                     if (d2w > P.hb2 && !(fabs(dlw) < P.near_d)) continue;
