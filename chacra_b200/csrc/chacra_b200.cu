@@ -124,7 +124,10 @@ static int plan(chc_ctx* ctx, size_t cells_cap = 49152) {
     };
     size_t q1b, qfb, q2b;
     const size_t queues = queue_bytes(true, &q1b, &qfb, &q2b);
-    const size_t tables = 2 * al16(4 * (size_t)T.K * T.K) + al16(sizeof(PairMisc));
+    // ring phase: float centroids + the list of (cation, ring) / (ring, ring) tasks that pass the centroid prefilter
+    const size_t ring_bytes = 0;
+    const int rlist_cap = T.n_rings <= 128 ? 1024 : 8192;
+    const size_t tables = 2 * al16(4 * (size_t)T.K * T.K) + al16(sizeof(PairMisc)) + ring_bytes + 4 * (size_t)rlist_cap;
     // ~3 cells per pair atom keeps the cells at the cutoff size for protein-like densities
     if (const char* e = getenv("CHACRA_MAX_CELLS")) cells_cap = std::min<size_t>(cells_cap, (size_t)std::max(2048, atoi(e)));   // test hook
     size_t want_cells = std::min<size_t>(cells_cap, std::max<size_t>(2048, 3 * (size_t)T.n_pair));
@@ -133,7 +136,8 @@ static int plan(chc_ctx* ctx, size_t cells_cap = 49152) {
     // slot (padded); the queues live in the float4 image of the record once that has been converted (when they fit there)
     const size_t e_pairs = ((size_t)T.n_pair + 1) / 2 + E1_PAD_PAIRS;
     const size_t partner_bytes = al16(4 * (size_t)E1_PARTNER_SETS * ((((size_t)T.n_pair + 2 * E1_PAD_PAIRS + 31) >> 5) + 2));
-    const size_t e_bytes = 2 * al16(16 * e_pairs) + partner_bytes + al16(4 * 2 * e_pairs) + al16(2 * 2 * e_pairs);
+    const size_t bypidx_bytes = al16(4 * (size_t)T.n_pair) + al16(2 * (size_t)T.n_pair) + al16((size_t)T.n_pair);
+    const size_t e_bytes = 2 * al16(16 * e_pairs) + partner_bytes + al16(4 * 2 * e_pairs) + bypidx_bytes;
     const bool alias_queues = queues <= 16 * (size_t)T.n_pair;
     ctx->small_path = false;
     for (size_t cells = std::min<size_t>(want_cells, 16384); cells >= 2048 && cells >= (size_t)T.n_pair; cells -= 1024) {
@@ -159,7 +163,10 @@ static int plan(chc_ctx* ctx, size_t cells_cap = 49152) {
         L.off_ez = (int)off;    off += al16(16 * e_pairs);
         L.off_ek = (int)off;    off += partner_bytes;
         L.off_sw = (int)off;    off += al16(4 * 2 * e_pairs);
-        L.off_sres = (int)off;  off += al16(2 * 2 * e_pairs);
+        L.off_sres = 0;
+        L.off_plkf = (int)off;  off += al16(4 * (size_t)T.n_pair);
+        L.off_pres = (int)off;  off += al16(2 * (size_t)T.n_pair);
+        L.off_pst = (int)off;   off += al16((size_t)T.n_pair);
         if (alias_queues) {
             L.off_q1 = L.off_qf = L.off_rec + B.off_spos;
             L.off_q2 = L.off_qf + (int)qfb;
@@ -167,6 +174,7 @@ static int plan(chc_ctx* ctx, size_t cells_cap = 49152) {
         }
     } else {
         L.off_rec = L.off_cells = L.off_lkey = L.off_bits = L.off_exy = L.off_ez = L.off_ek = L.off_sw = L.off_sres = 0;
+        L.off_plkf = L.off_pres = L.off_pst = 0;
         if ((ctx->n_pairs + 23) / 24 > 0x7fffffff) return CHC_E_TOO_LARGE;
         L.bits_words = (int)((ctx->n_pairs + 23) / 24);
     }
@@ -178,6 +186,9 @@ static int plan(chc_ctx* ctx, size_t cells_cap = 49152) {
     L.off_tv = (int)off; off += al16(4 * (size_t)T.K * T.K);
     L.off_th = (int)off; off += al16(4 * (size_t)T.K * T.K);
     L.off_misc = (int)off; off += al16(sizeof(PairMisc));
+    L.off_rc = (int)off; off += ring_bytes;
+    L.off_rlist = (int)off; off += 4 * (size_t)rlist_cap;
+    L.rlist_cap = rlist_cap;
     L.total = (int)off;
     ctx->bin_smem = (int)al16(4 * (size_t)B.max_cells);
     if ((size_t)L.total > SMEM_LIMIT || (size_t)ctx->bin_smem + 1024 > SMEM_LIMIT) return CHC_E_TOO_LARGE;
@@ -238,7 +249,24 @@ extern "C" int chc_create(chc_ctx** out, const chc_topology* t, const chc_params
     int rc;
     const size_t NP = t->n_pair, NR = t->n_rings, NC = t->n_cations, K2 = (size_t)t->n_elem * t->n_elem;
 #define UP(field, src, n) if ((rc = upload(ctx, src, (size_t)(n), &T.field)) != CHC_OK) return rc
-    UP(pair_atom, t->pair_atom, NP); UP(pair_info, t->pair_info, NP); UP(pair_lkey, t->pair_lkey, NP);
+    // I_PBOND: a polar pair atom (hydrogen-bond selection, ion, solvent) bonded to another polar pair atom -- only such pairs ever
+    // need the bonded-pair test of measure contacts / measure hbonds in the polar classes (frame_phases.cuh e3_finish)
+    std::vector<uint32_t> info(t->pair_info, t->pair_info + NP);
+    {
+        const uint32_t polar = I_HBU | I_ANION | I_CATION | I_SOLV;
+        std::vector<int> a2p((size_t)t->n_atoms, -1);
+        for (size_t k = 0; k < NP; ++k) if (t->pair_atom[k] >= 0 && t->pair_atom[k] < t->n_atoms) a2p[t->pair_atom[k]] = (int)k;
+        for (size_t k = 0; k < NP; ++k) {
+            info[k] &= ~I_PBOND;
+            if (!(info[k] & polar)) continue;
+            for (int b = t->pair_bond_start[k]; b < t->pair_bond_start[k + 1]; ++b) {
+                const int a = t->pair_bond_adj[b];
+                const int q = (a >= 0 && a < t->n_atoms) ? a2p[a] : -1;
+                if (q >= 0 && (t->pair_info[q] & polar)) { info[k] |= I_PBOND; break; }
+            }
+        }
+    }
+    UP(pair_atom, t->pair_atom, NP); UP(pair_info, info.data(), NP); UP(pair_lkey, t->pair_lkey, NP);
     UP(pair_res, t->pair_res, NP); UP(pair_resid, t->pair_resid, NP); UP(pair_h_start, t->pair_h_start, NP + 1);
     UP(pair_bond_start, t->pair_bond_start, NP + 1); UP(pair_bond_adj, t->pair_bond_adj, t->n_bond_adj);
     UP(aux_atom, t->aux_atom, t->n_aux); UP(pair_solv_ord, t->pair_solv_ord, NP);
@@ -301,7 +329,7 @@ extern "C" int chc_create(chc_ctx** out, const chc_topology* t, const chc_params
     for (size_t k = 0; k < NP; ++k) ctx->lkey_max = std::max(ctx->lkey_max, t->pair_lkey[k]);
     rc = plan(ctx);
     if (rc != CHC_OK) return fail(ctx, rc, "topology with %d pair atoms / %d residues does not fit any kernel path", T.n_pair, T.R);
-    CK(cudaFuncSetAttribute(pair_kernel_fn(ctx->small_path, p->track_near != 0), cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->L.total));
+    CK(cudaFuncSetAttribute(pair_kernel_fn(ctx->small_path, p->track_near != 0 || p->emit_contacts != 0), cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->L.total));
     // binning kernel variant: registers hold the frame's pair atoms when they fit (one HBM pass), else three gather passes
     ctx->bin_variant = T.n_pair <= 512 * 8 ? 1 : (T.n_pair <= 1024 * 8 ? 2 : 0);
     // frames that fit in shared memory stream through bulk async copies (bin_tma_kernel.cuh)
@@ -513,7 +541,7 @@ static int submit_impl(chc_ctx* ctx, int state, const float* d_xyz, const long l
             int nn = n; long long fi = first_index + c0, fr0 = frag0; int ff = F;
             unsigned* gs = ctx->small_path ? nullptr : ctx->gstamp; unsigned* gt = ctx->small_path ? nullptr : ctx->gstate;
             void* args[] = {&ctx->T, &ctx->P, &O, &ctx->L, &ctx->B, &ctx->binned, &nn, &fi, &ff, &fr0, &ctx->hpmask, &gs, &gt, &ctx->wscratch};
-            CK(cudaLaunchKernel(pair_kernel_fn(ctx->small_path, ctx->P.track_near != 0), dim3(grid), dim3(PAIR_THREADS), args, ctx->L.total, stream));
+            CK(cudaLaunchKernel(pair_kernel_fn(ctx->small_path, ctx->P.track_near != 0 || ctx->P.emit != 0), dim3(grid), dim3(PAIR_THREADS), args, ctx->L.total, stream));
         }
         CK(cudaGetLastError());
         if (ctx->timing) { CK(cudaEventRecord(ev.c, stream)); ctx->ev_pending.push_back(ev); }

@@ -24,6 +24,7 @@
 #define I_BB     (1u << 15)
 #define I_CYS    (1u << 16)
 #define I_XBOND  (1u << 17)
+#define I_PBOND  (1u << 18)   // set by chc_create: bonded to a polar pair atom (hydrogen-bond selection, ion, solvent) and polar itself
 #define I_PIDX_SHIFT 14        // the binned copy keeps the pair index in the bits above the dynamic flags
 #define I_WMASK  ((1u << I_PIDX_SHIFT) - 1u)
 #define MAX_PAIR_ATOMS (1 << 18)

@@ -112,12 +112,17 @@ __device__ __forceinline__ void emit_near(const DevOut& O, int frame, int kind, 
 //    an 8-bit generation in its top byte and 24 pair bits; a word whose generation is stale counts as empty.
 //    The generation runs 1..255 and the table is wiped when it wraps (pair_kernel.cuh).
 __device__ __forceinline__ void count_pair(const DevOut& O, unsigned* bits, unsigned gen, int ra, int rb, int R) {
-    long long idx = pair_index(ra, rb, R);
     if (gen == 0u) {
-        unsigned bit = 1u << (idx & 31);
-        unsigned old = atomicOr(&bits[idx >> 5], bit);
+        // plain shared-memory bitset: few residues (the set fits in shared memory), 32-bit index arithmetic; most contacts of a frame
+        // repeat a residue pair that is already set: look before the atomic
+        const unsigned lo = (unsigned)min(ra, rb), hi = (unsigned)max(ra, rb);
+        const unsigned idx = lo * (unsigned)R - (lo * (lo - 1u)) / 2u + (hi - lo);
+        const unsigned bit = 1u << (idx & 31u);
+        if (*reinterpret_cast<volatile unsigned*>(&bits[idx >> 5]) & bit) return;
+        const unsigned old = atomicOr(&bits[idx >> 5], bit);
         if (!(old & bit)) atomicAdd(&O.counts[idx], 1);
     } else {
+        long long idx = pair_index(ra, rb, R);
         unsigned* w = bits + idx / 24;
         unsigned bit = 1u << (unsigned)(idx % 24);
         unsigned old = *w;

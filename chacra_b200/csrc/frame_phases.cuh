@@ -9,7 +9,8 @@ template <bool SOA>
 struct FrameCtxT {
     const float4* spos;      // !SOA: cell-sorted pair atoms: x, y, z, (dynamic flags | pair_index << I_PIDX_SHIFT)
     const int* lkey;         // !SOA: locality key by pair index
-    const float4* exy; const float4* ezk; const unsigned* sw; const unsigned short* sres;   // SOA: x0 x1 y0 y1 | z0 z1 lkey0 lkey1 (floats)
+    const float4* exy; const float4* ezk; const unsigned* sw;   // SOA: x0 x1 y0 y1 | z0 z1 lkey0 lkey1 (floats) | flags, pair index
+    const unsigned short* pres; const unsigned char* pst;       // SOA, by pair index: residue rank; static bits (I_LIG .. I_PBOND) >> 14
     __device__ __forceinline__ float4 at(int j) const {
         if (SOA) {
             const float4 a = exy[j >> 1]; const float4 b = ezk[j >> 1];
@@ -22,7 +23,8 @@ struct FrameCtxT {
         if (SOA) { const float4 b = ezk[j >> 1]; return (int)((j & 1) ? b.w : b.z); }      // exact: locality keys are below 2^24 here
         return lkey[w >> I_PIDX_SHIFT];
     }
-    __device__ __forceinline__ int res(const DevTopo& T, int j, int pidx) const { return SOA ? (int)sres[j] : T.pair_res[pidx]; }
+    __device__ __forceinline__ int res(const DevTopo& T, int pidx) const { return SOA ? (int)pres[pidx] : T.pair_res[pidx]; }
+    __device__ __forceinline__ unsigned sinfo(const DevTopo& T, int pidx) const { return SOA ? ((unsigned)pst[pidx] << 14) : T.pair_info[pidx]; }
     const float* aux;        // [NA][3] donor hydrogens, ring atoms, cations
     unsigned* bits;          // residue-pair set of this frame
     unsigned gen;            // 0: plain bitset; 1..255: generation of the stamped bitset
@@ -61,7 +63,7 @@ __device__ __forceinline__ void ring_pc_task(const DevTopo& T, const DevParams& 
         if (!dir || ratom == catom) return;
         const float* pr = F.aux + 3 * slot;
         const float d2k = dist2_exact(xc[0], xc[1], xc[2], pr[0], pr[1], pr[2]);
-        if (TN) {
+        if (TN && P.track_near && P.track_near) {
             const double dl = (double)sqrtf(d2k) - P.pc_soft;
             if (fabs(dl) < P.near_d) { near_atom[n_near] = ratom; near_dl[n_near] = dl; ++n_near; }
             if (d2k > P.pc_soft2) { if (!(dl < P.near_d)) return; soft_fail = true; }
@@ -75,13 +77,13 @@ __device__ __forceinline__ void ring_pc_task(const DevTopo& T, const DevParams& 
     if (n_near > 0 && d - P.pc_dist < P.near_d)       // the soft 10 A search decides this group (pi_cation.py:22,70,98)
         for (int k = 0; k < n_near; ++k) emit_near(O, F.frame, CHC_NEAR_PC_SOFT, catom, near_atom[k], near_dl[k]);
     if (soft_fail) return;
-    if (TN && fabs(d - P.pc_dist) < P.near_d) emit_near(O, F.frame, CHC_NEAR_PC_DIST, catom, rep, d - P.pc_dist);
+    if (TN && P.track_near && fabs(d - P.pc_dist) < P.near_d) emit_near(O, F.frame, CHC_NEAR_PC_DIST, catom, rep, d - P.pc_dist);
     if (d > P.pc_dist) return;
     double t = fold180(angle_deg(normal3(a, b, cc), v));
-    if (TN && fabs(t - P.pc_angle) < P.near_a) emit_near(O, F.frame, CHC_NEAR_PC_ANGLE, catom, rep, t - P.pc_angle);
+    if (TN && P.track_near && fabs(t - P.pc_angle) < P.near_a) emit_near(O, F.frame, CHC_NEAR_PC_ANGLE, catom, rep, t - P.pc_angle);
     if (t > P.pc_angle) return;
     count_pair(O, F.bits, F.gen, T.cat_res[c], T.ring_res[r], T.R);
-    if (P.emit) {
+    if (TN && P.emit) {
         const float* pr = F.aux + 3 * T.ring_rep_aux[r];
         emit_contact(O, F.frame, CHC_PC, catom, rep, sqrtf(dist2_exact(xc[0], xc[1], xc[2], pr[0], pr[1], pr[2])));
     }
@@ -114,7 +116,7 @@ __device__ __forceinline__ void ring_stack_task(const DevTopo& T, const DevParam
     hit_ts = (P.itypes & CHC_IT_TS) && best <= P.ts_soft2;
     // the closest selected ring-atom pair within the near band of a soft search cutoff (aromatics.py:26-27,166)
     double soft_ps = 1.0, soft_ts = 1.0;
-    if (TN && best < 3.0e38f) {
+    if (TN && P.track_near && best < 3.0e38f) {
         const double db = (double)sqrtf(best);
         if (P.itypes & CHC_IT_PS) soft_ps = db - P.ps_soft;
         if (P.itypes & CHC_IT_TS) soft_ts = db - P.ts_soft;
@@ -137,7 +139,7 @@ __device__ __forceinline__ void ring_stack_task(const DevTopo& T, const DevParam
         if ((which == 0 ? near_ps : near_ts) && d - dcut < P.near_d)
             emit_near(O, F.frame, which == 0 ? CHC_NEAR_PS_SOFT : CHC_NEAR_TS_SOFT, rep1, rep2, which == 0 ? soft_ps : soft_ts);
         if (!on) continue;
-        if (TN && fabs(d - dcut) < P.near_d)
+        if (TN && P.track_near && fabs(d - dcut) < P.near_d)
             emit_near(O, F.frame, which == 0 ? CHC_NEAR_PS_DIST : CHC_NEAR_TS_DIST, rep1, rep2, d - dcut);
         if (d > dcut) continue;
         if (!have_ang) {
@@ -146,14 +148,14 @@ __device__ __forceinline__ void ring_stack_task(const DevTopo& T, const DevParam
             have_ang = true;
         }
         double v = which == 0 ? fold180(ang) : fabs(ang - 90.0);
-        if (TN && fabs(v - acut) < P.near_a)
+        if (TN && P.track_near && fabs(v - acut) < P.near_a)
             emit_near(O, F.frame, which == 0 ? CHC_NEAR_PS_ANGLE : CHC_NEAR_TS_ANGLE, rep1, rep2, v - acut);
         if (v > acut) continue;
-        if (TN && fabs(psi - pcut) < P.near_a)
+        if (TN && P.track_near && fabs(psi - pcut) < P.near_a)
             emit_near(O, F.frame, which == 0 ? CHC_NEAR_PS_PSI : CHC_NEAR_TS_PSI, rep1, rep2, psi - pcut);
         if (psi > pcut) continue;
         count_pair(O, F.bits, F.gen, T.ring_res[r1], T.ring_res[r2], T.R);
-        if (P.emit) {
+        if (TN && P.emit) {
             const float* q1 = F.aux + 3 * T.ring_rep_aux[r1]; const float* q2 = F.aux + 3 * T.ring_rep_aux[r2];
             emit_contact(O, F.frame, which == 0 ? CHC_PS : CHC_TS, rep1, rep2,
                          sqrtf(dist2_exact(q1[0], q1[1], q1[2], q2[0], q2[1], q2[2])));
@@ -189,7 +191,7 @@ __device__ __forceinline__ unsigned e2_classify(const DevTopo& T, const DevParam
     const bool edge = edge_pre && d2 <= P.hb2;
     // near-cutoff bands of the two plain distance cutoffs (salt_bridges.py:76-80, hbonds.py:64-82)
     bool band_sb = false, band_hb = false;
-    if (TN) {
+    if (TN && P.track_near && P.track_near) {
         const double dd = (double)sqrtf(d2);
         band_sb = fabs(dd - P.sb_dist) < P.near_d; band_hb = fabs(dd - P.hb_dist) < P.near_d;
     }
@@ -202,7 +204,7 @@ __device__ __forceinline__ unsigned e2_classify(const DevTopo& T, const DevParam
     if (dl >= P.vdw_rd) {
         if ((P.itypes & CHC_IT_VDW) && (wi & wj & I_VDW)) {
             if (d2 <= F.tv[e]) cls |= C_VDW;
-            if (TN && d2 <= P.soft2 && fabs((double)sqrtf(d2) - T.vcut[e]) < P.near_d) cls |= C_NEARV;
+            if (TN && P.track_near && d2 <= P.soft2 && fabs((double)sqrtf(d2) - T.vcut[e]) < P.near_d) cls |= C_NEARV;
         }
         if ((P.itypes & CHC_IT_HP) && d2 <= P.hp2) {
             // static base-carbon bits first, then this fragment's membership (hydrophobics.py:8-41)
@@ -215,7 +217,7 @@ __device__ __forceinline__ unsigned e2_classify(const DevTopo& T, const DevParam
                                     ((wj & I_HP1) && (hj & 1u) && (wi & I_HP2) && (hi & 2u)));
                 if (hp) {
                     if (d2 <= F.th[e]) cls |= C_HP;
-                    if (TN && fabs((double)sqrtf(d2) - T.vcut[e]) < P.near_d) cls |= C_NEARH;
+                    if (TN && P.track_near && fabs((double)sqrtf(d2) - T.vcut[e]) < P.near_d) cls |= C_NEARH;
                 }
             }
         }
@@ -255,7 +257,7 @@ __device__ __forceinline__ bool hb_direction(const DevTopo& T, const DevParams& 
             if (pcos <= 0.f || psin > pcos * P.hb_tan_hi) continue;                    // surely above it
         }
         float ang = 57.2958f * (float)atan2((double)psin, (double)pcos);
-        if (report && TN && fabs((double)ang - (double)P.hb_angle) < P.near_a)
+        if (report && TN && P.track_near && fabs((double)ang - (double)P.hb_angle) < P.near_a)
             emit_near(O, F.frame, CHC_NEAR_HB_ANGLE, atom_d, atom_a, (double)ang - (double)P.hb_angle);
         ok |= ang < P.hb_angle;
     }
@@ -270,12 +272,14 @@ __device__ __forceinline__ void e3_finish(const DevTopo& T, const DevParams& P, 
     const float d2 = dist2_exact(a.x, a.y, a.z, b.x, b.y, b.z);      // as in e2_classify (same operands, same order)
     unsigned wi = __float_as_uint(a.w), wj = __float_as_uint(b.w);
     int pi = wi >> I_PIDX_SHIFT, pj = wj >> I_PIDX_SHIFT;
-    int ai = T.pair_atom[pi], aj = T.pair_atom[pj];
-    const unsigned si = T.pair_info[pi], sj = T.pair_info[pj];       // static-only bits: ligand, backbone, CYS, xbond
-    // directly bonded pairs are excluded by measure contacts / measure hbonds (Appendix A.4, A.5)
-    bool need_bond = (cls & (C_SB | C_HB | C_HBW | C_NEARS | C_NEARB)) || ((si & I_XBOND) && (sj & I_XBOND));
-    if (need_bond && is_bonded(T, pi, aj)) return;
-    int ri = F.res(T, i, pi), rj = F.res(T, j, pj);
+    const unsigned si = F.sinfo(T, pi), sj = F.sinfo(T, pj);         // static-only bits: ligand, backbone, CYS, xbond, pbond
+    // directly bonded pairs are excluded by measure contacts / measure hbonds (Appendix A.4, A.5); the static flags say whether
+    // the atom has ANY bond that could matter (I_XBOND: one the residue-distance filters do not exclude; I_PBOND: one to a polar atom)
+    const bool need_bond = (si & sj & I_XBOND) || ((cls & (C_SB | C_HB | C_HBW | C_NEARS | C_NEARB)) && (si & sj & I_PBOND));
+    if (need_bond && is_bonded(T, pi, T.pair_atom[pj])) return;
+    int ai = 0, aj = 0;                                              // atom indices are only needed for records
+    if (TN) { ai = T.pair_atom[pi]; aj = T.pair_atom[pj]; }
+    int ri = F.res(T, pi), rj = F.res(T, pj);
     float dist = sqrtf(d2);
     if (cls & C_NEARS) emit_near(O, F.frame, CHC_NEAR_SB_DIST, ai, aj, (double)dist - P.sb_dist);
     if (cls & C_NEARB) emit_near(O, F.frame, CHC_NEAR_HB_DIST, ai, aj, (double)dist - P.hb_dist);
@@ -287,9 +291,9 @@ __device__ __forceinline__ void e3_finish(const DevTopo& T, const DevParams& P, 
             if (cls & C_NEARH) emit_near(O, F.frame, CHC_NEAR_HP_DIST, ai, aj, (double)dist - T.vcut[e]);
             if (cls & C_VDW) {
                 count_pair(O, F.bits, F.gen, ri, rj, T.R);
-                if (P.emit) emit_contact(O, F.frame, CHC_VDW, ai, aj, dist);
+                if (TN && P.emit) emit_contact(O, F.frame, CHC_VDW, ai, aj, dist);
             }
-            if ((cls & C_HP) && P.emit) {     // hp is not a counted type (get_contact_frequencies.py:107-109)
+            if (TN && (cls & C_HP) && P.emit) {     // hp is not a counted type (get_contact_frequencies.py:107-109)
                 bool li = si & I_LIG, lj = sj & I_LIG;
                 emit_contact(O, F.frame, (li || lj) ? ((li != lj) ? CHC_HPLP : CHC_HPLL) : CHC_HP, ai, aj, dist);
             }
@@ -302,7 +306,7 @@ __device__ __forceinline__ void e3_finish(const DevTopo& T, const DevParams& P, 
         int aa = ij ? ai : aj, ac = ij ? aj : ai;
         bool al = wa & I_LIG, cl = wc & I_LIG;
         if (!(al && cl)) count_pair(O, F.bits, F.gen, ri, rj, T.R);
-        if (P.emit) {
+        if (TN && P.emit) {
             emit_contact(O, F.frame, al ? (cl ? CHC_SBLL : CHC_SBLP) : (cl ? CHC_SBPL : CHC_SB), aa, ac, dist);
             // the reference's if / if / if-else also appends a plain `sb` line behind an `sblp` or `sbpl` one (salt_bridges.py:90-97):
             // it is the line get_contact_frequencies counts
@@ -337,7 +341,7 @@ __device__ __forceinline__ void e3_finish(const DevTopo& T, const DevParams& P, 
             else if (!bi && !bj) t = CHC_HBSS;
             else t = CHC_HBSB;
             if (t != CHC_HBLL) count_pair(O, F.bits, F.gen, ri, rj, T.R);
-            if (P.emit) emit_contact(O, F.frame, t, ai, aj, dist);
+            if (TN && P.emit) emit_contact(O, F.frame, t, ai, aj, dist);
         }
     }
 }

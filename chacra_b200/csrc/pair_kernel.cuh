@@ -46,6 +46,8 @@ struct PairLayout {         // shared-memory plan of the pair kernel (bytes)
     // SMALL: the sorted atoms as slot pairs (x0 x1 y0 y1 | z0 z1), and per slot the flag word, the filter key, the residue rank.
     // The float4 image the bulk copy lands (inside off_rec) is dead once these are built: the queues live there.
     int off_exy, off_ez, off_ek, off_sw, off_sres;      // off_ez: float4 z0 z1 lkey0 lkey1 per slot pair; off_ek: partner bit arrays
+    int off_plkf, off_pres, off_pst;                    // SMALL, by pair index (loaded once per launch): locality key (float), residue rank, static bits
+    int off_rc, off_rlist, rlist_cap;                   // ring centroids (float[3 n_rings]) and the ring tasks that passed the prefilter
     int bits_words;         // words of the residue-pair set (plain: P/32, stamped: P/24)
     int total;
 };
@@ -74,6 +76,7 @@ struct PairMisc {
     int ring_cursor;            // next unit of 32 ring tasks
     int nmark;                  // waters with at least one hydrogen bond to a non-solvent atom (this frame)
     int qcur[32];               // SMALL: entries in every warp's E2 queue (lanes reserve room with one shared atomic each)
+    int rn_pc, rn_st;           // ring tasks that passed the centroid prefilter: pi-cation from the front of the list, stacking from its end
 };
 
 // TN: the near-cutoff side channel is compiled in (chc_params.track_near); the counts-only production path carries none of it
@@ -103,7 +106,13 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
     for (int k = tid; k < T.K * T.K; k += THREADS) { tv[k] = T.tv[k]; th[k] = T.th[k]; }
     unsigned* bits;
     unsigned gen = 0;
+    float* p_lkf = reinterpret_cast<float*>(smem + L.off_plkf);
+    unsigned short* p_res = reinterpret_cast<unsigned short*>(smem + L.off_pres);
+    unsigned char* p_st = reinterpret_cast<unsigned char*>(smem + L.off_pst);
     if (SMALL) {
+        for (int k = tid; k < T.n_pair; k += THREADS) {
+            p_lkf[k] = (float)T.pair_lkey[k]; p_res[k] = (unsigned short)T.pair_res[k]; p_st[k] = (unsigned char)((T.pair_info[k] >> 14) & 0x1fu);
+        }
         bits = reinterpret_cast<unsigned*>(smem + L.off_bits);
         if (tid == 0) { mbar_init(&M->bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
     } else {
@@ -134,7 +143,7 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(nxt + B.off_cells), "r"(cbytes) : "memory");
                 }
 #endif
-                M->cursor = 0; M->ring_cursor = 0; M->nmark = 0;
+                M->cursor = 0; M->ring_cursor = 0; M->nmark = 0; M->rn_pc = 0; M->rn_st = 0;
             }
             for (int w = tid; w < L.bits_words; w += THREADS) bits[w] = 0u;
             mbar_wait(&M->bar, phase);
@@ -144,7 +153,7 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
             aux = reinterpret_cast<const float*>(smem + L.off_rec + B.off_aux);
             cells = reinterpret_cast<const cell_t*>(smem + L.off_cells);
         } else {
-            if (tid == 0) { M->cursor = 0; M->ring_cursor = 0; M->nmark = 0; }
+            if (tid == 0) { M->cursor = 0; M->ring_cursor = 0; M->nmark = 0; M->rn_pc = 0; M->rn_st = 0; }
             gen = gen + 1u;
             if (gen > 255u) {               // generations wrapped: wipe the table once per 255 frames
                 for (int w = tid; w < L.bits_words; w += THREADS) bits[w] = 0u;
@@ -156,15 +165,55 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
             cells = reinterpret_cast<const cell_t*>(rec + B.off_cells);
         }
         __syncthreads();
+        // ---- R1: ring tasks (cation x ring, ring x ring) through a float prefilter on the ring centroids; the few that can reach
+        //      a hard distance cutoff are listed and evaluated densely (float64) after the pair phase.  The prefilter radius is the
+        //      largest hard cutoff + 0.05 A: a superset of what ring_pc_task / ring_stack_task accept or report as near-cutoff.
+        //      Runs in the same barrier interval as the conversion below (both only read the record). ----
+        unsigned* rlist = reinterpret_cast<unsigned*>(smem + L.off_rlist);
+        const int n_pc = (P.itypes & CHC_IT_PC) ? T.n_cat * T.n_rings : 0;
+        const int n_st = (P.itypes & (CHC_IT_PS | CHC_IT_TS)) ? T.n_rings * (T.n_rings - 1) / 2 : 0;
+        if (n_pc + n_st > 0) {
+            const unsigned nr_m = 0xffffffffu / (unsigned)max(T.n_rings, 1) + 1u;
+            auto centroid = [&](int rr, float& cx, float& cy, float& cz) {
+                const int* t1 = T.ring_aux + 3 * rr;
+                if (t1[0] < 0) return false;                                  // a ring without its three atoms takes part in nothing
+                const float* p1 = aux + 3 * t1[0]; const float* p2 = aux + 3 * t1[1]; const float* p3 = aux + 3 * t1[2];
+                cx = (p1[0] + p2[0] + p3[0]) * (1.0f / 3.0f); cy = (p1[1] + p2[1] + p3[1]) * (1.0f / 3.0f); cz = (p1[2] + p2[2] + p3[2]) * (1.0f / 3.0f);
+                return true;
+            };
+            for (int t = tid; t < n_pc + n_st; t += THREADS) {
+                float ax, ay, az, bx, by, bz;
+                if (t < n_pc) {
+                    int c = (int)__umulhi((unsigned)t, nr_m);
+                    if (c * T.n_rings > t) --c;                               // rounded-up reciprocal: exact below 2^16, corrected above
+                    const int rr = t - c * T.n_rings;
+                    if (T.cat_excl[c] == rr || !centroid(rr, bx, by, bz)) continue;
+                    const float* xc = aux + 3 * T.cat_aux[c];
+                    ax = xc[0]; ay = xc[1]; az = xc[2];
+                } else {
+                    const int q = t - n_pc;
+                    int r2 = (int)((1.0f + sqrtf(1.0f + 8.0f * (float)q)) * 0.5f);
+                    while (r2 * (r2 - 1) / 2 > q) --r2;
+                    while ((r2 + 1) * r2 / 2 <= q) ++r2;
+                    const int r1 = q - r2 * (r2 - 1) / 2;
+                    if (T.ring_res[r1] == T.ring_res[r2] || !centroid(r1, ax, ay, az) || !centroid(r2, bx, by, bz)) continue;
+                }
+                const float dx = ax - bx, dy = ay - by, dz = az - bz;
+                if (!(dx * dx + dy * dy + dz * dz <= P.ring_pre2)) continue;
+                const bool pc = t < n_pc;
+                const int at = atomicAdd(pc ? &M->rn_pc : &M->rn_st, 1);
+                if (pc) { if (at < L.rlist_cap) rlist[at] = (unsigned)t; }
+                else if (at < L.rlist_cap) rlist[L.rlist_cap - 1 - at] = (unsigned)(t - n_pc);
+            }
+        }
         float4* exy = reinterpret_cast<float4*>(smem + L.off_exy);
         float4* ezk = reinterpret_cast<float4*>(smem + L.off_ez);
         unsigned* partner = reinterpret_cast<unsigned*>(smem + L.off_ek);      // [E1_PARTNER_SETS][pwords] bit per sorted slot
         const int pwords = ((T.n_pair + 2 * E1_PAD_PAIRS + 31) >> 5) + 2;
         unsigned* sw = reinterpret_cast<unsigned*>(smem + L.off_sw);
-        unsigned short* sres = reinterpret_cast<unsigned short*>(smem + L.off_sres);
         if (SMALL) {
-            // The float4 image becomes slot PAIRS (E1 tests two neighbours per packed instruction): x0 x1 y0 y1 | z0 z1, plus
-            // per slot the flag word, the filter key (locality key from the L1/L2-resident table) and the residue rank.
+            // The float4 image becomes slot PAIRS (E1 tests two neighbours per packed instruction): x0 x1 y0 y1 | z0 z1 lkey0 lkey1,
+            // plus the flag word per slot.
             const int NPs = T.n_pair, np2 = (NPs + 1) >> 1;
             for (int q = tid; q < np2 + E1_PAD_PAIRS; q += THREADS) {
                 const int j0 = 2 * q, j1 = j0 + 1;
@@ -173,10 +222,8 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                 exy[q] = make_float4(a.x, b.x, a.y, b.y);
                 const unsigned wa = __float_as_uint(a.w), wb = __float_as_uint(b.w);
                 const int pa = wa >> I_PIDX_SHIFT, pb = wb >> I_PIDX_SHIFT;
-                ezk[q] = make_float4(a.z, b.z, j0 < NPs ? (float)__ldg(&T.pair_lkey[pa]) : -3.0e7f, j1 < NPs ? (float)__ldg(&T.pair_lkey[pb]) : -3.0e7f);
+                ezk[q] = make_float4(a.z, b.z, j0 < NPs ? p_lkf[pa] : -3.0e7f, j1 < NPs ? p_lkf[pb] : -3.0e7f);
                 sw[j0] = wa; sw[j1] = wb;
-                sres[j0] = j0 < NPs ? (unsigned short)__ldg(&T.pair_res[pa]) : (unsigned short)0;
-                sres[j1] = j1 < NPs ? (unsigned short)__ldg(&T.pair_res[pb]) : (unsigned short)0;
             }
             for (int wd = warp; wd < pwords; wd += THREADS / 32) {        // partner bits, one word of 32 slots per warp round
                 const int j = wd * 32 + lane;
@@ -188,9 +235,9 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
             }
             if (tid < 32) M->qcur[tid] = 0;
             __syncthreads();               // from here on the float4 image is dead: its shared memory holds the (empty) queues
-        }
+        } else if (n_pc + n_st > 0) __syncthreads();     // the ring list is complete before any warp reaches the ring phase
         const int px = hdr->nc[0] + 2, pxy = px * (hdr->nc[1] + 2), ncell = hdr->ncell;
-        FrameCtxT<SMALL> F{spos, T.pair_lkey, exy, ezk, sw, sres, aux, bits, gen, tv, th,
+        FrameCtxT<SMALL> F{spos, T.pair_lkey, exy, ezk, sw, p_res, p_st, aux, bits, gen, tv, th,
                            hpmask + (size_t)(gidx / frag_frames - frag0) * T.n_pair, (int)gidx,
                            water_scratch(wscratch, blockIdx.x, T.n_solv), &M->nmark};
         // ---- E: pair interactions ------------------------------------------------------------------------------
@@ -457,23 +504,29 @@ CHC_UNROLL(E1_UNROLL)
                 __syncwarp();
             }
         }
-        // ---- R: ring interactions (small lists; float prefilter, float64 geometry), in units of 32 tasks handed out through a
-        //      shared counter AFTER the pair phase: warps that run out of atom tiles early fill the end-of-frame tail ----
-        {
-            const int n_pc = (P.itypes & CHC_IT_PC) ? T.n_cat * T.n_rings : 0;
-            const int n_st = (P.itypes & (CHC_IT_PS | CHC_IT_TS)) ? T.n_rings * (T.n_rings - 1) / 2 : 0;
-            const int u_pc = (n_pc + 31) >> 5, u_all = u_pc + ((n_st + 31) >> 5);
+        // ---- R2: the listed ring tasks (float64 geometry), 32 per unit, handed out through a shared counter AFTER the pair phase:
+        //      warps that run out of atom tiles early fill the end-of-frame tail.  If the list overflowed (rlist_cap) every task is
+        //      evaluated the slow way instead. ----
+        if (n_pc + n_st > 0) {
+            const int rn_pc = M->rn_pc, rn_st = M->rn_st;
+            const bool listed = rn_pc + rn_st <= L.rlist_cap;
+            const int m_pc = listed ? rn_pc : n_pc, m_st = listed ? rn_st : n_st;
+            const int u_pc = (m_pc + 31) >> 5, u_all = u_pc + ((m_st + 31) >> 5);
             for (;;) {
                 int u = 0;
                 if (lane == 0) u = atomicAdd(&M->ring_cursor, 1);
                 u = __shfl_sync(FULL, u, 0);
                 if (u >= u_all) break;
                 if (u < u_pc) {
-                    const int t = u * 32 + lane;
-                    if (t < n_pc) ring_pc_task<TN>(T, P, O, F, t / T.n_rings, t % T.n_rings);
+                    const int k = u * 32 + lane;
+                    if (k < m_pc) {
+                        const int t = listed ? (int)rlist[k] : k;
+                        ring_pc_task<TN>(T, P, O, F, t / T.n_rings, t % T.n_rings);
+                    }
                 } else {
-                    const int t = (u - u_pc) * 32 + lane;
-                    if (t < n_st) {
+                    const int k = (u - u_pc) * 32 + lane;
+                    if (k < m_st) {
+                        const int t = listed ? (int)rlist[L.rlist_cap - 1 - k] : k;
                         int r2 = (int)((1.0f + sqrtf(1.0f + 8.0f * (float)t)) * 0.5f);
                         while (r2 * (r2 - 1) / 2 > t) --r2;
                         while ((r2 + 1) * r2 / 2 <= t) ++r2;

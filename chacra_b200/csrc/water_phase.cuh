@@ -74,7 +74,7 @@ __device__ __forceinline__ void water_bridges(const DevTopo& T, const DevParams&
                     if (nj == 0) continue;                                      // no non-solvent partner: cannot close a bridge
                     if (F.lk(sw, ww) == F.lk(j, wj)) continue;                     // same residue (hbonds.py:131)
                     const float d2w = dist2_exact(xw.x, xw.y, xw.z, xj.x, xj.y, xj.z);
-                    const double dlw = TN ? (double)sqrtf(d2w) - P.hb_dist : 1.0;
+                    const double dlw = (TN && P.track_near) ? (double)sqrtf(d2w) - P.hb_dist : 1.0;
                     if (d2w > P.hb2 && !(fabs(dlw) < P.near_d)) continue;
                     if (!((ww | wj) & I_HASH) || is_bonded(T, pw, aj)) continue;
                     if (fabs(dlw) < P.near_d) emit_near(O, F.frame, CHC_NEAR_HB_DIST, aw, aj, dlw);

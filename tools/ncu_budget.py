@@ -14,16 +14,15 @@ ANCHORS = [
     ("prologue / frame setup", "pair_kernel.cuh", "pair_frames_kernel(DevTopo T", "if (SMALL) {\n            // The float4 image becomes"),
     ("record -> slot pairs", "pair_kernel.cuh", "// The float4 image becomes slot PAIRS", "const int px = hdr->nc[0] + 2"),
     ("E state setup", "pair_kernel.cuh", "const int px = hdr->nc[0] + 2", "// Slot pairs, packed float32 arithmetic"),
-    ("E1 flush (scan + queue)", "pair_kernel.cuh", "// Slot pairs, packed float32 arithmetic", "k0 += 32;"),
+    ("E1 flush (reserve + queue)", "pair_kernel.cuh", "// Slot pairs, packed float32 arithmetic", "k0 += 32;"),
     ("E1 unit grab / ranges", "pair_kernel.cuh", "k0 += 32;", "// up to 16 slot pairs of every lane"),
-    ("E1 test loop", "pair_kernel.cuh", "// up to 16 slot pairs of every lane", "// F, per lane:"),
-    ("F per-lane filter", "pair_kernel.cuh", "// F, per lane:", "if (qfn == 0 && q2n == 0 && q3n == 0) break;"),
+    ("E1 test loop + filter", "pair_kernel.cuh", "// up to 16 slot pairs of every lane", "// slot k of the chunk sits at bit"),
+    ("E1 masks / partner window", "pair_kernel.cuh", "// slot k of the chunk sits at bit", "if (qfn == 0 && q2n == 0 && q3n == 0) break;"),
     ("in-place E1/F (unused on SMALL)", "pair_kernel.cuh", "if (qfn == 0 && q2n == 0 && q3n == 0) break;", "// ---- E2: 32 filtered survivors"),
     ("E2 dispatch", "pair_kernel.cuh", "// ---- E2: 32 filtered survivors", "// ---- E3: 32 classified pairs"),
     ("E3 dispatch", "pair_kernel.cuh", "// ---- E3: 32 classified pairs", "// ---- R: ring interactions"),
     ("R ring dispatch", "pair_kernel.cuh", "// ---- R: ring interactions", "// ---- W: water bridges"),
     ("end barrier / water", "pair_kernel.cuh", "// ---- W: water bridges", "\x00"),
-    ("F per-lane filter", "pair_kernel.cuh", "__device__ __forceinline__ unsigned e1_key", "struct PairMisc"),
     ("queue put/get lambdas", "pair_kernel.cuh", "auto qput = []", "for (int k = tid; k < T.K * T.K"),
     ("slot accessors (E2/E3)", "frame_phases.cuh", "struct FrameCtxT", "// ---- R: pi-cation"),
     ("R ring tasks", "frame_phases.cuh", "// ---- R: pi-cation", "// ---- F: can this pair get any class"),
