@@ -257,12 +257,15 @@ extern "C" int chc_create(chc_ctx** out, const chc_topology* t, const chc_params
         std::vector<int> a2p((size_t)t->n_atoms, -1);
         for (size_t k = 0; k < NP; ++k) if (t->pair_atom[k] >= 0 && t->pair_atom[k] < t->n_atoms) a2p[t->pair_atom[k]] = (int)k;
         for (size_t k = 0; k < NP; ++k) {
-            info[k] &= ~I_PBOND;
-            if (!(info[k] & polar)) continue;
+            // I_XBOND, recomputed for the van der Waals / hydrophobic classes: a bond to a pair atom that the residue-distance
+            // filter of those classes (|dlkey| < vdw_res_diff) does not already exclude (disulfides, links between chains)
+            info[k] &= ~(I_PBOND | I_XBOND);
             for (int b = t->pair_bond_start[k]; b < t->pair_bond_start[k + 1]; ++b) {
                 const int a = t->pair_bond_adj[b];
                 const int q = (a >= 0 && a < t->n_atoms) ? a2p[a] : -1;
-                if (q >= 0 && (t->pair_info[q] & polar)) { info[k] |= I_PBOND; break; }
+                if (q < 0) continue;
+                if ((info[k] & polar) && (t->pair_info[q] & polar)) info[k] |= I_PBOND;
+                if (std::abs(t->pair_lkey[k] - t->pair_lkey[q]) >= p->vdw_res_diff) info[k] |= I_XBOND;
             }
         }
     }

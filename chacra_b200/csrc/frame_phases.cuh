@@ -275,7 +275,8 @@ __device__ __forceinline__ void e3_finish(const DevTopo& T, const DevParams& P, 
     const unsigned si = F.sinfo(T, pi), sj = F.sinfo(T, pj);         // static-only bits: ligand, backbone, CYS, xbond, pbond
     // directly bonded pairs are excluded by measure contacts / measure hbonds (Appendix A.4, A.5); the static flags say whether
     // the atom has ANY bond that could matter (I_XBOND: one the residue-distance filters do not exclude; I_PBOND: one to a polar atom)
-    const bool need_bond = (si & sj & I_XBOND) || ((cls & (C_SB | C_HB | C_HBW | C_NEARS | C_NEARB)) && (si & sj & I_PBOND));
+    const bool need_bond = ((cls & (C_VDW | C_HP | C_NEARV | C_NEARH)) && (si & sj & I_XBOND)) ||
+                           ((cls & (C_SB | C_HB | C_HBW | C_NEARS | C_NEARB)) && (si & sj & I_PBOND));
     if (need_bond && is_bonded(T, pi, T.pair_atom[pj])) return;
     int ai = 0, aj = 0;                                              // atom indices are only needed for records
     if (TN) { ai = T.pair_atom[pi]; aj = T.pair_atom[pj]; }

@@ -66,6 +66,9 @@ __device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 r; asm(
 // | (c & 4 ? anions : 0) | solvent, set 8 = everything but solvent (for a solvent atom): 9 bit arrays over the sorted slots.
 #define E1_PAD_PAIRS 20        // slot pairs past the last atom that the unmasked E1 loads may touch
 #define E1_PARTNER_SETS 9
+#ifndef E1_TAIL_TILES
+#define E1_TAIL_TILES 24       // the last tiles of a frame are handed out range by range
+#endif
 __device__ __forceinline__ int e1_partner_set(unsigned w) {
     return (w & I_SOLV) ? 8 : (int)(((w >> 6) & 1u) | (((w >> 8) & 1u) << 1) | (((w >> 9) & 1u) << 2));   // hbu | anion -> wants cations | cation -> wants anions
 }
@@ -251,6 +254,8 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
         const unsigned nr_magic = 0xffffffffu / (unsigned)nr + 1u;
         const int ntiles = (nA + 31) >> 5;
         const int nunits = ntiles * nr;
+        const int n_whole = max(ntiles - E1_TAIL_TILES, 0), nunits_s = n_whole + (ntiles - n_whole) * nr;   // SMALL: unit numbering
+        bool whole = false;
         int r = 0, tile = -1, k0 = 0, maxlen = 0;      // warp-uniform: current range and tile, chunk offset, longest lane range
         int my_i = -1, my_c = 0, beg = 0, len = 0;     // this lane's atom, its cell, its current range
         float ix = 0.f, iy = 0.f, iz = 0.f;
@@ -290,13 +295,20 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                         continue;
                     }
                     k0 += 32;
-                    if (k0 >= maxlen) {                // next unit of work = (tile, range)
-                        int u = 0;
-                        if (lane == 0) u = atomicAdd(&M->cursor, 1);
-                        u = __shfl_sync(FULL, u, 0);
-                        if (u >= nunits) { exhausted = true; break; }
-                        const int t = (int)__umulhi((unsigned)u, nr_magic);
-                        r = u - t * nr;
+                    if (k0 >= maxlen) {
+                        // next range of a whole-tile unit, or the next unit of work: whole tiles while many remain (one shared
+                        // atomic per five ranges), single (tile, range) units for the last E1_TAIL_TILES tiles (short frame tail)
+                        int t = tile;
+                        if (whole && r + 1 < nr) ++r;
+                        else {
+                            int u = 0;
+                            if (lane == 0) u = atomicAdd(&M->cursor, 1);
+                            u = __shfl_sync(FULL, u, 0);
+                            if (u >= nunits_s) { exhausted = true; break; }
+                            whole = u < n_whole;
+                            if (whole) { t = u; r = 0; }
+                            else { const int v = u - n_whole; const int q = (int)__umulhi((unsigned)v, nr_magic); t = n_whole + q; r = v - q * nr; }
+                        }
                         if (t != tile) {
                             tile = t;
                             my_i = t * 32 + lane;
