@@ -99,6 +99,7 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
     using cell_t = typename std::conditional<SMALL, unsigned short, int>::type;     // BinLayout::cell16 <=> SMALL
     unsigned* q1 = reinterpret_cast<unsigned*>(smem + L.off_q1) + (SMALL ? 0 : warp * (QW * Q1_CAP));   // survivors (in-place path only)
     unsigned* qf = reinterpret_cast<unsigned*>(smem + L.off_qf) + warp * (QW * QF_CAP);            // filtered survivors
+    uint2* qe = reinterpret_cast<uint2*>(smem + L.off_qf) + warp * (QF_CAP / 2);                  // SMALL: (atom | first slot << 16, survivor mask) entries
     unsigned* q2 = reinterpret_cast<unsigned*>(smem + L.off_q2) + warp * (2 * (QW + 1) * Q2_CAP);  // plain | polar: pair, class
     auto qput = [](unsigned* q, int cap, int at, unsigned i, unsigned j) {
         if (SMALL) q[at] = i | (j << 16); else { q[at] = i; q[cap + at] = j; }
@@ -236,7 +237,6 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                 if (lane < E1_PARTNER_SETS)
                     partner[lane * pwords + wd] = lane == 8 ? ~solv : (((lane & 1) ? hbu : 0u) | ((lane & 2) ? cat : 0u) | ((lane & 4) ? an : 0u) | solv);
             }
-            if (tid < 32) M->qcur[tid] = 0;
             __syncthreads();               // from here on the float4 image is dead: its shared memory holds the (empty) queues
         } else if (n_pc + n_st > 0) __syncthreads();     // the ring list is complete before any warp reaches the ring phase
         const int px = hdr->nc[0] + 2, pxy = px * (hdr->nc[1] + 2), ncell = hdr->ncell;
@@ -267,33 +267,9 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
         for (;;) {
             // ---- E1 ----
             if (SMALL) {
-                // Slot pairs, packed float32 arithmetic; distance AND locality / polar-partner filter in one pass, survivors queued
-                // straight into the E2 queue.
+                // Slot pairs, packed float32 arithmetic; distance AND locality / polar-partner filter in one pass; the survivor masks
+                // go to the warp's entry queue (qfn = entries queued; 32 entries hold at least one E2 batch).
                 while (qfn < E1_TARGET && !exhausted) {
-                    if (__any_sync(FULL, mask != 0u)) {
-                        // Queue the pending survivors: every lane reserves room with ONE shared atomic on the warp's cursor (no scan).
-                        // Reservations are served in some order; those past the capacity are taken back (all later ones are past it too,
-                        // so the cursor ends on the last entry written) and stay pending until E2 has drained a batch.  qfn < 32 here
-                        // and a lane holds at most 32, so somebody always gets in.
-                        const int cnt = __popc(mask);
-                        if (cnt) {
-                            int at = atomicAdd(&M->qcur[warp], cnt);
-                            if (at + cnt <= QF_CAP) {
-                                unsigned m = mask;
-                                while (m) {
-                                    const int k = __ffs(m) - 1;
-                                    m &= m - 1u;
-                                    qf[at++] = (unsigned)my_i | ((unsigned)(mbase + k) << 16);
-                                }
-                                mask = 0u;
-                            } else atomicSub(&M->qcur[warp], cnt);
-                        }
-                        __syncwarp();
-                        qfn = *reinterpret_cast<volatile int*>(&M->qcur[warp]);
-                        if (qfn >= E1_TARGET) break;
-                        if (__any_sync(FULL, mask != 0u)) break;     // the queue is full: let E2 run
-                        continue;
-                    }
                     k0 += 32;
                     if (k0 >= maxlen) {
                         // next range of a whole-tile unit, or the next unit of work: whole tiles while many remain (one shared
@@ -372,9 +348,14 @@ CHC_UNROLL(E1_UNROLL)
                     const unsigned part = __funnelshift_r(my_partner[wq], my_partner[wq + 1], wr);
                     const int lo = max(lead - k0, 0), hi = min(len - k0, 32);
                     const unsigned valid = hi > lo ? ((hi >= 32 ? 0xffffffffu : ((1u << hi) - 1u)) & ~((1u << lo) - 1u)) : 0u;
-                    mask = hits & (~local | part) & valid;
+                    // One queue entry per lane with survivors: (atom slot | first slot << 16, survivor mask), placed by ballot rank
+                    // (no per-survivor loop, no atomics); E2 deals the survivors of the entries out to its 32 lanes.  qfn < 32 here
+                    // and at most 32 entries are added: QE_CAP = 64 always holds them.
+                    const unsigned surv = hits & (~local | part) & valid;
+                    const unsigned bal = __ballot_sync(FULL, surv != 0u);
+                    if (surv) qe[qfn + __popc(bal & ((1u << lane) - 1u))] = make_uint2((unsigned)my_i | ((unsigned)mbase << 16), surv);
+                    qfn += __popc(bal);
                 }
-                if (exhausted) qfn = *reinterpret_cast<volatile int*>(&M->qcur[warp]);
                 if (qfn == 0 && q2n == 0 && q3n == 0) break;           // only reachable when exhausted
                 __syncwarp();
             } else {
@@ -481,13 +462,47 @@ CHC_UNROLL(E1_UNROLL)
             //      polar queue (salt bridge, hydrogen bond, water edge), so that an E3 batch runs one kind of code ----
             const bool drain1 = exhausted && q1n == 0;
             if (qfn >= 32 || (drain1 && qfn > 0)) {
-                const int nb = min(qfn, 32);
-                qfn -= nb;
-                if (SMALL) { if (lane == 0) M->qcur[warp] = qfn; }     // the lanes' reservations start from here again
                 unsigned cls = 0u; float d2 = 0.f; unsigned ei = 0u, ej = 0u;
-                if (lane < nb) {
-                    qget(qf, QF_CAP, qfn + lane, ei, ej);
-                    cls = e2_classify<TN>(T, P, F, (int)ei, (int)ej, d2);
+                if (SMALL) {
+                    // Deal out up to 32 survivors from the top entries of the queue (lane L looks at entry qfn - 1 - L): prefix sum
+                    // of the entries' survivor counts, the entry of survivor s by binary search over the prefix sums, its bit by
+                    // clearing the lower ones.  Entries used up leave the queue; the one cut by the batch keeps its unused bits.
+                    const int nw = min(qfn, 32);
+                    uint2 ent = make_uint2(0u, 0u);
+                    if (lane < nw) ent = qe[qfn - 1 - lane];
+                    const int c = __popc(ent.y);
+                    int incl = c;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += t; }
+                    const int S = min(32, __shfl_sync(FULL, incl, 31));          // survivors in this batch
+                    int e = 0;                                                    // entries with incl <= lane  ==  the entry of survivor `lane`
+#pragma unroll
+                    for (int step = 16; step; step >>= 1) { const int v = __shfl_sync(FULL, incl, (e + step - 1) & 31); if (v <= lane) e += step; }
+                    e &= 31;
+                    const unsigned im = __shfl_sync(FULL, ent.x, e), em = __shfl_sync(FULL, ent.y, e);
+                    const int before = __shfl_sync(FULL, incl - c, e);
+                    if (lane < S) {
+                        unsigned m = em;
+                        for (int n = lane - before; n > 0; --n) m &= m - 1u;
+                        ei = im & 0xffffu; ej = (im >> 16) + (unsigned)(__ffs(m) - 1);
+                    }
+                    // the entry holding survivor S - 1 is the last one touched: keep what the batch did not use of it
+                    const int lb = __shfl_sync(FULL, e, S - 1);
+                    int keep = 0;
+                    if (lane == lb) {
+                        unsigned m = ent.y;
+                        for (int n = S - (incl - c); n > 0; --n) m &= m - 1u;
+                        if (m) { qe[qfn - 1 - lane].y = m; keep = 1; }
+                    }
+                    qfn -= lb + 1 - __shfl_sync(FULL, keep, lb);
+                    if (lane < S) cls = e2_classify<TN>(T, P, F, (int)ei, (int)ej, d2);
+                } else {
+                    const int nb = min(qfn, 32);
+                    qfn -= nb;
+                    if (lane < nb) {
+                        qget(qf, QF_CAP, qfn + lane, ei, ej);
+                        cls = e2_classify<TN>(T, P, F, (int)ei, (int)ej, d2);
+                    }
                 }
                 const bool polar = (cls & (C_SB | C_HB | C_HBW | C_NEARS | C_NEARB)) != 0u;
                 const unsigned balp = __ballot_sync(FULL, polar), balv = __ballot_sync(FULL, cls != 0u && !polar);
