@@ -72,7 +72,7 @@ class ChcStats(C.Structure):
                                          "contacts_dropped", "near_total")] + \
                [(n, C.c_int32) for n in ("path", "smem_bytes", "threads", "grid", "bin_smem_bytes", "bin_grid")] + \
                [("chunk_frames", C.c_int64), ("record_bytes", C.c_int64), ("pair_ms_total", C.c_double),
-                ("bin_ms_total", C.c_double), ("timed_chunks", C.c_int64), ("bin_variant", C.c_int32), ("bin_apt", C.c_int32)]
+                ("bin_ms_total", C.c_double), ("timed_chunks", C.c_int64), ("bin_variant", C.c_int32), ("bin_apt", C.c_int32), ("fused", C.c_int32), ("fused_smem_bytes", C.c_int32)]
 
 
 # every symbol include/chacra_b200.h declares: name -> (restype, argtypes)

@@ -27,6 +27,9 @@ struct chc_ctx {
     DevTopo T{};
     DevParams P{};
     PairLayout L{};
+    PairLayout LF{};             // shared-memory plan of the fused kernel (the CTA sorts its own frame); valid when fused_ok
+    bool fused_ok = false;
+    long long* open_idx = nullptr; int64_t open_cap = 0;     // fragment-opening frames of a chunk (hydrophobic masks ahead of the fused kernel)
     BinLayout B{};
     BinTmaLayout Y{};
     bool small_path = true, bin_tma = false; int tma_apt = 8;
@@ -96,9 +99,17 @@ static const void* bin_kernel_fn(int variant, int apt, int* threads) {
     }
 }
 
-static const void* pair_kernel_fn(bool small, bool near) {
-    if (small) return near ? (const void*)pair_frames_kernel<PAIR_THREADS, true, true> : (const void*)pair_frames_kernel<PAIR_THREADS, true, false>;
-    return near ? (const void*)pair_frames_kernel<PAIR_THREADS, false, true> : (const void*)pair_frames_kernel<PAIR_THREADS, false, false>;
+// small: the frame lives in shared memory; rec: records mode (contact records and / or near-cutoff channel); fused: the CTA
+// sorts its frame itself from the caller's coordinates (no binned record)
+static const void* pair_kernel_fn(bool small, bool rec, bool fused = false) {
+    if (fused) return rec ? (const void*)pair_frames_kernel<PAIR_THREADS, true, true, true> : (const void*)pair_frames_kernel<PAIR_THREADS, true, false, true>;
+    if (small) return rec ? (const void*)pair_frames_kernel<PAIR_THREADS, true, true, false> : (const void*)pair_frames_kernel<PAIR_THREADS, true, false, false>;
+    return rec ? (const void*)pair_frames_kernel<PAIR_THREADS, false, true, false> : (const void*)pair_frames_kernel<PAIR_THREADS, false, false, false>;
+}
+
+__global__ void iota_stride_kernel(long long* out, long long first, long long step, int n) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < n) out[k] = first + (long long)k * step;
 }
 
 static size_t al16(size_t v) { return (v + 15) & ~size_t(15); }
@@ -190,6 +201,34 @@ static int plan(chc_ctx* ctx, size_t cells_cap = 49152) {
     L.off_rlist = (int)off; off += 4 * (size_t)rlist_cap;
     L.rlist_cap = rlist_cap;
     L.total = (int)off;
+    // ---- fused kernel: no landing zone for a record; queues in their own space; aux atoms copied out of the frame ----
+    ctx->fused_ok = false;
+    if (ctx->small_path && T.n_pair <= FUSED_APT * PAIR_THREADS && 3 * T.n_aux <= FUSED_AUX * PAIR_THREADS && B.max_cells + 1 < 4 * 8 * PAIR_THREADS && getenv("CHACRA_FUSED") && !getenv("CHACRA_BIN_VARIANT")) {   // opt-in (CHACRA_FUSED=1): measured 7 % slower than the two-kernel path, DESIGN.md 3
+        PairLayout& G = ctx->LF;
+        G = L;
+        size_t o = 0;
+        G.off_rec = 0;
+        G.off_cells = (int)o; o += al16(cell_bytes * (size_t)B.max_cells + 32);
+        G.off_cnt = (int)o;   o += al16(cell_bytes * (size_t)B.max_cells + 32);
+        G.off_bits = (int)o;  o += plain_bits;
+        G.off_exy = (int)o;   o += al16(16 * e_pairs);
+        G.off_ez = (int)o;    o += al16(16 * e_pairs);
+        G.off_ek = (int)o;    o += partner_bytes;
+        G.off_sw = (int)o;    o += al16(4 * 2 * e_pairs);
+        G.off_plkf = 0;
+        G.off_pres = (int)o;  o += al16(2 * (size_t)T.n_pair);
+        G.off_pst = (int)o;   o += al16((size_t)T.n_pair);
+        G.off_aux = (int)o;   o += al16(12 * (size_t)std::max(T.n_aux, 1));
+        G.off_q1 = G.off_qf = (int)o; o += qfb;
+        G.off_q2 = (int)o;    o += q2b;
+        G.off_tv = (int)o;    o += al16(4 * (size_t)T.K * T.K);
+        G.off_th = (int)o;    o += al16(4 * (size_t)T.K * T.K);
+        G.off_misc = (int)o;  o += al16(sizeof(PairMisc));
+        G.off_rc = (int)o;
+        G.off_rlist = (int)o; o += 4 * (size_t)rlist_cap;
+        G.total = (int)o;
+        ctx->fused_ok = (size_t)G.total <= SMEM_LIMIT;
+    }
     ctx->bin_smem = (int)al16(4 * (size_t)B.max_cells);
     if ((size_t)L.total > SMEM_LIMIT || (size_t)ctx->bin_smem + 1024 > SMEM_LIMIT) return CHC_E_TOO_LARGE;
     return CHC_OK;
@@ -210,7 +249,7 @@ extern "C" void chc_destroy(chc_ctx* ctx) {
     if (ctx->counts_owned) cudaFree(ctx->counts);
     cudaFree(ctx->contacts); cudaFree(ctx->contact_n); cudaFree(ctx->near); cudaFree(ctx->near_n);
     cudaFree(ctx->hpmask); cudaFree(ctx->binned); cudaFree(ctx->gstamp); cudaFree(ctx->gstate);
-    cudaFree(ctx->wscratch); cudaFree(ctx->status);
+    cudaFree(ctx->wscratch); cudaFree(ctx->status); cudaFree(ctx->open_idx);
     for (int k = 0; k < 2; ++k) {
         cudaFree(ctx->dev_stage[k]); if (ctx->pin_stage[k]) cudaFreeHost(ctx->pin_stage[k]);
         if (ctx->stage_done[k]) cudaEventDestroy(ctx->stage_done[k]);
@@ -333,6 +372,8 @@ extern "C" int chc_create(chc_ctx** out, const chc_topology* t, const chc_params
     rc = plan(ctx);
     if (rc != CHC_OK) return fail(ctx, rc, "topology with %d pair atoms / %d residues does not fit any kernel path", T.n_pair, T.R);
     CK(cudaFuncSetAttribute(pair_kernel_fn(ctx->small_path, p->track_near != 0 || p->emit_contacts != 0), cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->L.total));
+    if (ctx->fused_ok)
+        CK(cudaFuncSetAttribute(pair_kernel_fn(true, p->track_near != 0 || p->emit_contacts != 0, true), cudaFuncAttributeMaxDynamicSharedMemorySize, ctx->LF.total));
     // binning kernel variant: registers hold the frame's pair atoms when they fit (one HBM pass), else three gather passes
     ctx->bin_variant = T.n_pair <= 512 * 8 ? 1 : (T.n_pair <= 1024 * 8 ? 2 : 0);
     // frames that fit in shared memory stream through bulk async copies (bin_tma_kernel.cuh)
@@ -419,6 +460,8 @@ extern "C" int chc_create(chc_ctx** out, const chc_topology* t, const chc_params
     ctx->st.grid = ctx->pair_grid; ctx->st.bin_smem_bytes = ctx->bin_smem; ctx->st.bin_grid = ctx->bin_grid;
     ctx->st.chunk_frames = ctx->chunk_frames; ctx->st.record_bytes = ctx->B.stride;
     ctx->st.bin_variant = ctx->bin_variant; ctx->st.bin_apt = ctx->bin_tma ? ctx->tma_apt : 0;
+    ctx->st.fused = ctx->fused_ok && (!((p->itype_mask & CHC_IT_HP) && t->n_hp_base > 0) || (ctx->bin_tma && t->same_selection)) ? 1 : 0;
+    ctx->st.fused_smem_bytes = ctx->fused_ok ? ctx->LF.total : 0;
     return CHC_OK;
 }
 
@@ -515,40 +558,68 @@ static int submit_impl(chc_ctx* ctx, int state, const float* d_xyz, const long l
         }
         const bool hp_on = (ctx->P.itypes & CHC_IT_HP) && ctx->T.n_hp_base > 0;
         const bool fuse_hp = hp_on && ctx->bin_tma && ctx->T.same;      // the binning CTA answers the 1.7 A query itself
-        {
-            int nn = n; long long fi = first_index + c0, fs = frame_stride, fr0 = frag0; int ff = F, fuse = fuse_hp ? 1 : 0;
+        // Fused path: the pair kernel sorts every frame itself; only the frames that OPEN a fragment go through the binning
+        // kernel first, for the hydrophobic masks of their fragments (the binning kernel with fragment length 1 and a source index).
+        const bool fused = ctx->fused_ok && !d_src && (!hp_on || fuse_hp);
+        auto launch_bin = [&](const float* bx, const long long* bsrc, int nn, long long fi, int ff, long long slot0, int open_phase, int fuse) -> int {
+            long long fs = frame_stride, fr0 = frag0;
             BinTmaLayout Y = ctx->Y;
-            Y.open_phase = (int)(fi % F);
-            long long slot0 = fi / F - frag0;
-            void* args_reg[] = {&ctx->T, &ctx->P, &ctx->B, &x, &fs, &nn, &fi, &ff, &fr0, &ctx->binned, &ctx->hpmask, &src};
-            void* args_tma[] = {&ctx->T, &ctx->P, &ctx->B, &Y, &x, &fs, &nn, &ff, &slot0, &ctx->binned, &ctx->hpmask, &fuse, &src};
-            CK(cudaLaunchKernel(bin_kernel_fn(ctx->bin_variant, ctx->tma_apt, nullptr), dim3(std::min(n, ctx->bin_grid)), dim3(ctx->bin_threads),
+            Y.open_phase = open_phase;
+            void* args_reg[] = {&ctx->T, &ctx->P, &ctx->B, &bx, &fs, &nn, &fi, &ff, &fr0, &ctx->binned, &ctx->hpmask, &bsrc};
+            void* args_tma[] = {&ctx->T, &ctx->P, &ctx->B, &Y, &bx, &fs, &nn, &ff, &slot0, &ctx->binned, &ctx->hpmask, &fuse, &bsrc};
+            CK(cudaLaunchKernel(bin_kernel_fn(ctx->bin_variant, ctx->tma_apt, nullptr), dim3(std::min(nn, ctx->bin_grid)), dim3(ctx->bin_threads),
                                 ctx->bin_tma ? args_tma : args_reg, ctx->bin_smem, stream));
-        }
-        CK(cudaGetLastError());
-        if (ctx->timing) CK(cudaEventRecord(ev.b, stream));        // the hydrophobic query kernel (below) is timed with the pair kernel
-        if (hp_on && !fuse_hp) {
-            const int64_t fi = first_index + c0;
-            const int64_t f0 = (F - fi % F) % F;                  // first fragment-opening frame of the chunk
-            if (f0 < n) {
+            CK(cudaGetLastError());
+            ctx->st.kernel_launches++;
+            return CHC_OK;
+        };
+        const long long fi0 = first_index + c0;
+        if (fused) {
+            const int64_t f0 = (F - fi0 % F) % F;                 // first fragment-opening frame of the chunk
+            if (hp_on && f0 < n) {
                 const int n_open = (int)((n - f0 + F - 1) / F);
-                const int by = std::max(1, std::min(1024, (ctx->T.n_hp_base + 7) / 8));     // one base carbon per warp
-                hp_mask_kernel<<<dim3(n_open, by), 256, 0, stream>>>(ctx->T, ctx->P, ctx->B, x, frame_stride, n, fi, F, frag0,
-                                                                     ctx->binned, ctx->hpmask, src);
+                if (n_open > ctx->open_cap) {
+                    CK(cudaStreamSynchronize(stream));
+                    cudaFree(ctx->open_idx);
+                    ctx->open_cap = std::max<int64_t>(256, 2 * (int64_t)n_open);
+                    CK(cudaMalloc(&ctx->open_idx, (size_t)ctx->open_cap * sizeof(long long)));
+                }
+                iota_stride_kernel<<<(n_open + 255) / 256, 256, 0, stream>>>(ctx->open_idx, (long long)f0, (long long)F, n_open);
                 CK(cudaGetLastError());
-                ctx->st.kernel_launches++;
+                int rcb = launch_bin(x, ctx->open_idx, n_open, fi0 + f0, 1, (fi0 + f0) / F - frag0, 0, 1);
+                if (rcb != CHC_OK) return rcb;
             }
-        }
-        const int grid = std::min(n, ctx->pair_grid);
-        {
-            int nn = n; long long fi = first_index + c0, fr0 = frag0; int ff = F;
+            if (ctx->timing) CK(cudaEventRecord(ev.b, stream));
+            int nn = n; long long fi = fi0, fr0 = frag0, fs = frame_stride; int ff = F;
+            unsigned* gs = nullptr; unsigned* gt = nullptr;
+            void* args[] = {&ctx->T, &ctx->P, &O, &ctx->LF, &ctx->B, &ctx->binned, &nn, &fi, &ff, &fr0, &ctx->hpmask, &gs, &gt, &ctx->wscratch, &x, &fs};
+            CK(cudaLaunchKernel(pair_kernel_fn(true, ctx->P.track_near != 0 || ctx->P.emit != 0, true), dim3(std::min(n, ctx->pair_grid)), dim3(PAIR_THREADS),
+                                args, ctx->LF.total, stream));
+            ctx->st.kernel_launches++;
+        } else {
+            int rcb = launch_bin(x, src, n, fi0, F, fi0 / F - frag0, (int)(fi0 % F), fuse_hp ? 1 : 0);
+            if (rcb != CHC_OK) return rcb;
+            if (ctx->timing) CK(cudaEventRecord(ev.b, stream));        // the hydrophobic query kernel (below) is timed with the pair kernel
+            if (hp_on && !fuse_hp) {
+                const int64_t f0 = (F - fi0 % F) % F;                 // first fragment-opening frame of the chunk
+                if (f0 < n) {
+                    const int n_open = (int)((n - f0 + F - 1) / F);
+                    const int by = std::max(1, std::min(1024, (ctx->T.n_hp_base + 7) / 8));     // one base carbon per warp
+                    hp_mask_kernel<<<dim3(n_open, by), 256, 0, stream>>>(ctx->T, ctx->P, ctx->B, x, frame_stride, n, fi0, F, frag0,
+                                                                         ctx->binned, ctx->hpmask, src);
+                    CK(cudaGetLastError());
+                    ctx->st.kernel_launches++;
+                }
+            }
+            const int grid = std::min(n, ctx->pair_grid);
+            int nn = n; long long fi = fi0, fr0 = frag0, fs = frame_stride; int ff = F;
             unsigned* gs = ctx->small_path ? nullptr : ctx->gstamp; unsigned* gt = ctx->small_path ? nullptr : ctx->gstate;
-            void* args[] = {&ctx->T, &ctx->P, &O, &ctx->L, &ctx->B, &ctx->binned, &nn, &fi, &ff, &fr0, &ctx->hpmask, &gs, &gt, &ctx->wscratch};
+            void* args[] = {&ctx->T, &ctx->P, &O, &ctx->L, &ctx->B, &ctx->binned, &nn, &fi, &ff, &fr0, &ctx->hpmask, &gs, &gt, &ctx->wscratch, &x, &fs};
             CK(cudaLaunchKernel(pair_kernel_fn(ctx->small_path, ctx->P.track_near != 0 || ctx->P.emit != 0), dim3(grid), dim3(PAIR_THREADS), args, ctx->L.total, stream));
+            ctx->st.kernel_launches++;
         }
         CK(cudaGetLastError());
         if (ctx->timing) { CK(cudaEventRecord(ev.c, stream)); ctx->ev_pending.push_back(ev); }
-        ctx->st.kernel_launches += 2;
     }
     ctx->st.frames_submitted += n_frames;
     ctx->last_state = state; ctx->next_index = first_index + n_frames;

@@ -47,7 +47,8 @@ struct PairLayout {         // shared-memory plan of the pair kernel (bytes)
     // The float4 image the bulk copy lands (inside off_rec) is dead once these are built: the queues live there.
     int off_exy, off_ez, off_ek, off_sw, off_sres;      // off_ez: float4 z0 z1 lkey0 lkey1 per slot pair; off_ek: partner bit arrays
     int off_plkf, off_pres, off_pst;                    // SMALL, by pair index (loaded once per launch): locality key (float), residue rank, static bits
-    int off_rc, off_rlist, rlist_cap;                   // ring centroids (float[3 n_rings]) and the ring tasks that passed the prefilter
+    int off_rc, off_rlist, rlist_cap;
+    int off_aux, off_cnt;                               // FUSED: aux atoms copied out of the frame; transient cell counters                   // ring centroids (float[3 n_rings]) and the ring tasks that passed the prefilter
     int bits_words;         // words of the residue-pair set (plain: P/32, stamped: P/24)
     int total;
 };
@@ -80,15 +81,27 @@ struct PairMisc {
     int nmark;                  // waters with at least one hydrogen bond to a non-solvent atom (this frame)
     int qcur[32];               // SMALL: entries in every warp's E2 queue (lanes reserve room with one shared atomic each)
     int rn_pc, rn_st;           // ring tasks that passed the centroid prefilter: pi-cation from the front of the list, stacking from its end
+    // FUSED (the CTA sorts its own frame): bounding box as ordered ints, warp totals of the scan, the grid of this frame
+    int bb_min[2][3], bb_max[2][3];
+    int carry[32];
+    BinHeader hdr;
 };
 
-// TN: the near-cutoff side channel is compiled in (chc_params.track_near); the counts-only production path carries none of it
-template <int THREADS, bool SMALL, bool TN>
+// TN: records mode -- contact records and / or the near-cutoff side channel are compiled in (chc_params.emit_contacts,
+//     track_near); the counts-only production path carries none of it.
+// FUSED (with SMALL): no binned record at all.  The CTA reads its frame straight from the caller's coordinates (the frame it
+//     needs next is prefetched into L2 one frame ahead with a bulk prefetch), sorts the pair atoms into the cell list itself
+//     (shared-memory counting sort: cell + rank by one shared atomic, packed 16-bit scan, scatter into the slot-pair arrays)
+//     and goes on to the pair phase: every coordinate crosses HBM once and nothing is written back but counts.
+#define FUSED_APT 4             // pair atoms per thread the in-kernel sort can take (n_pair <= FUSED_APT * THREADS)
+#define FUSED_AUX 3             // aux coordinates per thread (3 n_aux <= FUSED_AUX * THREADS)
+template <int THREADS, bool SMALL, bool TN, bool FUSED>
 __global__ void __launch_bounds__(THREADS, 1)
 pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, const unsigned char* __restrict__ binned,
                    int n_frames, long long first_index, int frag_frames, long long frag0,
                    const unsigned char* __restrict__ hpmask, unsigned* __restrict__ gstamp, unsigned* __restrict__ gstate,
-                   int* __restrict__ wscratch) {
+                   int* __restrict__ wscratch, const float* __restrict__ xyz, long long frame_stride) {
+    static_assert(!FUSED || SMALL, "the in-kernel sort feeds the shared-memory path");
     extern __shared__ __align__(128) unsigned char smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     float* tv = reinterpret_cast<float*>(smem + L.off_tv);
@@ -115,22 +128,196 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
     unsigned char* p_st = reinterpret_cast<unsigned char*>(smem + L.off_pst);
     if (SMALL) {
         for (int k = tid; k < T.n_pair; k += THREADS) {
-            p_lkf[k] = (float)T.pair_lkey[k]; p_res[k] = (unsigned short)T.pair_res[k]; p_st[k] = (unsigned char)((T.pair_info[k] >> 14) & 0x1fu);
+            if (!FUSED) p_lkf[k] = (float)T.pair_lkey[k];
+            p_res[k] = (unsigned short)T.pair_res[k]; p_st[k] = (unsigned char)((T.pair_info[k] >> 14) & 0x1fu);
         }
         bits = reinterpret_cast<unsigned*>(smem + L.off_bits);
-        if (tid == 0) { mbar_init(&M->bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+        if (!FUSED && tid == 0) { mbar_init(&M->bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+        if (FUSED) {
+            // the padding slots behind the last atom never change; all cell counters start at zero; the box starts empty
+            float4* e0 = reinterpret_cast<float4*>(smem + L.off_exy); float4* z0 = reinterpret_cast<float4*>(smem + L.off_ez);
+            unsigned* w0 = reinterpret_cast<unsigned*>(smem + L.off_sw);
+            const int np2 = (T.n_pair + 1) >> 1;
+            for (int q = tid; q < np2 + E1_PAD_PAIRS; q += THREADS) {
+                e0[q] = make_float4(3.0e18f, 3.0e18f, 3.0e18f, 3.0e18f); z0[q] = make_float4(3.0e18f, 3.0e18f, -3.0e7f, -3.0e7f);
+                w0[2 * q] = 0u; w0[2 * q + 1] = 0u;
+            }
+            unsigned* cw = reinterpret_cast<unsigned*>(smem + L.off_cnt);
+            for (int q = tid; q < 4 * ((B.max_cells + 8) / 8); q += THREADS) cw[q] = 0u;
+            if (tid < 6) { M->bb_min[tid / 3][tid % 3] = 0x7fffffff; M->bb_max[tid / 3][tid % 3] = (int)0x80000000; }
+        }
     } else {
         bits = gstamp + (size_t)blockIdx.x * L.bits_words;
         gen = gstate[blockIdx.x];          // generation carried across launches (0 on the first one)
     }
     __syncthreads();
     unsigned phase = 0;
+    // FUSED: this thread's pair atoms p = tid + k THREADS of the frame to be sorted next (coordinates, locality key, flag word)
+    // and its share of the aux coordinates; loaded by fused_load, which also merges the atoms into the bounding box M->bb_*[box].
+    float rx[FUSED ? FUSED_APT : 1], ry[FUSED ? FUSED_APT : 1], rz[FUSED ? FUSED_APT : 1], rlk[FUSED ? FUSED_APT : 1], raux[FUSED ? FUSED_AUX : 1];
+    unsigned rinfo[FUSED ? FUSED_APT : 1];
+    int par = 0;
+    auto fused_load = [&](int fn, int box) {
+        if (!FUSED) return;
+        // every register is (re)defined on every call, also past the last frame: nothing stays live through the pair phase
+        const bool live = fn < n_frames;
+        const float* X = xyz + (size_t)(live ? fn : 0) * (size_t)frame_stride;
+        float lo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, hi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
+#pragma unroll
+        for (int k = 0; k < (FUSED ? FUSED_APT : 1); ++k) {
+            const int p = tid + k * THREADS;
+            rx[k] = 0.f; ry[k] = 0.f; rz[k] = 0.f; rlk[k] = 0.f; rinfo[k] = 0u;
+            if (live && p < T.n_pair) {
+                const float* q = X + 3 * (size_t)__ldg(&T.pair_atom[p]);
+                rx[k] = __ldcs(q); ry[k] = __ldcs(q + 1); rz[k] = __ldcs(q + 2);
+                rlk[k] = (float)__ldg(&T.pair_lkey[p]);
+                rinfo[k] = (__ldg(&T.pair_info[p]) & I_WMASK) | ((unsigned)p << I_PIDX_SHIFT);
+                lo[0] = fminf(lo[0], rx[k]); hi[0] = fmaxf(hi[0], rx[k]);
+                lo[1] = fminf(lo[1], ry[k]); hi[1] = fmaxf(hi[1], ry[k]);
+                lo[2] = fminf(lo[2], rz[k]); hi[2] = fmaxf(hi[2], rz[k]);
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < (FUSED ? FUSED_AUX : 1); ++k) {
+            const int e = tid + k * THREADS;
+            raux[k] = 0.f;
+            if (live && e < 3 * T.n_aux) { const int a = e / 3; raux[k] = __ldcs(X + 3 * (size_t)__ldg(&T.aux_atom[a]) + (e - 3 * a)); }
+        }
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+            const int a = __reduce_min_sync(FULL, f2ord(lo[d])), c = __reduce_max_sync(FULL, f2ord(hi[d]));
+            if (live && lane == 0) { atomicMin(&M->bb_min[box][d], a); atomicMax(&M->bb_max[box][d], c); }
+        }
+    };
+    if (FUSED) {
+        if (tid == 0 && (int)(blockIdx.x + gridDim.x) < n_frames) {
+            const unsigned long long a = reinterpret_cast<unsigned long long>(xyz + (size_t)(blockIdx.x + gridDim.x) * (size_t)frame_stride);
+            const unsigned long long a0 = a & ~15ull;
+            const unsigned bytes = ((unsigned)(a - a0) + 12u * (unsigned)T.n_atoms) & ~15u;
+            if (bytes) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a0), "r"(bytes) : "memory");
+        }
+        fused_load((int)blockIdx.x, 0);
+        __syncthreads();
+    }
 
     for (int f = blockIdx.x; f < n_frames; f += gridDim.x) {
         const unsigned char* rec = binned + (size_t)f * B.stride;
         const long long gidx = first_index + f;
         const float4* spos; const float* aux; const cell_t* cells; const BinHeader* hdr;
-        if (SMALL) {
+        if (FUSED) {
+            // ---- S: this CTA's frame into the cell-sorted slot-pair arrays.  The coordinates (and the static words) of this
+            //      thread's pair atoms are already in registers: every warp loaded them at the end of its pair phase of the
+            //      previous frame (fused_load below: the global-memory latency hides in the frame tail), and the bounding box
+            //      of the frame is complete in M->bb_*[par]. ----
+            const int NPs = T.n_pair;
+            const bool gridb = T.n_pair_a < NPs;
+            float4* e_xy = reinterpret_cast<float4*>(smem + L.off_exy);
+            float4* e_zk = reinterpret_cast<float4*>(smem + L.off_ez);
+            unsigned* e_w = reinterpret_cast<unsigned*>(smem + L.off_sw);
+            float* auxs = reinterpret_cast<float*>(smem + L.off_aux);
+            unsigned short* cnt16 = reinterpret_cast<unsigned short*>(smem + L.off_cells);
+            unsigned* cntw = reinterpret_cast<unsigned*>(smem + L.off_cnt);          // transient counters: all zero between frames
+            if (tid == 0) {
+#ifndef NO_L2_PREFETCH
+                if (f + 2 * (int)gridDim.x < n_frames) {   // two frames ahead: the next one is read in this frame's tail
+                    const unsigned long long a = reinterpret_cast<unsigned long long>(xyz + (size_t)(f + 2 * (int)gridDim.x) * (size_t)frame_stride);
+                    const unsigned long long a0 = a & ~15ull;
+                    const unsigned bytes = ((unsigned)(a - a0) + 12u * (unsigned)T.n_atoms) & ~15u;     // rounded down: stays inside the frame
+                    if (bytes) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a0), "r"(bytes) : "memory");
+                }
+#endif
+                M->cursor = 0; M->ring_cursor = 0; M->nmark = 0; M->rn_pc = 0; M->rn_st = 0;
+            }
+            float org[3], inv; int nc[3];
+            {
+                float ext[3];
+#pragma unroll
+                for (int d = 0; d < 3; ++d) { org[d] = ord2f(M->bb_min[par][d]); ext[d] = ord2f(M->bb_max[par][d]) - org[d]; }
+                grid_dims(ext, P.cell, B.max_cells, gridb, inv, nc);
+            }
+            const int fpx = nc[0] + 2, fpxy = fpx * (nc[1] + 2), fncell = fpxy * (nc[2] + 2);
+            const int nkey = gridb ? 2 * fncell : fncell;
+            // S2: cell of every atom; the shared atomic on the packed 16-bit counters returns the atom's rank inside its cell.
+            //     The aux atoms (donor hydrogens, ring atoms, cations) and the empty residue-pair set ride in the same interval.
+            unsigned r_cr[FUSED_APT];
+#pragma unroll
+            for (int k = 0; k < FUSED_APT; ++k) {
+                const int p = tid + k * THREADS;
+                if (p < NPs) {
+                    int c = (cell_of(rz[k], org[2], inv, nc[2]) + 1) * fpxy + (cell_of(ry[k], org[1], inv, nc[1]) + 1) * fpx + cell_of(rx[k], org[0], inv, nc[0]) + 1;
+                    if (p >= T.n_pair_a) c += fncell;
+                    const unsigned sh = ((unsigned)c & 1u) << 4;
+                    const unsigned old = atomicAdd(&cntw[c >> 1], 1u << sh);
+                    r_cr[k] = (unsigned)c | (((old >> sh) & 0xffffu) << 16);
+                } else r_cr[k] = 0u;
+            }
+#pragma unroll
+            for (int k = 0; k < FUSED_AUX; ++k) { const int e = tid + k * THREADS; if (e < 3 * T.n_aux) auxs[e] = raux[k]; }
+            for (int w = tid; w < L.bits_words; w += THREADS) bits[w] = 0u;
+            __syncthreads();
+            if (tid < 3) { M->bb_min[par ^ 1][tid] = 0x7fffffff; M->bb_max[par ^ 1][tid] = (int)0x80000000; }   // the box this frame's tail fills
+            // S3: exclusive scan of counters 0..nkey into the cell starts; the counters go back to zero.  Thread t owns counters
+            //     [8 groups t, 8 groups (t + 1)).
+            {
+                const int groups = (nkey + 8 * THREADS) / (8 * THREADS);
+                uint4 v[4];
+                unsigned s2 = 0u;         // even counters in the low half, odd ones in the high half (sums <= n_pair < 65 536)
+#pragma unroll
+                for (int g = 0; g < 4; ++g)
+                    if (g < groups) {
+                        const bool have = 8 * (tid * groups + g) <= nkey;      // only the counters 0..nkey exist
+                        v[g] = have ? reinterpret_cast<const uint4*>(cntw)[tid * groups + g] : make_uint4(0u, 0u, 0u, 0u);
+                        if (have) reinterpret_cast<uint4*>(cntw)[tid * groups + g] = make_uint4(0u, 0u, 0u, 0u);
+                        s2 += (v[g].x + v[g].y) + (v[g].z + v[g].w);
+                    }
+                const int sum = (int)((s2 & 0xffffu) + (s2 >> 16));
+                int incl = sum;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += t; }
+                if (lane == 31) M->carry[warp] = incl;
+                __syncthreads();
+                const int w0 = lane < (THREADS >> 5) ? M->carry[lane] : 0;
+                int w = w0;
+#pragma unroll
+                for (int o = 1; o < (THREADS >> 5); o <<= 1) { const int t = __shfl_up_sync(FULL, w, o); if (lane >= o) w += t; }
+                unsigned run = (unsigned)(__shfl_sync(FULL, w - w0, warp) + incl - sum);
+                auto ex2 = [&](unsigned word) {      // two counters -> their two exclusive starts
+                    const unsigned lo2 = word & 0xffffu, e = run | ((run + lo2) << 16);
+                    run += lo2 + (word >> 16);
+                    return e;
+                };
+#pragma unroll
+                for (int g = 0; g < 4; ++g)
+                    if (g < groups && 8 * (tid * groups + g) <= nkey) {
+                        uint4 e;
+                        e.x = ex2(v[g].x); e.y = ex2(v[g].y); e.z = ex2(v[g].z); e.w = ex2(v[g].w);
+                        reinterpret_cast<uint4*>(smem + L.off_cells)[tid * groups + g] = e;
+                    }
+            }
+            __syncthreads();
+            // S4: scatter into the slot-pair arrays (x0 x1 y0 y1 | z0 z1 lkey0 lkey1) and the flag words
+            {
+                float* fxy = reinterpret_cast<float*>(e_xy); float* fzk = reinterpret_cast<float*>(e_zk);
+#pragma unroll
+                for (int k = 0; k < FUSED_APT; ++k) {
+                    const int p = tid + k * THREADS;
+                    if (p < NPs) {
+                        const int dst = (int)cnt16[r_cr[k] & 0xffffu] + (int)(r_cr[k] >> 16);
+                        const int o4 = 4 * (dst >> 1) + (dst & 1);
+                        fxy[o4] = rx[k]; fxy[o4 + 2] = ry[k];
+                        fzk[o4] = rz[k]; fzk[o4 + 2] = rlk[k];
+                        e_w[dst] = rinfo[k];
+                    }
+                }
+                if (tid == 0) {
+                    BinHeader h;
+                    h.org[0] = org[0]; h.org[1] = org[1]; h.org[2] = org[2]; h.inv = inv;
+                    h.nc[0] = nc[0]; h.nc[1] = nc[1]; h.nc[2] = nc[2]; h.ncell = fncell;
+                    M->hdr = h;
+                }
+            }
+            hdr = &M->hdr; spos = nullptr; aux = auxs; cells = reinterpret_cast<const cell_t*>(smem + L.off_cells);
+        } else if (SMALL) {
             if (tid == 0) {
                 const int ncell = __ldcg(&reinterpret_cast<const BinHeader*>(rec)->ncell);
                 const unsigned cbytes = (unsigned)((sizeof(cell_t) * ((T.n_pair_a < T.n_pair ? 2 : 1) * ncell + 1) + 15) & ~15);
@@ -219,7 +406,7 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
             // The float4 image becomes slot PAIRS (E1 tests two neighbours per packed instruction): x0 x1 y0 y1 | z0 z1 lkey0 lkey1,
             // plus the flag word per slot.
             const int NPs = T.n_pair, np2 = (NPs + 1) >> 1;
-            for (int q = tid; q < np2 + E1_PAD_PAIRS; q += THREADS) {
+            if (!FUSED) for (int q = tid; q < np2 + E1_PAD_PAIRS; q += THREADS) {
                 const int j0 = 2 * q, j1 = j0 + 1;
                 const float4 far = make_float4(3.0e18f, 3.0e18f, 3.0e18f, 0.f);
                 const float4 a = j0 < NPs ? spos[j0] : far, b = j1 < NPs ? spos[j1] : far;
@@ -231,7 +418,7 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
             }
             for (int wd = warp; wd < pwords; wd += THREADS / 32) {        // partner bits, one word of 32 slots per warp round
                 const int j = wd * 32 + lane;
-                const unsigned w = j < NPs ? __float_as_uint(spos[j].w) : 0u;
+                const unsigned w = j < NPs ? (FUSED ? sw[j] : __float_as_uint(spos[j].w)) : 0u;
                 const unsigned hbu = __ballot_sync(FULL, (w & I_HBU) != 0u), cat = __ballot_sync(FULL, (w & I_CATION) != 0u),
                                an = __ballot_sync(FULL, (w & I_ANION) != 0u), solv = __ballot_sync(FULL, (w & I_SOLV) != 0u);
                 if (lane < E1_PARTNER_SETS)
@@ -563,6 +750,9 @@ CHC_UNROLL(E1_UNROLL)
                 __syncwarp();
             }
         }
+        // FUSED: a warp that is done with this frame fetches its atoms of the frame the CTA sorts next (registers + bounding box)
+        fused_load(f + (int)gridDim.x, par ^ 1);
+        par ^= 1;
         __syncthreads();
         // ---- W: water bridges from the (non-solvent, solvent) hydrogen bonds the pair phase recorded ----------------
         if (T.n_solv > 0 && (P.itypes & CHC_IT_HB)) {

@@ -182,6 +182,9 @@ typedef struct chc_stats {
     int64_t timed_chunks;
     int32_t bin_variant;          /* binning kernel: 3 / 4 = bulk-copy (two CTAs per SM / double buffered), 1 / 2 = registers, 0 = gather */
     int32_t bin_apt;              /* pair atoms per thread of the bulk-copy binning kernel (template instantiation) */
+    int32_t fused;                /* 1: chc_submit_frames runs the fused kernel (the pair kernel sorts every frame itself; the binning kernel
+                                     only sees fragment-opening frames, for the hydrophobic masks); indexed submissions use the two-kernel path */
+    int32_t fused_smem_bytes;     /* fused kernel, dynamic shared memory per CTA */
 } chc_stats;
 
 typedef struct chc_ctx chc_ctx;

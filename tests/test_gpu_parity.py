@@ -379,3 +379,22 @@ def test_unaligned_growing_submissions_keep_the_hydrophobic_set(oracle_5xnd):
                 assert np.array_equal(got[0], outs[0][0]) and np.array_equal(got[1], outs[0][1]), variant
         finally:
             os.environ.pop("CHACRA_BIN_VARIANT", None)
+
+
+def test_fused_kernel_option_matches_oracle(oracle_5xnd, monkeypatch):
+    """CHACRA_FUSED=1: the pair kernel sorts every frame itself from the caller's coordinates (no binned record; only the
+    fragment-opening frames pass through the binning kernel for the hydrophobic masks).  Same contacts, counts and near-cutoff
+    list over three fragments, device and host entry points."""
+    import getcontacts_oracle as o
+    monkeypatch.setenv("CHACRA_FUSED", "1")
+    base = oracle_5xnd["frames"]
+    frames = np.ascontiguousarray(base[np.arange(250) % 20])
+    frames[100:200] = base[(np.arange(100) + 7) % 20]
+    top = os.path.join(GOLDEN, "5xnd_topology.pdb")
+    res = o.run(top, top, ALL, frames=frames, collect_near=True)
+    want, want_near = _oracle_sets(res)
+    for host in (False, True):
+        run = _engine_run(top, frames, ALL, host=host)
+        assert run["engine"].stats()["fused"] == 1
+        assert run["contacts"] == want and run["near"] == want_near
+        _check_counts(run, res)
