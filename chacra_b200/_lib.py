@@ -12,7 +12,7 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-LIB_PATH = os.path.join(CSRC, "libchacra_b200.so")
+LIB_PATH = os.environ.get("CHACRA_LIB") or os.path.join(CSRC, "libchacra_b200.so")    # CHACRA_LIB: A/B runs of build variants
 SOURCES = ["chacra_b200.cu"]
 HEADERS = ["device_types.cuh", "bin_tma_kernel.cuh", "xtc_decode.cuh", "pca_perm.cuh", "dcd_unpack.cuh", "tsv_writer.h", "tsv_counts.h", "frame_kernel.cuh", "frame_phases.cuh", "bin_kernel.cuh", "pair_kernel.cuh", "water_phase.cuh",
            os.path.join("..", "..", "include", "chacra_b200.h")]

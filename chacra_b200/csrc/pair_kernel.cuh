@@ -32,7 +32,7 @@
 #endif
 static_assert(Q1_CAP - E1_TARGET >= 32 && QF_CAP - E1_TARGET >= 32 && E1_TARGET >= 32, "a lane's 32 pending hits must fit behind E1_TARGET queued survivors");
 #ifndef E1_UNROLL
-#define E1_UNROLL 2
+#define E1_UNROLL 4
 #endif
 #define CHC_PRAGMA(x) _Pragma(#x)
 #define CHC_UNROLL(n) CHC_PRAGMA(unroll n)
@@ -68,7 +68,7 @@ __device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 r; asm(
 #define E1_PAD_PAIRS 20        // slot pairs past the last atom that the unmasked E1 loads may touch
 #define E1_PARTNER_SETS 9
 #ifndef E1_TAIL_TILES
-#define E1_TAIL_TILES 24       // the last tiles of a frame are handed out range by range
+#define E1_TAIL_TILES 16       // the last tiles of a frame are handed out range by range
 #endif
 __device__ __forceinline__ int e1_partner_set(unsigned w) {
     return (w & I_SOLV) ? 8 : (int)(((w >> 6) & 1u) | (((w >> 8) & 1u) << 1) | (((w >> 9) & 1u) << 2));   // hbu | anion -> wants cations | cation -> wants anions
@@ -675,10 +675,10 @@ CHC_UNROLL(E1_UNROLL)
                     }
                     // the entry holding survivor S - 1 is the last one touched: keep what the batch did not use of it
                     const int lb = __shfl_sync(FULL, e, S - 1);
+                    const unsigned last = __shfl_sync(FULL, ej - (im >> 16), S - 1);     // bit of survivor S - 1 inside that entry
                     int keep = 0;
                     if (lane == lb) {
-                        unsigned m = ent.y;
-                        for (int n = S - (incl - c); n > 0; --n) m &= m - 1u;
+                        const unsigned m = ent.y & ~((2u << last) - 1u);
                         if (m) { qe[qfn - 1 - lane].y = m; keep = 1; }
                     }
                     qfn -= lb + 1 - __shfl_sync(FULL, keep, lb);
