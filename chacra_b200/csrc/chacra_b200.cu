@@ -38,6 +38,7 @@ struct chc_ctx {
     int64_t chunk_frames = 0;
     unsigned char* binned = nullptr;
     unsigned* gstamp = nullptr; unsigned* gstate = nullptr;
+    unsigned char* gsoa = nullptr;       // large path: per-CTA slot-pair arrays
     int* wscratch = nullptr; unsigned* status = nullptr;
     std::vector<void*> dev_allocs;
     int32_t* counts = nullptr; bool counts_owned = false; int64_t n_pairs = 0;
@@ -128,8 +129,8 @@ static int plan(chc_ctx* ctx, size_t cells_cap = 49152) {
     B.off_cells = B.fixed_bytes;
     auto queue_bytes = [&](bool small, size_t* q1, size_t* qf, size_t* q2) {
         const size_t qw = small ? 1 : 2;
-        // the shared-memory path filters its hits per lane and queues them straight into qf: no survivor queue q1
-        *q1 = small ? 0 : al16(4 * qw * (size_t)warps * Q1_CAP); *qf = al16(4 * qw * (size_t)warps * QF_CAP);
+        // E1 -> E2 entries (atom slot, first neighbour slot, survivor mask): 8 bytes each on the shared-memory path, 16 otherwise
+        *q1 = 0; *qf = al16((small ? 8 : 16) * (size_t)warps * QE_CAP);
         *q2 = al16(8 * (qw + 1) * (size_t)warps * Q2_CAP);
         return *q1 + *qf + *q2;
     };
@@ -156,7 +157,7 @@ static int plan(chc_ctx* ctx, size_t cells_cap = 49152) {
         if (need <= SMEM_LIMIT) { ctx->small_path = true; want_cells = cells; break; }
     }
     if (getenv("CHACRA_FORCE_LARGE")) ctx->small_path = false;     // test hook: exercise the in-place path on small systems
-    if (ctx->lkey_max >= (1 << 24) || T.R > 65535) ctx->small_path = false;   // locality keys are exact floats, residue ranks 16 bit there
+    if (T.R > 65535) ctx->small_path = false;   // residue ranks are 16 bit there
     B.max_cells = (int)want_cells;
     B.cell16 = ctx->small_path ? 1 : 0;     // n_pair < 65 536 there by a wide margin; the large path keeps 32-bit starts
     const size_t cell_bytes = B.cell16 ? 2 : 4;
@@ -184,8 +185,15 @@ static int plan(chc_ctx* ctx, size_t cells_cap = 49152) {
             queues_placed = true;
         }
     } else {
-        L.off_rec = L.off_cells = L.off_lkey = L.off_bits = L.off_exy = L.off_ez = L.off_ek = L.off_sw = L.off_sres = 0;
+        L.off_rec = L.off_cells = L.off_lkey = L.off_bits = L.off_sres = 0;
         L.off_plkf = L.off_pres = L.off_pst = 0;
+        // the slot-pair arrays of the large path live in a per-CTA slice of a global scratch (L2 / L1), offsets from its start
+        size_t g = 0;
+        L.off_exy = (int)g; g += al16(16 * e_pairs);
+        L.off_ez = (int)g;  g += al16(16 * e_pairs);
+        L.off_sw = (int)g;  g += al16(4 * 2 * e_pairs);
+        L.off_ek = (int)g;  g += partner_bytes;
+        L.soa_stride = (long long)((g + 127) & ~size_t(127));
         if ((ctx->n_pairs + 23) / 24 > 0x7fffffff) return CHC_E_TOO_LARGE;
         L.bits_words = (int)((ctx->n_pairs + 23) / 24);
     }
@@ -249,7 +257,7 @@ extern "C" void chc_destroy(chc_ctx* ctx) {
     if (ctx->counts_owned) cudaFree(ctx->counts);
     cudaFree(ctx->contacts); cudaFree(ctx->contact_n); cudaFree(ctx->near); cudaFree(ctx->near_n);
     cudaFree(ctx->hpmask); cudaFree(ctx->binned); cudaFree(ctx->gstamp); cudaFree(ctx->gstate);
-    cudaFree(ctx->wscratch); cudaFree(ctx->status); cudaFree(ctx->open_idx);
+    cudaFree(ctx->wscratch); cudaFree(ctx->status); cudaFree(ctx->open_idx); cudaFree(ctx->gsoa);
     for (int k = 0; k < 2; ++k) {
         cudaFree(ctx->dev_stage[k]); if (ctx->pin_stage[k]) cudaFreeHost(ctx->pin_stage[k]);
         if (ctx->stage_done[k]) cudaEventDestroy(ctx->stage_done[k]);
@@ -444,7 +452,10 @@ extern "C" int chc_create(chc_ctx** out, const chc_topology* t, const chc_params
         size_t ints = (size_t)ctx->pair_grid * (size_t)T.n_solv * (3 + WADJ);
         CK(cudaMalloc(&ctx->wscratch, ints * 4)); CK(cudaMemset(ctx->wscratch, 0, ints * 4));
     }
+    if (ctx->lkey_max >= (1 << 24))
+        return fail(ctx, CHC_E_TOO_LARGE, "residue ids span more than 2^24 (locality keys are carried as exact floats)");
     if (!ctx->small_path) {
+        CK(cudaMalloc(&ctx->gsoa, (size_t)ctx->pair_grid * (size_t)ctx->L.soa_stride));
         size_t words = (size_t)ctx->pair_grid * (size_t)ctx->L.bits_words;
         CK(cudaMalloc(&ctx->gstamp, words * 4)); CK(cudaMemset(ctx->gstamp, 0, words * 4));
         CK(cudaMalloc(&ctx->gstate, (size_t)ctx->pair_grid * 4)); CK(cudaMemset(ctx->gstate, 0, (size_t)ctx->pair_grid * 4));
@@ -592,7 +603,7 @@ static int submit_impl(chc_ctx* ctx, int state, const float* d_xyz, const long l
             if (ctx->timing) CK(cudaEventRecord(ev.b, stream));
             int nn = n; long long fi = fi0, fr0 = frag0, fs = frame_stride; int ff = F;
             unsigned* gs = nullptr; unsigned* gt = nullptr;
-            void* args[] = {&ctx->T, &ctx->P, &O, &ctx->LF, &ctx->B, &ctx->binned, &nn, &fi, &ff, &fr0, &ctx->hpmask, &gs, &gt, &ctx->wscratch, &x, &fs};
+            void* args[] = {&ctx->T, &ctx->P, &O, &ctx->LF, &ctx->B, &ctx->binned, &nn, &fi, &ff, &fr0, &ctx->hpmask, &gs, &gt, &ctx->wscratch, &x, &fs, &ctx->gsoa};
             CK(cudaLaunchKernel(pair_kernel_fn(true, ctx->P.track_near != 0 || ctx->P.emit != 0, true), dim3(std::min(n, ctx->pair_grid)), dim3(PAIR_THREADS),
                                 args, ctx->LF.total, stream));
             ctx->st.kernel_launches++;
@@ -614,7 +625,7 @@ static int submit_impl(chc_ctx* ctx, int state, const float* d_xyz, const long l
             const int grid = std::min(n, ctx->pair_grid);
             int nn = n; long long fi = fi0, fr0 = frag0, fs = frame_stride; int ff = F;
             unsigned* gs = ctx->small_path ? nullptr : ctx->gstamp; unsigned* gt = ctx->small_path ? nullptr : ctx->gstate;
-            void* args[] = {&ctx->T, &ctx->P, &O, &ctx->L, &ctx->B, &ctx->binned, &nn, &fi, &ff, &fr0, &ctx->hpmask, &gs, &gt, &ctx->wscratch, &x, &fs};
+            void* args[] = {&ctx->T, &ctx->P, &O, &ctx->L, &ctx->B, &ctx->binned, &nn, &fi, &ff, &fr0, &ctx->hpmask, &gs, &gt, &ctx->wscratch, &x, &fs, &ctx->gsoa};
             CK(cudaLaunchKernel(pair_kernel_fn(ctx->small_path, ctx->P.track_near != 0 || ctx->P.emit != 0), dim3(grid), dim3(PAIR_THREADS), args, ctx->L.total, stream));
             ctx->st.kernel_launches++;
         }

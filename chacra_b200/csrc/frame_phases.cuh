@@ -2,29 +2,25 @@
 #pragma once
 #include "frame_kernel.cuh"
 
-// Per-CTA view of the current frame.  SOA = the shared-memory path: the sorted atoms live as slot pairs (x0 x1 y0 y1 | z0 z1) plus
-// per-slot words (flags | pair index, filter key with the locality key, residue rank); otherwise the binned record is read in
-// place (float4 per slot) and the locality key / residue rank come from the global tables by pair index.
-template <bool SOA>
+// Per-CTA view of the current frame.  The sorted atoms live as slot pairs (x0 x1 y0 y1 | z0 z1 lkey0 lkey1, locality key as an
+// exact float) plus one flag word per slot: in shared memory on the small path, in a per-CTA global scratch (L2) on the large
+// one.  TAB = the by-pair-index tables (residue rank, static bits) are in shared memory too (small path); otherwise they are
+// read from the global topology tables.
+template <bool TAB>
 struct FrameCtxT {
-    const float4* spos;      // !SOA: cell-sorted pair atoms: x, y, z, (dynamic flags | pair_index << I_PIDX_SHIFT)
-    const int* lkey;         // !SOA: locality key by pair index
-    const float4* exy; const float4* ezk; const unsigned* sw;   // SOA: x0 x1 y0 y1 | z0 z1 lkey0 lkey1 (floats) | flags, pair index
-    const unsigned short* pres; const unsigned char* pst;       // SOA, by pair index: residue rank; static bits (I_LIG .. I_PBOND) >> 14
+    const float4* exy; const float4* ezk; const unsigned* sw;   // x0 x1 y0 y1 | z0 z1 lkey0 lkey1 (floats) | flags, pair index
+    const unsigned short* pres; const unsigned char* pst;       // TAB, by pair index: residue rank; static bits (I_LIG .. I_PBOND) >> 14
     __device__ __forceinline__ float4 at(int j) const {
-        if (SOA) {
-            const float4 a = exy[j >> 1]; const float4 b = ezk[j >> 1];
-            const float w = __uint_as_float(sw[j]);
-            return (j & 1) ? make_float4(a.y, a.w, b.y, w) : make_float4(a.x, a.z, b.x, w);
-        }
-        return spos[j];
+        const float4 a = exy[j >> 1]; const float4 b = ezk[j >> 1];
+        const float w = __uint_as_float(sw[j]);
+        return (j & 1) ? make_float4(a.y, a.w, b.y, w) : make_float4(a.x, a.z, b.x, w);
     }
-    __device__ __forceinline__ int lk(int j, unsigned w) const {
-        if (SOA) { const float4 b = ezk[j >> 1]; return (int)((j & 1) ? b.w : b.z); }      // exact: locality keys are below 2^24 here
-        return lkey[w >> I_PIDX_SHIFT];
+    __device__ __forceinline__ int lk(int j, unsigned) const {
+        const float4 b = ezk[j >> 1];
+        return (int)((j & 1) ? b.w : b.z);              // exact: locality keys are below 2^24 (checked by chc_create)
     }
-    __device__ __forceinline__ int res(const DevTopo& T, int pidx) const { return SOA ? (int)pres[pidx] : T.pair_res[pidx]; }
-    __device__ __forceinline__ unsigned sinfo(const DevTopo& T, int pidx) const { return SOA ? ((unsigned)pst[pidx] << 14) : T.pair_info[pidx]; }
+    __device__ __forceinline__ int res(const DevTopo& T, int pidx) const { return TAB ? (int)pres[pidx] : T.pair_res[pidx]; }
+    __device__ __forceinline__ unsigned sinfo(const DevTopo& T, int pidx) const { return TAB ? ((unsigned)pst[pidx] << 14) : T.pair_info[pidx]; }
     const float* aux;        // [NA][3] donor hydrogens, ring atoms, cations
     unsigned* bits;          // residue-pair set of this frame
     unsigned gen;            // 0: plain bitset; 1..255: generation of the stamped bitset
@@ -161,18 +157,6 @@ __device__ __forceinline__ void ring_stack_task(const DevTopo& T, const DevParam
                          sqrtf(dist2_exact(q1[0], q1[1], q1[2], q2[0], q2[1], q2[2])));
         }
     }
-}
-
-// ---- F: can this pair get any class at all?  A cheap SUFFICIENT test for e2_classify(...) == 0 (every class below needs
-// one of the things tested here): vdW / hydrophobic / their near-cutoff reports need dl >= vdw_res_diff; a salt bridge
-// needs an anion and a cation; a hydrogen bond needs both atoms in the hydrogen-bond selection; a water edge needs
-// exactly one solvent atom.
-template <class FrameCtx>
-__device__ __forceinline__ bool e2_may_classify(const DevParams& P, const FrameCtx& F, unsigned wi, unsigned wj) {
-    const bool polar = (((wi & I_ANION) && (wj & I_CATION)) || ((wj & I_ANION) && (wi & I_CATION))) || (wi & wj & I_HBU) ||
-                       ((wi ^ wj) & I_SOLV);
-    const int dl = abs(F.lkey[wi >> I_PIDX_SHIFT] - F.lkey[wj >> I_PIDX_SHIFT]);
-    return polar || dl >= P.vdw_rd;
 }
 
 // ---- E2: exact float32 d2 and class tests for one prefilter survivor ---------------------------------------

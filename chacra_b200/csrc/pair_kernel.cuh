@@ -18,11 +18,8 @@
 #include "frame_phases.cuh"
 #include "water_phase.cuh"
 
-#ifndef Q1_CAP
-#define Q1_CAP 128          // (i, j) survivors per warp (>= 64: see the flush in E1; 128 measured 1.2 % faster than 96, 160+ no better)
-#endif
-#ifndef QF_CAP
-#define QF_CAP 128          // survivors that passed the cheap filter, per warp (>= E1_TARGET + 32: see the flush in E1)
+#ifndef QE_CAP
+#define QE_CAP 64           // E1 -> E2 entries per warp: E1 runs while fewer than 32 are queued and adds at most 32
 #endif
 #ifndef Q2_CAP
 #define Q2_CAP 64           // classified pairs per warp and queue (plain, polar)
@@ -30,7 +27,7 @@
 #ifndef E1_TARGET
 #define E1_TARGET 32        // E1 runs until this many survivors are queued (one F batch)
 #endif
-static_assert(Q1_CAP - E1_TARGET >= 32 && QF_CAP - E1_TARGET >= 32 && E1_TARGET >= 32, "a lane's 32 pending hits must fit behind E1_TARGET queued survivors");
+static_assert(QE_CAP - E1_TARGET >= 32 && E1_TARGET >= 32, "one entry per lane must fit behind E1_TARGET queued entries");
 #ifndef E1_UNROLL
 #define E1_UNROLL 4
 #endif
@@ -48,7 +45,8 @@ struct PairLayout {         // shared-memory plan of the pair kernel (bytes)
     int off_exy, off_ez, off_ek, off_sw, off_sres;      // off_ez: float4 z0 z1 lkey0 lkey1 per slot pair; off_ek: partner bit arrays
     int off_plkf, off_pres, off_pst;                    // SMALL, by pair index (loaded once per launch): locality key (float), residue rank, static bits
     int off_rc, off_rlist, rlist_cap;
-    int off_aux, off_cnt;                               // FUSED: aux atoms copied out of the frame; transient cell counters                   // ring centroids (float[3 n_rings]) and the ring tasks that passed the prefilter
+    int off_aux, off_cnt;                               // FUSED: aux atoms copied out of the frame; transient cell counters
+    long long soa_stride;                               // !SMALL: bytes of one CTA's slot-pair arrays in the global scratch (off_exy .. count from its start)                   // ring centroids (float[3 n_rings]) and the ring tasks that passed the prefilter
     int bits_words;         // words of the residue-pair set (plain: P/32, stamped: P/24)
     int total;
 };
@@ -61,8 +59,7 @@ __device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 r; asm("mul.rn.f
 __device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
 
 // The cheap SUFFICIENT test for "no class" (most close pairs sit in the same or adjacent residues and only matter when both atoms
-// are polar; e2_may_classify in frame_phases.cuh states it for the in-place path) runs inside the E1 loop on the shared-memory
-// path: the locality key rides along as a float next to z, sign(dl^2 - (vdw_res_diff - 1/2)^2) marks a LOCAL neighbour, and
+// are polar) runs inside the E1 loop: the locality key rides along as a float next to z, sign(dl^2 - (vdw_res_diff - 1/2)^2) marks a LOCAL neighbour, and
 // "polar partner" comes from a bit per slot: partner set c of a lane = (c & 1 ? hydrogen-bond selection : 0) | (c & 2 ? cations : 0)
 // | (c & 4 ? anions : 0) | solvent, set 8 = everything but solvent (for a solvent atom): 9 bit arrays over the sorted slots.
 #define E1_PAD_PAIRS 20        // slot pairs past the last atom that the unmasked E1 loads may touch
@@ -100,7 +97,7 @@ __global__ void __launch_bounds__(THREADS, 1)
 pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, const unsigned char* __restrict__ binned,
                    int n_frames, long long first_index, int frag_frames, long long frag0,
                    const unsigned char* __restrict__ hpmask, unsigned* __restrict__ gstamp, unsigned* __restrict__ gstate,
-                   int* __restrict__ wscratch, const float* __restrict__ xyz, long long frame_stride) {
+                   int* __restrict__ wscratch, const float* __restrict__ xyz, long long frame_stride, unsigned char* __restrict__ gsoa) {
     static_assert(!FUSED || SMALL, "the in-kernel sort feeds the shared-memory path");
     extern __shared__ __align__(128) unsigned char smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -110,9 +107,17 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
     // queue entries: the pair (i, j) of sorted slots is one word on the shared-memory path (slots < 65 536), two otherwise
     constexpr int QW = SMALL ? 1 : 2;
     using cell_t = typename std::conditional<SMALL, unsigned short, int>::type;     // BinLayout::cell16 <=> SMALL
-    unsigned* q1 = reinterpret_cast<unsigned*>(smem + L.off_q1) + (SMALL ? 0 : warp * (QW * Q1_CAP));   // survivors (in-place path only)
-    unsigned* qf = reinterpret_cast<unsigned*>(smem + L.off_qf) + warp * (QW * QF_CAP);            // filtered survivors
-    uint2* qe = reinterpret_cast<uint2*>(smem + L.off_qf) + warp * (QF_CAP / 2);                  // SMALL: (atom | first slot << 16, survivor mask) entries
+    // E1 -> E2 entries (atom slot, first neighbour slot, survivor mask): 8 bytes on the shared-memory path, 16 otherwise
+    uint2* qe = reinterpret_cast<uint2*>(smem + L.off_qf) + warp * QE_CAP;
+    uint4* qe4 = reinterpret_cast<uint4*>(smem + L.off_qf) + warp * QE_CAP;
+    auto ent_put = [&](int at, unsigned i, unsigned first, unsigned m) {
+        if (SMALL) qe[at] = make_uint2(i | (first << 16), m); else qe4[at] = make_uint4(i, first, m, 0u);
+    };
+    auto ent_get = [&](int at, unsigned& i, unsigned& first, unsigned& m) {
+        if (SMALL) { const uint2 e = qe[at]; i = e.x & 0xffffu; first = e.x >> 16; m = e.y; }
+        else { const uint4 e = qe4[at]; i = e.x; first = e.y; m = e.z; }
+    };
+    auto ent_mask = [&](int at, unsigned m) { if (SMALL) qe[at].y = m; else qe4[at].z = m; };
     unsigned* q2 = reinterpret_cast<unsigned*>(smem + L.off_q2) + warp * (2 * (QW + 1) * Q2_CAP);  // plain | polar: pair, class
     auto qput = [](unsigned* q, int cap, int at, unsigned i, unsigned j) {
         if (SMALL) q[at] = i | (j << 16); else { q[at] = i; q[cap + at] = j; }
@@ -397,12 +402,14 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                 else if (at < L.rlist_cap) rlist[L.rlist_cap - 1 - at] = (unsigned)(t - n_pc);
             }
         }
-        float4* exy = reinterpret_cast<float4*>(smem + L.off_exy);
-        float4* ezk = reinterpret_cast<float4*>(smem + L.off_ez);
-        unsigned* partner = reinterpret_cast<unsigned*>(smem + L.off_ek);      // [E1_PARTNER_SETS][pwords] bit per sorted slot
+        // the slot-pair arrays: shared memory (small path) or this CTA's slice of the global scratch (large path: L2 / L1)
+        unsigned char* soa = SMALL ? smem : gsoa + (size_t)blockIdx.x * (size_t)L.soa_stride;
+        float4* exy = reinterpret_cast<float4*>(soa + L.off_exy);
+        float4* ezk = reinterpret_cast<float4*>(soa + L.off_ez);
+        unsigned* partner = reinterpret_cast<unsigned*>(soa + L.off_ek);      // [E1_PARTNER_SETS][pwords] bit per sorted slot
         const int pwords = ((T.n_pair + 2 * E1_PAD_PAIRS + 31) >> 5) + 2;
-        unsigned* sw = reinterpret_cast<unsigned*>(smem + L.off_sw);
-        if (SMALL) {
+        unsigned* sw = reinterpret_cast<unsigned*>(soa + L.off_sw);
+        {
             // The float4 image becomes slot PAIRS (E1 tests two neighbours per packed instruction): x0 x1 y0 y1 | z0 z1 lkey0 lkey1,
             // plus the flag word per slot.
             const int NPs = T.n_pair, np2 = (NPs + 1) >> 1;
@@ -413,7 +420,9 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                 exy[q] = make_float4(a.x, b.x, a.y, b.y);
                 const unsigned wa = __float_as_uint(a.w), wb = __float_as_uint(b.w);
                 const int pa = wa >> I_PIDX_SHIFT, pb = wb >> I_PIDX_SHIFT;
-                ezk[q] = make_float4(a.z, b.z, j0 < NPs ? p_lkf[pa] : -3.0e7f, j1 < NPs ? p_lkf[pb] : -3.0e7f);
+                const float la = j0 < NPs ? (SMALL ? p_lkf[pa] : (float)__ldg(&T.pair_lkey[pa])) : -3.0e7f;
+                const float lb = j1 < NPs ? (SMALL ? p_lkf[pb] : (float)__ldg(&T.pair_lkey[pb])) : -3.0e7f;
+                ezk[q] = make_float4(a.z, b.z, la, lb);
                 sw[j0] = wa; sw[j1] = wb;
             }
             for (int wd = warp; wd < pwords; wd += THREADS / 32) {        // partner bits, one word of 32 slots per warp round
@@ -424,15 +433,15 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
                 if (lane < E1_PARTNER_SETS)
                     partner[lane * pwords + wd] = lane == 8 ? ~solv : (((lane & 1) ? hbu : 0u) | ((lane & 2) ? cat : 0u) | ((lane & 4) ? an : 0u) | solv);
             }
-            __syncthreads();               // from here on the float4 image is dead: its shared memory holds the (empty) queues
-        } else if (n_pc + n_st > 0) __syncthreads();     // the ring list is complete before any warp reaches the ring phase
+            __syncthreads();               // small path: from here on the float4 image is dead, its shared memory holds the (empty) queues
+        }
         const int px = hdr->nc[0] + 2, pxy = px * (hdr->nc[1] + 2), ncell = hdr->ncell;
-        FrameCtxT<SMALL> F{spos, T.pair_lkey, exy, ezk, sw, p_res, p_st, aux, bits, gen, tv, th,
+        FrameCtxT<SMALL> F{exy, ezk, sw, p_res, p_st, aux, bits, gen, tv, th,
                            hpmask + (size_t)(gidx / frag_frames - frag0) * T.n_pair, (int)gidx,
                            water_scratch(wscratch, blockIdx.x, T.n_solv), &M->nmark};
         // ---- E: pair interactions ------------------------------------------------------------------------------
         const float cut2p = P.pre2 * 1.000002f;       // largest cutoff^2 of the enabled pair types, padded for the fused filter
-        int q1n = 0, qfn = 0, q2n = 0, q3n = 0;
+        int qfn = 0, q2n = 0, q3n = 0;            // entries queued for E2; classified pairs queued for E3 (plain, polar)
         // E1 state.  A tile = 32 consecutive cell-sorted atoms of grid A, one per lane (atom i).  Lane ranges:
         // 0..4 = half shell of grid A (own row from the slot after i to the end of cell x+1, then rows (y+1,z) (y-1,z+1)
         // (y,z+1) (y+1,z+1) from x-1 to x+1); 5..13 (only with unselected solvent) = the full 3x3 rows of grid B.
@@ -440,20 +449,19 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
         const int nr = T.n_pair_a < T.n_pair ? 14 : 5;
         const unsigned nr_magic = 0xffffffffu / (unsigned)nr + 1u;
         const int ntiles = (nA + 31) >> 5;
-        const int nunits = ntiles * nr;
         const int n_whole = max(ntiles - E1_TAIL_TILES, 0), nunits_s = n_whole + (ntiles - n_whole) * nr;   // SMALL: unit numbering
         bool whole = false;
         int r = 0, tile = -1, k0 = 0, maxlen = 0;      // warp-uniform: current range and tile, chunk offset, longest lane range
         int my_i = -1, my_c = 0, beg = 0, len = 0;     // this lane's atom, its cell, its current range
         float ix = 0.f, iy = 0.f, iz = 0.f;
-        unsigned mask = 0u; int mbase = 0;             // this lane's hits of the last chunk not yet queued: j = mbase + bit
+        int mbase = 0;                                 // first slot of the chunk this lane tests: neighbour j = mbase + bit
         bool exhausted = false;
         // SMALL: this lane's locality key (float) and partner bit array; lead = its range starts on an odd slot
         float my_lk = 0.f; const unsigned* my_partner = partner; int lead = 0;
         const float loc_thr = P.vdw_rd > 0 ? -((float)P.vdw_rd - 0.5f) * ((float)P.vdw_rd - 0.5f) : 1.0f;   // dl^2 + loc_thr < 0 <=> |dl| < vdw_res_diff
         for (;;) {
             // ---- E1 ----
-            if (SMALL) {
+            {
                 // Slot pairs, packed float32 arithmetic; distance AND locality / polar-partner filter in one pass; the survivor masks
                 // go to the warp's entry queue (qfn = entries queued; 32 entries hold at least one E2 batch).
                 while (qfn < E1_TARGET && !exhausted) {
@@ -540,124 +548,25 @@ CHC_UNROLL(E1_UNROLL)
                     // and at most 32 entries are added: QE_CAP = 64 always holds them.
                     const unsigned surv = hits & (~local | part) & valid;
                     const unsigned bal = __ballot_sync(FULL, surv != 0u);
-                    if (surv) qe[qfn + __popc(bal & ((1u << lane) - 1u))] = make_uint2((unsigned)my_i | ((unsigned)mbase << 16), surv);
+                    if (surv) ent_put(qfn + __popc(bal & ((1u << lane) - 1u)), (unsigned)my_i, (unsigned)mbase, surv);
                     qfn += __popc(bal);
                 }
                 if (qfn == 0 && q2n == 0 && q3n == 0) break;           // only reachable when exhausted
                 __syncwarp();
-            } else {
-                while (q1n < E1_TARGET && !exhausted) {
-                    if (__any_sync(FULL, mask != 0u)) {
-                        // queue the pending hits, whole lanes at a time, as far as the queue has room (q1n < 32 here and a
-                        // lane holds at most 32 hits, so the first pending lane always fits: Q1_CAP - 32 >= 32)
-                        const int cnt = __popc(mask);
-                        int incl = cnt;
-#pragma unroll
-                        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += t; }
-                        const bool ok = incl <= Q1_CAP - q1n;
-                        if (ok) {
-                            int at = q1n + incl - cnt;
-                            unsigned m = mask;
-                            while (m) {
-                                const int k = __ffs(m) - 1;
-                                m &= m - 1u;
-                                qput(q1, Q1_CAP, at, (unsigned)my_i, (unsigned)(mbase + k));
-                                ++at;
-                            }
-                            mask = 0u;
-                        }
-                        q1n += __reduce_max_sync(FULL, ok ? incl : 0);
-                        continue;
-                    }
-                    k0 += 32;
-                    if (k0 >= maxlen) {                    // next unit of work = (tile, range); fine grain keeps the frame's tail short
-                        int u = 0;
-                        if (lane == 0) u = atomicAdd(&M->cursor, 1);
-                        u = __shfl_sync(FULL, u, 0);
-                        if (u >= nunits) { exhausted = true; break; }
-                        const int t = (int)__umulhi((unsigned)u, nr_magic);         // u / nr (u < 2^16: exact with the rounded-up reciprocal)
-                        r = u - t * nr;
-                        if (t != tile) {
-                            tile = t;
-                            my_i = t * 32 + lane;
-                            if (my_i < nA) {
-                                const float4 p = spos[my_i];
-                                ix = p.x; iy = p.y; iz = p.z;
-                                my_c = (cell_of(iz, hdr->org[2], hdr->inv, hdr->nc[2]) + 1) * pxy +
-                                       (cell_of(iy, hdr->org[1], hdr->inv, hdr->nc[1]) + 1) * px +
-                                       cell_of(ix, hdr->org[0], hdr->inv, hdr->nc[0]) + 1;
-                            } else my_i = -1;
-                        }
-                        len = 0;
-                        if (my_i >= 0) {
-                            if (r == 0) { beg = my_i + 1; len = (int)cells[my_c + 2] - beg; }
-                            else {
-                                int base;
-                                if (r < 5) base = my_c + ((r == 1 || r == 4) - (r == 2)) * px + (r >= 2 ? pxy : 0);
-                                else { const int q = r - 5; base = my_c + ncell + (q % 3 - 1) * px + (q / 3 - 1) * pxy; }
-                                beg = (int)cells[base - 1];
-                                len = (int)cells[base + 2] - beg;
-                            }
-                        }
-                        maxlen = __reduce_max_sync(FULL, len);
-                        k0 = 0;
-                        if (maxlen == 0) continue;
-                    }
-                    // 32 candidate slots of every lane's range, four at a time: fused-multiply-add d2 against the padded largest cutoff
-                    // (a superset filter: every class test in E2 compares the EXACT float32 d2 with its own cutoff).
-                    // Slots past the lane's own range are computed too (they lie inside the record: at most 35 slots after
-                    // the sorted atoms, where the aux atoms and the cell starts follow) and masked off afterwards.
-                    const int n = min(32, maxlen - k0);
-                    const int lim = len - k0;
-                    mbase = beg + k0;
-                    const float4* pj = spos + mbase;
-                    unsigned m = 0u;
-CHC_UNROLL(E1_UNROLL)
-                    for (int k4 = 0; k4 < n; k4 += 4) {
-                        const float4 a = pj[k4], b = pj[k4 + 1], c = pj[k4 + 2], d = pj[k4 + 3];
-                        const unsigned nib = (dist2_fused(ix, iy, iz, a.x, a.y, a.z) <= cut2p ? 1u : 0u) |
-                                             (dist2_fused(ix, iy, iz, b.x, b.y, b.z) <= cut2p ? 2u : 0u) |
-                                             (dist2_fused(ix, iy, iz, c.x, c.y, c.z) <= cut2p ? 4u : 0u) |
-                                             (dist2_fused(ix, iy, iz, d.x, d.y, d.z) <= cut2p ? 8u : 0u);
-                        m |= nib << k4;
-                    }
-                    m = lim >= 32 ? m : (lim > 0 ? m & ((1u << lim) - 1u) : 0u);
-                    mask = m;
-                }
-                if (q1n == 0 && qfn == 0 && q2n == 0 && q3n == 0) break;           // only reachable when exhausted
-                __syncwarp();
-                // ---- F: up to 32 survivors through the cheap sufficient test for "no class": most close pairs sit in the
-                //      same or adjacent residues and only matter when both atoms are polar ----
-                if (q1n > 0) {
-                    const int nb = min(q1n, 32);
-                    q1n -= nb;
-                    bool keep = false; unsigned ei = 0u, ej = 0u;
-                    if (lane < nb) {
-                        qget(q1, Q1_CAP, q1n + lane, ei, ej);
-                        keep = e2_may_classify(P, F, __float_as_uint(spos[ei].w), __float_as_uint(spos[ej].w));
-                    }
-                    const unsigned bal = __ballot_sync(FULL, keep);
-                    if (keep) {
-                        const int at = qfn + __popc(bal & ((1u << lane) - 1u));
-                        qput(qf, QF_CAP, at, ei, ej);
-                    }
-                    qfn += __popc(bal);
-                    __syncwarp();
-                }
             }
             // ---- E2: 32 filtered survivors; classified pairs go to the plain queue (vdW / hydrophobic only) or to the
             //      polar queue (salt bridge, hydrogen bond, water edge), so that an E3 batch runs one kind of code ----
-            const bool drain1 = exhausted && q1n == 0;
+            const bool drain1 = exhausted;
             if (qfn >= 32 || (drain1 && qfn > 0)) {
                 unsigned cls = 0u; float d2 = 0.f; unsigned ei = 0u, ej = 0u;
-                if (SMALL) {
+                {
                     // Deal out up to 32 survivors from the top entries of the queue (lane L looks at entry qfn - 1 - L): prefix sum
                     // of the entries' survivor counts, the entry of survivor s by binary search over the prefix sums, its bit by
                     // clearing the lower ones.  Entries used up leave the queue; the one cut by the batch keeps its unused bits.
                     const int nw = min(qfn, 32);
-                    uint2 ent = make_uint2(0u, 0u);
-                    if (lane < nw) ent = qe[qfn - 1 - lane];
-                    const int c = __popc(ent.y);
+                    unsigned ent_i = 0u, ent_first = 0u, ent_m = 0u;
+                    if (lane < nw) ent_get(qfn - 1 - lane, ent_i, ent_first, ent_m);
+                    const int c = __popc(ent_m);
                     int incl = c;
 #pragma unroll
                     for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += t; }
@@ -666,30 +575,25 @@ CHC_UNROLL(E1_UNROLL)
 #pragma unroll
                     for (int step = 16; step; step >>= 1) { const int v = __shfl_sync(FULL, incl, (e + step - 1) & 31); if (v <= lane) e += step; }
                     e &= 31;
-                    const unsigned im = __shfl_sync(FULL, ent.x, e), em = __shfl_sync(FULL, ent.y, e);
+                    const unsigned src_i = __shfl_sync(FULL, ent_i, e), src_first = __shfl_sync(FULL, ent_first, e), em = __shfl_sync(FULL, ent_m, e);
                     const int before = __shfl_sync(FULL, incl - c, e);
+                    unsigned bitpos = 0u;
                     if (lane < S) {
                         unsigned m = em;
                         for (int n = lane - before; n > 0; --n) m &= m - 1u;
-                        ei = im & 0xffffu; ej = (im >> 16) + (unsigned)(__ffs(m) - 1);
+                        bitpos = (unsigned)(__ffs(m) - 1);
+                        ei = src_i; ej = src_first + bitpos;
                     }
                     // the entry holding survivor S - 1 is the last one touched: keep what the batch did not use of it
                     const int lb = __shfl_sync(FULL, e, S - 1);
-                    const unsigned last = __shfl_sync(FULL, ej - (im >> 16), S - 1);     // bit of survivor S - 1 inside that entry
+                    const unsigned last = __shfl_sync(FULL, bitpos, S - 1);               // bit of survivor S - 1 inside that entry
                     int keep = 0;
                     if (lane == lb) {
-                        const unsigned m = ent.y & ~((2u << last) - 1u);
-                        if (m) { qe[qfn - 1 - lane].y = m; keep = 1; }
+                        const unsigned m = ent_m & ~((2u << last) - 1u);
+                        if (m) { ent_mask(qfn - 1 - lane, m); keep = 1; }
                     }
                     qfn -= lb + 1 - __shfl_sync(FULL, keep, lb);
                     if (lane < S) cls = e2_classify<TN>(T, P, F, (int)ei, (int)ej, d2);
-                } else {
-                    const int nb = min(qfn, 32);
-                    qfn -= nb;
-                    if (lane < nb) {
-                        qget(qf, QF_CAP, qfn + lane, ei, ej);
-                        cls = e2_classify<TN>(T, P, F, (int)ei, (int)ej, d2);
-                    }
                 }
                 const bool polar = (cls & (C_SB | C_HB | C_HBW | C_NEARS | C_NEARB)) != 0u;
                 const unsigned balp = __ballot_sync(FULL, polar), balv = __ballot_sync(FULL, cls != 0u && !polar);
