@@ -11,27 +11,25 @@ from collections import defaultdict
 CSRC = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "chacra_b200", "csrc")
 # (stage, file, start anchor, end anchor): from the first line containing `start` up to the line before the first later line containing `end`
 ANCHORS = [
-    ("prologue / frame setup", "pair_kernel.cuh", "pair_frames_kernel(DevTopo T", "if (SMALL) {\n            // The float4 image becomes"),
-    ("record -> slot pairs", "pair_kernel.cuh", "// The float4 image becomes slot PAIRS", "const int px = hdr->nc[0] + 2"),
+    ("prologue / frame setup", "pair_kernel.cuh", "pair_frames_kernel(DevTopo T", "// ---- R1: ring tasks (cation x ring"),
+    ("R1 ring prefilter", "pair_kernel.cuh", "// ---- R1: ring tasks (cation x ring", "// the slot-pair arrays: shared memory"),
+    ("record -> slot pairs, partner bits", "pair_kernel.cuh", "// the slot-pair arrays: shared memory", "const int px = hdr->nc[0] + 2"),
     ("E state setup", "pair_kernel.cuh", "const int px = hdr->nc[0] + 2", "// Slot pairs, packed float32 arithmetic"),
-    ("E1 flush (reserve + queue)", "pair_kernel.cuh", "// Slot pairs, packed float32 arithmetic", "k0 += 32;"),
+    ("E1 loop head", "pair_kernel.cuh", "// Slot pairs, packed float32 arithmetic", "k0 += 32;"),
     ("E1 unit grab / ranges", "pair_kernel.cuh", "k0 += 32;", "// up to 16 slot pairs of every lane"),
     ("E1 test loop + filter", "pair_kernel.cuh", "// up to 16 slot pairs of every lane", "// slot k of the chunk sits at bit"),
-    ("E1 masks / partner window", "pair_kernel.cuh", "// slot k of the chunk sits at bit", "if (qfn == 0 && q2n == 0 && q3n == 0) break;"),
-    ("in-place E1/F (unused on SMALL)", "pair_kernel.cuh", "if (qfn == 0 && q2n == 0 && q3n == 0) break;", "// ---- E2: 32 filtered survivors"),
+    ("E1 masks / partner window / entry", "pair_kernel.cuh", "// slot k of the chunk sits at bit", "// ---- E2: 32 filtered survivors"),
     ("E2 dispatch", "pair_kernel.cuh", "// ---- E2: 32 filtered survivors", "// ---- E3: 32 classified pairs"),
-    ("E3 dispatch", "pair_kernel.cuh", "// ---- E3: 32 classified pairs", "// ---- R: ring interactions"),
-    ("R ring dispatch", "pair_kernel.cuh", "// ---- R: ring interactions", "// ---- W: water bridges"),
+    ("E3 dispatch", "pair_kernel.cuh", "// ---- E3: 32 classified pairs", "// ---- R2: the listed ring tasks"),
+    ("R2 ring dispatch", "pair_kernel.cuh", "// ---- R2: the listed ring tasks", "// ---- W: water bridges"),
     ("end barrier / water", "pair_kernel.cuh", "// ---- W: water bridges", "\x00"),
     ("queue put/get lambdas", "pair_kernel.cuh", "auto qput = []", "for (int k = tid; k < T.K * T.K"),
     ("slot accessors (E2/E3)", "frame_phases.cuh", "struct FrameCtxT", "// ---- R: pi-cation"),
-    ("R ring tasks", "frame_phases.cuh", "// ---- R: pi-cation", "// ---- F: can this pair get any class"),
-    ("F (in-place path)", "frame_phases.cuh", "// ---- F: can this pair get any class", "// ---- E2: exact float32 d2"),
+    ("R2 ring tasks", "frame_phases.cuh", "// ---- R: pi-cation", "// ---- E2: exact float32 d2"),
     ("E2 classify", "frame_phases.cuh", "// ---- E2: exact float32 d2", "// does donor d see acceptor a"),
     ("E3 hb_direction", "frame_phases.cuh", "// does donor d see acceptor a", "// ---- E3: everything that needs"),
     ("E3 finish", "frame_phases.cuh", "// ---- E3: everything that needs", "\x00"),
     ("dist2_exact (E2/E3/R)", "device_types.cuh", "__device__ __forceinline__ float dist2_exact", "// superset prefilter only"),
-    ("in-place E1 test", "device_types.cuh", "// superset prefilter only", "__device__ __forceinline__ long long pair_index"),
     ("count_pair", "device_types.cuh", "__device__ __forceinline__ long long pair_index", "\x00"),
     ("mbarrier / bulk copy", "frame_kernel.cuh", "// ---- mbarrier + bulk async copy", "// grid coordinate of x along one axis"),
     ("cell_of", "frame_kernel.cuh", "__device__ __forceinline__ int cell_of", "// ---- output helpers"),

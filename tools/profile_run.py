@@ -15,6 +15,8 @@ def main():
     ap.add_argument("--copies", type=int, default=4)
     ap.add_argument("--no-rotate", action="store_true")
     ap.add_argument("--itypes", default=",".join(bench.ITYPES))
+    ap.add_argument("--emit", action="store_true", help="records mode: contact records are emitted (and dropped) -- the kernel the drop-in script runs")
+    ap.add_argument("--near", action="store_true", help="near-cutoff channel on")
     a = ap.parse_args()
     import torch
     from chacra_b200 import compile_topology
@@ -22,7 +24,7 @@ def main():
     from chacra_b200.synthetic import FrameGenerator
     path, atoms = bench.make_topology(a.copies)
     topo = compile_topology(atoms)
-    eng = ContactEngine(topo, a.itypes.split(","), n_states=1)
+    eng = ContactEngine(topo, a.itypes.split(","), n_states=1, emit_contacts=a.emit, track_near=a.near, contact_capacity=1 << 20, near_capacity=1 << 16)
     gen = FrameGenerator(atoms.xyz, 2000, device="cuda", rotate=not a.no_rotate)
     x = torch.cat([gen.frames(min(500, a.frames - b)) for b in range(0, a.frames, 500)])
     eng.set_timing(True)
