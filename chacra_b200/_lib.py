@@ -107,6 +107,7 @@ SYMBOLS = {
     "chc_tsv_counts_free": (None, [vp]),
     "chc_dcd_unpack": (C.c_int, [vp, C.c_int64, C.c_int64, C.c_int64, C.c_int32, C.c_int, vp, C.c_int64, C.c_int, vp]),
     "chc_permuted_pca": (C.c_int, [vp, C.c_int32, C.c_int32, C.c_int32, vp, vp, C.c_uint64, vp, vp, C.c_int, vp]),
+    "chc_permuted_pca_static": (C.c_int, [vp, C.c_int32, C.c_int32, C.c_int32, vp, vp, C.c_uint64, vp, C.c_int, vp]),
 }
 
 _lib = None

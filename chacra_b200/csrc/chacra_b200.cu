@@ -6,6 +6,7 @@
 #include <cmath>
 #include <vector>
 #include <algorithm>
+#include <mutex>
 #include "bin_kernel.cuh"
 #include "bin_tma_kernel.cuh"
 #include "pair_kernel.cuh"
@@ -875,6 +876,43 @@ extern "C" int chc_permuted_pca(const double* d_vals, int32_t n, int32_t p, int3
     void* args[] = {&xct, &n, &p, &n_perm, &pin, &pout, &sd, &S, &d_evr};
     if (cudaLaunchKernel(fn, dim3(grid), dim3(PCA_THREADS), args, S.total, stream) != cudaSuccess) return CHC_E_CUDA;
     return cudaGetLastError() == cudaSuccess ? CHC_OK : CHC_E_CUDA;
+}
+
+// ---- the same test for callers that must not allocate (no counterpart in the reference).
+// The centred table `xct` (the only scratch of the path) lives in a file-scope device array instead of a caller
+// buffer: CHC_PCA_STATIC_MAX_ELEMS float64 = 4 MiB held by every device that loads the library.  In host code the array's name
+// is only a stand-in; its device address is looked up once per device (with that device current) and handed to the kernels.
+// pca_center_kernel rewrites every element the permutation kernel reads, so nothing has to start at zero; all calls share the
+// array, so calls that overlap on the GPU (two streams, two threads) race.
+static __device__ __align__(256) double g_pca_static_xct[CHC_PCA_STATIC_MAX_ELEMS];
+static double* g_pca_static_ptr[64];
+static std::mutex g_pca_static_mu;
+
+extern "C" int chc_permuted_pca_static(const double* d_vals, int32_t n, int32_t p, int32_t n_perm, const uint8_t* d_perms_in,
+                                       uint8_t* d_perms_out, uint64_t seed, double* d_evr, int device, void* stream_) {
+    if (n_perm == 0) return CHC_OK;
+    if (!d_vals || !d_evr || n < 1 || n > PCA_MAXN || p < 1 || n_perm < 0 || device < 0 || device >= 64) return CHC_E_INVALID;
+    if ((int64_t)n * (int64_t)p > (int64_t)CHC_PCA_STATIC_MAX_ELEMS) {
+        fprintf(stderr, "chc_permuted_pca_static: n_samples*n_features = %lld exceeds CHC_PCA_STATIC_MAX_ELEMS = %lld; "
+                        "use chc_permuted_pca with a caller-owned work buffer\n", (long long)n * p, (long long)CHC_PCA_STATIC_MAX_ELEMS);
+        return CHC_E_TOO_LARGE;
+    }
+    if (cudaSetDevice(device) != cudaSuccess) return CHC_E_CUDA;
+    double* work = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_pca_static_mu);
+        if (!g_pca_static_ptr[device]) {
+            void* addr = nullptr;
+            const cudaError_t e = cudaGetSymbolAddress(&addr, g_pca_static_xct);
+            if (e != cudaSuccess || !addr) {
+                fprintf(stderr, "chc_permuted_pca_static: cudaGetSymbolAddress failed on device %d: %s\n", device, cudaGetErrorString(e));
+                return CHC_E_CUDA;
+            }
+            g_pca_static_ptr[device] = static_cast<double*>(addr);
+        }
+        work = g_pca_static_ptr[device];
+    }
+    return chc_permuted_pca(d_vals, n, p, n_perm, d_perms_in, d_perms_out, seed, work, d_evr, device, stream_);
 }
 
 extern "C" int chc_get_stats(chc_ctx* ctx, chc_stats* out) {

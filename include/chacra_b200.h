@@ -296,6 +296,18 @@ int chc_permuted_pca(const double* d_vals, int32_t n_samples, int32_t n_features
                      const uint8_t* d_perms_in, uint8_t* d_perms_out, uint64_t seed, double* d_work, double* d_evr,
                      int device, void* stream);
 
+/* The same permutation test for callers that cannot allocate device memory (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Identical to chc_permuted_pca except that the work table lives in a static device array inside the library
+ * (CHC_PCA_STATIC_MAX_ELEMS float64 = 4 MiB, held by every GPU that loads the library until exit) instead of d_work; the
+ * call performs no cudaMalloc / cudaFree.  n_samples * n_features > CHC_PCA_STATIC_MAX_ELEMS returns CHC_E_TOO_LARGE (and
+ * says so on stderr).  All calls on a device share the one array: calls that overlap on the GPU (different streams or
+ * threads) race; calls ordered on one stream are fine.  Results are bit-identical to chc_permuted_pca. */
+#define CHC_PCA_STATIC_MAX_ELEMS (1 << 19)
+int chc_permuted_pca_static(const double* d_vals, int32_t n_samples, int32_t n_features, int32_t n_perm,
+                            const uint8_t* d_perms_in, uint8_t* d_perms_out, uint64_t seed, double* d_evr,
+                            int device, void* stream);
+
 int chc_get_stats(chc_ctx* ctx, chc_stats* out);
 int chc_set_timing(chc_ctx* ctx, int on);
 
