@@ -561,7 +561,7 @@ CHC_UNROLL(E1_UNROLL)
                 unsigned cls = 0u; float d2 = 0.f; unsigned ei = 0u, ej = 0u;
                 {
                     // Deal out up to 32 survivors from the top entries of the queue (lane L looks at entry qfn - 1 - L): prefix sum
-                    // of the entries' survivor counts, the entry of survivor s by binary search over the prefix sums, its bit by
+                    // of the entries' survivor counts, the entry of survivor s from the entries' end marks (below), its bit by
                     // clearing the lower ones.  Entries used up leave the queue; the one cut by the batch keeps its unused bits.
                     const int nw = min(qfn, 32);
                     unsigned ent_i = 0u, ent_first = 0u, ent_m = 0u;
@@ -571,12 +571,13 @@ CHC_UNROLL(E1_UNROLL)
 #pragma unroll
                     for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += t; }
                     const int S = min(32, __shfl_sync(FULL, incl, 31));          // survivors in this batch
-                    int e = 0;                                                    // entries with incl <= lane  ==  the entry of survivor `lane`
-#pragma unroll
-                    for (int step = 16; step; step >>= 1) { const int v = __shfl_sync(FULL, incl, (e + step - 1) & 31); if (v <= lane) e += step; }
-                    e &= 31;
+                    // entry e ends with survivor incl_e - 1: the OR of those end marks over the warp tells every survivor how many
+                    // entries end before it (= its entry) and where its entry starts (one past the last end mark below it)
+                    const unsigned endm = __reduce_or_sync(FULL, (lane < nw && incl <= 32) ? 1u << (incl - 1) : 0u);
+                    const unsigned endb = endm & ((1u << lane) - 1u);
+                    const int e = __popc(endb) & 31;
+                    const int before = 32 - __clz(endb);
                     const unsigned src_i = __shfl_sync(FULL, ent_i, e), src_first = __shfl_sync(FULL, ent_first, e), em = __shfl_sync(FULL, ent_m, e);
-                    const int before = __shfl_sync(FULL, incl - c, e);
                     unsigned bitpos = 0u;
                     if (lane < S) {
                         unsigned m = em;
@@ -585,7 +586,7 @@ CHC_UNROLL(E1_UNROLL)
                         ei = src_i; ej = src_first + bitpos;
                     }
                     // the entry holding survivor S - 1 is the last one touched: keep what the batch did not use of it
-                    const int lb = __shfl_sync(FULL, e, S - 1);
+                    const int lb = __popc(endm & ((1u << (S - 1)) - 1u));
                     const unsigned last = __shfl_sync(FULL, bitpos, S - 1);               // bit of survivor S - 1 inside that entry
                     int keep = 0;
                     if (lane == lb) {
