@@ -472,6 +472,17 @@ def main():
                 "gpu_launches": int(launches), "clocks": clocks, "build_tag": build_tag, "parity": parity, "near": near,
                 "engine": {k: st[k] for k in ("path", "smem_bytes", "threads", "grid", "bin_smem_bytes", "bin_grid", "chunk_frames", "record_bytes",
                                               "bin_variant", "bin_apt")}}
+        if st.get("fused"):
+            # CHACRA_FUSED=1 (opt-in): the pair CTAs sort their own frames, there is no streaming kernel and no binned record; the
+            # binning kernel only sees the fragment-opening frames.  One roofline for the whole path.
+            path_ms = pair_ms + bin_ms
+            tf = traffic["fused_path_bytes_per_frame"] * frames_per_chunk if traffic and "fused_path_bytes_per_frame" in traffic and N == 6516 else None
+            line["roofline"].update({"achieved": bytes_per_launch / (path_ms * 1e-3) / 1e9, "frac": bytes_per_launch / (path_ms * 1e-3) / 1e9 / peak,
+                                     "traffic": tf, "traffic_source": "profiles/" + traffic["fused_source"] if tf else None,
+                                     "kernel": "pair_frames_kernel (fused: sorts its own frames) + bin_frames_kernel on fragment-opening frames",
+                                     "avg_launch_ms": path_ms, "kernel_share_of_step": (st["pair_ms_total"] + st["bin_ms_total"]) / ms})
+            line["roofline_stream"] = {"note": "fused path: no coordinate-streaming kernel, no binned record (see roofline.traffic)"}
+            line["engine"]["fused"] = 1
         line.update(extras)
         if world == 1 and not args.no_cpu_baseline:
             # the C++/OpenMP twin on ALL host cores, a bounded sample of the same workload (4 000 frames of state 0, >= 10 s)
