@@ -138,7 +138,7 @@ static int plan(chc_ctx* ctx, size_t cells_cap = 49152) {
     size_t q1b, qfb, q2b;
     const size_t queues = queue_bytes(true, &q1b, &qfb, &q2b);
     // ring phase: float centroids + the list of (cation, ring) / (ring, ring) tasks that pass the centroid prefilter
-    const size_t ring_bytes = 0;
+    const size_t ring_bytes = al16(12 * (size_t)std::max(T.n_rings, 1));
     const int rlist_cap = T.n_rings <= 128 ? 1024 : 8192;
     const size_t tables = 2 * al16(4 * (size_t)T.K * T.K) + al16(sizeof(PairMisc)) + ring_bytes + 4 * (size_t)rlist_cap;
     // ~3 cells per pair atom keeps the cells at the cutoff size for protein-like densities
@@ -209,6 +209,20 @@ static int plan(chc_ctx* ctx, size_t cells_cap = 49152) {
     L.off_rc = (int)off; off += ring_bytes;
     L.off_rlist = (int)off; off += 4 * (size_t)rlist_cap;
     L.rlist_cap = rlist_cap;
+    L.off_rgrid = L.off_rsort = 0;
+    // coarse grid over the ring centroids (pair_kernel.cuh R1) once the all-pairs prefilter would dominate a frame
+    const long long ring_tasks = (long long)T.n_cat * T.n_rings + (long long)T.n_rings * (T.n_rings - 1) / 2;
+    if (!ctx->small_path && T.n_rings <= 65535 && (ring_tasks > 200000 || getenv("CHACRA_RING_GRID")) && !getenv("CHACRA_RING_ALLPAIRS")) {
+        L.off_rgrid = (int)off; off += al16(4 * (size_t)(RG_CAP + 1));
+        L.off_rsort = (int)off; off += al16(2 * (size_t)std::max(T.n_rings, 1));
+    }
+    L.bits_plain = 0;
+    if (!ctx->small_path && ctx->n_pairs < (1ll << 31) && off + plain_bits + 1024 <= SMEM_LIMIT && !getenv("CHACRA_STAMPED_SET")) {
+        // mid-size systems: the plain per-frame residue-pair set fits in shared memory beside the queues (no stamped global set)
+        L.bits_plain = 1;
+        L.off_bits = (int)off; off += plain_bits;
+        L.bits_words = (int)((ctx->n_pairs + 31) / 32);
+    }
     L.total = (int)off;
     // ---- fused kernel: no landing zone for a record; queues in their own space; aux atoms copied out of the frame ----
     ctx->fused_ok = false;
@@ -233,7 +247,7 @@ static int plan(chc_ctx* ctx, size_t cells_cap = 49152) {
         G.off_tv = (int)o;    o += al16(4 * (size_t)T.K * T.K);
         G.off_th = (int)o;    o += al16(4 * (size_t)T.K * T.K);
         G.off_misc = (int)o;  o += al16(sizeof(PairMisc));
-        G.off_rc = (int)o;
+        G.off_rc = (int)o;    o += ring_bytes;
         G.off_rlist = (int)o; o += 4 * (size_t)rlist_cap;
         G.total = (int)o;
         ctx->fused_ok = (size_t)G.total <= SMEM_LIMIT;
@@ -244,7 +258,7 @@ static int plan(chc_ctx* ctx, size_t cells_cap = 49152) {
 }
 
 #ifndef CHC_BUILD_TAG
-#define CHC_BUILD_TAG "r02_v4"
+#define CHC_BUILD_TAG "r02_v5"
 #endif
 extern "C" int chc_abi_version(void) { return CHC_ABI_VERSION; }
 extern "C" const char* chc_build_tag(void) { return CHC_BUILD_TAG; }

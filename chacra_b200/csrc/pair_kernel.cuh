@@ -44,7 +44,9 @@ struct PairLayout {         // shared-memory plan of the pair kernel (bytes)
     // The float4 image the bulk copy lands (inside off_rec) is dead once these are built: the queues live there.
     int off_exy, off_ez, off_ek, off_sw, off_sres;      // off_ez: float4 z0 z1 lkey0 lkey1 per slot pair; off_ek: partner bit arrays
     int off_plkf, off_pres, off_pst;                    // SMALL, by pair index (loaded once per launch): locality key (float), residue rank, static bits
-    int off_rc, off_rlist, rlist_cap;
+    int off_rc, off_rlist, rlist_cap;                   // ring centroids (float[3 n_rings]); ring tasks that passed the prefilter
+    int off_rgrid, off_rsort;                           // !SMALL: coarse grid over the ring centroids (RG_CAP + 1 counters), ring ids sorted by its cells; 0 = none
+    int bits_plain;                                     // !SMALL: the residue-pair set is a plain bitset in shared memory (off_bits) as on the small path
     int off_aux, off_cnt;                               // FUSED: aux atoms copied out of the frame; transient cell counters
     long long soa_stride;                               // !SMALL: bytes of one CTA's slot-pair arrays in the global scratch (off_exy .. count from its start)                   // ring centroids (float[3 n_rings]) and the ring tasks that passed the prefilter
     int bits_words;         // words of the residue-pair set (plain: P/32, stamped: P/24)
@@ -71,6 +73,7 @@ __device__ __forceinline__ int e1_partner_set(unsigned w) {
     return (w & I_SOLV) ? 8 : (int)(((w >> 6) & 1u) | (((w >> 8) & 1u) << 1) | (((w >> 9) & 1u) << 2));   // hbu | anion -> wants cations | cation -> wants anions
 }
 
+#define RG_CAP 1024            // cells of the coarse ring grid (large path; shared memory there is taken from the L1 the slot arrays live in)
 struct PairMisc {
     unsigned long long bar;     // mbarrier of the bulk copies
     int cursor;                 // next tile of 32 sorted atoms
@@ -152,8 +155,11 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
             if (tid < 6) { M->bb_min[tid / 3][tid % 3] = 0x7fffffff; M->bb_max[tid / 3][tid % 3] = (int)0x80000000; }
         }
     } else {
-        bits = gstamp + (size_t)blockIdx.x * L.bits_words;
-        gen = gstate[blockIdx.x];          // generation carried across launches (0 on the first one)
+        if (L.bits_plain) bits = reinterpret_cast<unsigned*>(smem + L.off_bits);      // mid-size systems: the plain set fits beside the queues
+        else {
+            bits = gstamp + (size_t)blockIdx.x * L.bits_words;
+            gen = gstate[blockIdx.x];          // generation carried across launches (0 on the first one)
+        }
     }
     __syncthreads();
     unsigned phase = 0;
@@ -350,49 +356,139 @@ pair_frames_kernel(DevTopo T, DevParams P, DevOut O, PairLayout L, BinLayout B, 
             cells = reinterpret_cast<const cell_t*>(smem + L.off_cells);
         } else {
             if (tid == 0) { M->cursor = 0; M->ring_cursor = 0; M->nmark = 0; M->rn_pc = 0; M->rn_st = 0; }
-            gen = gen + 1u;
-            if (gen > 255u) {               // generations wrapped: wipe the table once per 255 frames
+            if (L.bits_plain) {
                 for (int w = tid; w < L.bits_words; w += THREADS) bits[w] = 0u;
-                gen = 1u;
+            } else {
+                gen = gen + 1u;
+                if (gen > 255u) {               // generations wrapped: wipe the table once per 255 frames
+                    for (int w = tid; w < L.bits_words; w += THREADS) bits[w] = 0u;
+                    gen = 1u;
+                }
             }
             hdr = reinterpret_cast<const BinHeader*>(rec);
             spos = reinterpret_cast<const float4*>(rec + B.off_spos);
             aux = reinterpret_cast<const float*>(rec + B.off_aux);
             cells = reinterpret_cast<const cell_t*>(rec + B.off_cells);
         }
+        // ring centroids (float) for the prefilter below, in the barrier interval that ends the frame set-up
+        float* rc = reinterpret_cast<float*>(smem + L.off_rc);
+        const int n_pc = (P.itypes & CHC_IT_PC) ? T.n_cat * T.n_rings : 0;
+        const int n_st = (P.itypes & (CHC_IT_PS | CHC_IT_TS)) ? T.n_rings * (T.n_rings - 1) / 2 : 0;
+        if (n_pc + n_st > 0)
+            for (int rr = tid; rr < T.n_rings; rr += THREADS) {
+                const int* t1 = T.ring_aux + 3 * rr;
+                float cx = 3.0e18f, cy = 0.f, cz = 0.f;                       // a ring without its three atoms takes part in nothing
+                if (t1[0] >= 0) {
+                    const float* p1 = aux + 3 * t1[0]; const float* p2 = aux + 3 * t1[1]; const float* p3 = aux + 3 * t1[2];
+                    cx = (p1[0] + p2[0] + p3[0]) * (1.0f / 3.0f); cy = (p1[1] + p2[1] + p3[1]) * (1.0f / 3.0f); cz = (p1[2] + p2[2] + p3[2]) * (1.0f / 3.0f);
+                }
+                rc[3 * rr] = cx; rc[3 * rr + 1] = cy; rc[3 * rr + 2] = cz;
+            }
         __syncthreads();
         // ---- R1: ring tasks (cation x ring, ring x ring) through a float prefilter on the ring centroids; the few that can reach
         //      a hard distance cutoff are listed and evaluated densely (float64) after the pair phase.  The prefilter radius is the
         //      largest hard cutoff + 0.05 A: a superset of what ring_pc_task / ring_stack_task accept or report as near-cutoff.
         //      Runs in the same barrier interval as the conversion below (both only read the record). ----
         unsigned* rlist = reinterpret_cast<unsigned*>(smem + L.off_rlist);
-        const int n_pc = (P.itypes & CHC_IT_PC) ? T.n_cat * T.n_rings : 0;
-        const int n_st = (P.itypes & (CHC_IT_PS | CHC_IT_TS)) ? T.n_rings * (T.n_rings - 1) / 2 : 0;
-        if (n_pc + n_st > 0) {
-            const unsigned nr_m = 0xffffffffu / (unsigned)max(T.n_rings, 1) + 1u;
-            auto centroid = [&](int rr, float& cx, float& cy, float& cz) {
-                const int* t1 = T.ring_aux + 3 * rr;
-                if (t1[0] < 0) return false;                                  // a ring without its three atoms takes part in nothing
-                const float* p1 = aux + 3 * t1[0]; const float* p2 = aux + 3 * t1[1]; const float* p3 = aux + 3 * t1[2];
-                cx = (p1[0] + p2[0] + p3[0]) * (1.0f / 3.0f); cy = (p1[1] + p2[1] + p3[1]) * (1.0f / 3.0f); cz = (p1[2] + p2[2] + p3[2]) * (1.0f / 3.0f);
-                return true;
+        if (!SMALL && L.off_rgrid > 0 && n_pc + n_st > 0) {
+            // Large systems: the all-pairs prefilter below is quadratic (config 4: 2.8 M (cation, ring) and (ring, ring) tasks per
+            // frame).  The ring centroids are binned into a coarse grid laid over the pair grid's box -- cells of k x k x k pair
+            // cells, k edges >= the prefilter radius, at most RG_CAP cells -- and every cation / ring looks at its 27 cells only.
+            unsigned* gcnt = reinterpret_cast<unsigned*>(smem + L.off_rgrid);
+            unsigned short* gring = reinterpret_cast<unsigned short*>(smem + L.off_rsort);
+            int k = max(1, (int)ceilf(sqrtf(P.ring_pre2) * hdr->inv * 1.001f + 0.01f));
+            int gx, gy, gz;
+            for (;; ++k) {
+                gx = (hdr->nc[0] + k - 1) / k; gy = (hdr->nc[1] + k - 1) / k; gz = (hdr->nc[2] + k - 1) / k;
+                if ((long long)gx * gy * gz <= RG_CAP) break;
+            }
+            const int gcells = gx * gy * gz;
+            const unsigned kmagic = 0xffffffffu / (unsigned)k + 1u;           // pair-cell index / k (indices < 2^16)
+            auto coarse = [&](float x, float y, float z, int& cx, int& cy, int& cz) {
+                cx = (int)__umulhi((unsigned)cell_of(x, hdr->org[0], hdr->inv, hdr->nc[0]), kmagic);
+                cy = (int)__umulhi((unsigned)cell_of(y, hdr->org[1], hdr->inv, hdr->nc[1]), kmagic);
+                cz = (int)__umulhi((unsigned)cell_of(z, hdr->org[2], hdr->inv, hdr->nc[2]), kmagic);
             };
+            for (int c = tid; c <= gcells; c += THREADS) gcnt[c] = 0u;
+            __syncthreads();
+            for (int rr = tid; rr < T.n_rings; rr += THREADS) {
+                if (rc[3 * rr] > 1.0e18f) continue;
+                int cx, cy, cz; coarse(rc[3 * rr], rc[3 * rr + 1], rc[3 * rr + 2], cx, cy, cz);
+                atomicAdd(&gcnt[(cz * gy + cy) * gx + cx], 1u);
+            }
+            __syncthreads();
+            {   // exclusive scan of the counts (thread t owns RG_CAP / THREADS consecutive cells)
+                constexpr int PER = (RG_CAP + THREADS - 1) / THREADS;
+                unsigned v[PER], sum = 0u;
+#pragma unroll
+                for (int q = 0; q < PER; ++q) { const int c = tid * PER + q; v[q] = c < gcells ? gcnt[c] : 0u; sum += v[q]; }
+                unsigned incl = sum;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += t; }
+                if (lane == 31) M->carry[warp] = (int)incl;
+                __syncthreads();
+                unsigned base = 0u;
+                for (int w = 0; w < warp; ++w) base += (unsigned)M->carry[w];
+                unsigned run = base + incl - sum;
+#pragma unroll
+                for (int q = 0; q < PER; ++q) { const int c = tid * PER + q; if (c < gcells) gcnt[c] = run; run += v[q]; }
+            }
+            __syncthreads();
+            // fill: the running start of a cell ends up as its END; cell c then spans [c ? gcnt[c - 1] : 0, gcnt[c])
+            for (int rr = tid; rr < T.n_rings; rr += THREADS) {
+                if (rc[3 * rr] > 1.0e18f) continue;
+                int cx, cy, cz; coarse(rc[3 * rr], rc[3 * rr + 1], rc[3 * rr + 2], cx, cy, cz);
+                gring[atomicAdd(&gcnt[(cz * gy + cy) * gx + cx], 1u)] = (unsigned short)rr;
+            }
+            __syncthreads();
+            const int n_cat_on = n_pc > 0 ? T.n_cat : 0, n_ring_on = n_st > 0 ? T.n_rings : 0;
+            for (int sidx = tid; sidx < n_cat_on + n_ring_on; sidx += THREADS) {
+                const bool pc = sidx < n_cat_on;
+                const int me = pc ? sidx : sidx - n_cat_on;
+                float ax, ay, az;
+                if (pc) { const float* xc = aux + 3 * T.cat_aux[me]; ax = xc[0]; ay = xc[1]; az = xc[2]; }
+                else { ax = rc[3 * me]; ay = rc[3 * me + 1]; az = rc[3 * me + 2]; if (ax > 1.0e18f) continue; }
+                const int excl = pc ? T.cat_excl[me] : -1;
+                int cx, cy, cz; coarse(ax, ay, az, cx, cy, cz);
+                const int x0 = max(cx - 1, 0), x1 = min(cx + 1, gx - 1);
+                for (int zz = max(cz - 1, 0); zz <= min(cz + 1, gz - 1); ++zz)
+                    for (int yy = max(cy - 1, 0); yy <= min(cy + 1, gy - 1); ++yy) {
+                        const int row = (zz * gy + yy) * gx;
+                        const int s0 = row + x0 > 0 ? (int)gcnt[row + x0 - 1] : 0, s1 = (int)gcnt[row + x1];
+                        for (int sl = s0; sl < s1; ++sl) {
+                            const int rr = (int)gring[sl];
+                            if (pc ? rr == excl : rr <= me) continue;
+                            const float dx = ax - rc[3 * rr], dy = ay - rc[3 * rr + 1], dz = az - rc[3 * rr + 2];
+                            if (!(dx * dx + dy * dy + dz * dz <= P.ring_pre2)) continue;
+                            const int at = atomicAdd(pc ? &M->rn_pc : &M->rn_st, 1);
+                            if (at < L.rlist_cap) {
+                                if (pc) rlist[at] = (unsigned)(me * T.n_rings + rr);
+                                else rlist[L.rlist_cap - 1 - at] = (unsigned)(rr * (rr - 1) / 2 + me);
+                            }
+                        }
+                    }
+            }
+        } else if (n_pc + n_st > 0) {
+            const unsigned nr_m = 0xffffffffu / (unsigned)max(T.n_rings, 1) + 1u;
             for (int t = tid; t < n_pc + n_st; t += THREADS) {
                 float ax, ay, az, bx, by, bz;
                 if (t < n_pc) {
                     int c = (int)__umulhi((unsigned)t, nr_m);
                     if (c * T.n_rings > t) --c;                               // rounded-up reciprocal: exact below 2^16, corrected above
                     const int rr = t - c * T.n_rings;
-                    if (T.cat_excl[c] == rr || !centroid(rr, bx, by, bz)) continue;
+                    if (T.cat_excl[c] == rr) continue;
                     const float* xc = aux + 3 * T.cat_aux[c];
                     ax = xc[0]; ay = xc[1]; az = xc[2];
+                    bx = rc[3 * rr]; by = rc[3 * rr + 1]; bz = rc[3 * rr + 2];
                 } else {
                     const int q = t - n_pc;
                     int r2 = (int)((1.0f + sqrtf(1.0f + 8.0f * (float)q)) * 0.5f);
                     while (r2 * (r2 - 1) / 2 > q) --r2;
                     while ((r2 + 1) * r2 / 2 <= q) ++r2;
                     const int r1 = q - r2 * (r2 - 1) / 2;
-                    if (T.ring_res[r1] == T.ring_res[r2] || !centroid(r1, ax, ay, az) || !centroid(r2, bx, by, bz)) continue;
+                    ax = rc[3 * r1]; ay = rc[3 * r1 + 1]; az = rc[3 * r1 + 2];
+                    bx = rc[3 * r2]; by = rc[3 * r2 + 1]; bz = rc[3 * r2 + 2];
+                    if (ax > 1.0e18f || bx > 1.0e18f) continue;
                 }
                 const float dx = ax - bx, dy = ay - by, dz = az - bz;
                 if (!(dx * dx + dy * dy + dz * dz <= P.ring_pre2)) continue;
@@ -666,5 +762,5 @@ CHC_UNROLL(E1_UNROLL)
             __syncthreads();
         }
     }
-    if (!SMALL && tid == 0) gstate[blockIdx.x] = gen;
+    if (!SMALL && !L.bits_plain && tid == 0) gstate[blockIdx.x] = gen;
 }

@@ -68,6 +68,7 @@ def test_stamped_pair_set_survives_generation_wrap(monkeypatch, oracle_5xnd):
     from chacra_b200 import read_pdb, compile_topology
     from chacra_b200.engine import ContactEngine
     monkeypatch.setenv("CHACRA_FORCE_LARGE", "1")
+    monkeypatch.setenv("CHACRA_STAMPED_SET", "1")          # mid-size systems would keep a plain set in shared memory
     monkeypatch.setenv("CHACRA_PAIR_GRID", "2")
     base = oracle_5xnd["frames"]
     topo = compile_topology(read_pdb(os.path.join(GOLDEN, "5xnd_topology.pdb")), base[0])

@@ -157,7 +157,8 @@ def test_tiny_and_odd_sized_systems(tmp_path, oracle_5xnd, first, last):
     frames = np.ascontiguousarray(oracle_5xnd["frames"][:, keep, :])
     res = o.run(top, top, ALL, frames=frames, collect_near=True)
     want, want_near = _oracle_sets(res)
-    for env in ({}, {"CHACRA_FORCE_LARGE": "1"}, {"CHACRA_BIN_VARIANT": "0"}, {"CHACRA_BIN_VARIANT": "4"}):
+    for env in ({}, {"CHACRA_FORCE_LARGE": "1"}, {"CHACRA_FORCE_LARGE": "1", "CHACRA_STAMPED_SET": "1", "CHACRA_RING_GRID": "1"}, {"CHACRA_BIN_VARIANT": "0"},
+                {"CHACRA_BIN_VARIANT": "4"}):
         os.environ.update(env)
         try:
             run = _engine_run(top, frames, ALL)
