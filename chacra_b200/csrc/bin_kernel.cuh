@@ -93,7 +93,10 @@ bin_frames_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__
         }
         const int px = nc[0] + 2, pxy = px * (nc[1] + 2), ncell = pxy * (nc[2] + 2);
         const int nkey = gridb ? 2 * ncell : ncell;
-        for (int c = tid; c < nkey; c += THREADS) cells[c] = 0;
+        // gather variant on systems below 65 536 pair atoms: two 16-bit counters per word (twice the cells in the same shared
+        // memory: the cells stay at the cutoff size for up to ~65 k pair atoms); no half can overflow, every value is <= n_pair
+        const bool pk = APT == 0 && B.count16 != 0;
+        for (int c = tid; c < (pk ? (nkey + 1) >> 1 : nkey); c += THREADS) cells[c] = 0;
         __syncthreads();
         // ---- 2: count ---------------------------------------------------------------------------------
         int r_cell[NR];
@@ -111,16 +114,18 @@ bin_frames_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__
                 const float* q = X + 3 * (size_t)T.pair_atom[p];
                 int c = (cell_of(q[2], org[2], inv, nc[2]) + 1) * pxy + (cell_of(q[1], org[1], inv, nc[1]) + 1) * px +
                         cell_of(q[0], org[0], inv, nc[0]) + 1 + (p >= T.n_pair_a ? ncell : 0);
-                atomicAdd(&cells[c], 1);
+                if (pk) atomicAdd(&cells[c >> 1], 1 << ((c & 1) << 4)); else atomicAdd(&cells[c], 1);
             }
         }
         __syncthreads();
         // ---- 3: exclusive scan over the cells --------------------------------------------------------------
         {
-            const int per = (nkey + THREADS - 1) / THREADS;
-            const int b = min(tid * per, nkey), e = min(b + per, nkey);
+            const int nscan = pk ? (nkey + 1) >> 1 : nkey;            // words to scan
+            const int per = (nscan + THREADS - 1) / THREADS;
+            const int b = min(tid * per, nscan), e = min(b + per, nscan);
             int s = 0;
-            for (int c = b; c < e; ++c) s += cells[c];
+            if (pk) for (int c = b; c < e; ++c) { const unsigned w = (unsigned)cells[c]; s += (int)((w & 0xffffu) + (w >> 16)); }
+            else for (int c = b; c < e; ++c) s += cells[c];
             int incl = s;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += t; }
@@ -134,7 +139,12 @@ bin_frames_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__
             }
             __syncthreads();
             int run = M.scan_carry[warp] + incl - s;
-            for (int c = b; c < e; ++c) { int v = cells[c]; cells[c] = run; run += v; }
+            if (pk) for (int c = b; c < e; ++c) {
+                const unsigned w = (unsigned)cells[c], lo2 = w & 0xffffu;
+                cells[c] = (int)((unsigned)run | (((unsigned)run + lo2) << 16));
+                run += (int)(lo2 + (w >> 16));
+            }
+            else for (int c = b; c < e; ++c) { int v = cells[c]; cells[c] = run; run += v; }
         }
         __syncthreads();
         // ---- 4: scatter (cells[c] becomes the END of cell c), aux atoms, header ----------------------------------
@@ -153,7 +163,9 @@ bin_frames_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__
                 const float x = q[0], y = q[1], z = q[2];
                 int c = (cell_of(z, org[2], inv, nc[2]) + 1) * pxy + (cell_of(y, org[1], inv, nc[1]) + 1) * px +
                         cell_of(x, org[0], inv, nc[0]) + 1 + (p >= T.n_pair_a ? ncell : 0);
-                int dst = atomicAdd(&cells[c], 1);
+                int dst;
+                if (pk) { const int sh = (c & 1) << 4; dst = (atomicAdd(&cells[c >> 1], 1 << sh) >> sh) & 0xffff; }
+                else dst = atomicAdd(&cells[c], 1);
                 spos[dst] = make_float4(x, y, z, __uint_as_float((T.pair_info[p] & I_WMASK) | ((unsigned)p << I_PIDX_SHIFT)));
             }
         }
@@ -170,7 +182,13 @@ bin_frames_kernel(DevTopo T, DevParams P, BinLayout B, const float* __restrict__
             if (B.cell16) reinterpret_cast<unsigned short*>(cells_out)[0] = 0; else cells_out[0] = 0;
         }
         __syncthreads();
-        if (B.cell16) for (int c = tid; c < nkey; c += THREADS) reinterpret_cast<unsigned short*>(cells_out)[c + 1] = (unsigned short)cells[c];
+        if (pk) {
+            for (int c = tid; c < nkey; c += THREADS) {
+                const int v = (int)(((unsigned)cells[c >> 1] >> ((c & 1) << 4)) & 0xffffu);
+                if (B.cell16) reinterpret_cast<unsigned short*>(cells_out)[c + 1] = (unsigned short)v; else cells_out[c + 1] = v;
+            }
+        }
+        else if (B.cell16) for (int c = tid; c < nkey; c += THREADS) reinterpret_cast<unsigned short*>(cells_out)[c + 1] = (unsigned short)cells[c];
         else for (int c = tid; c < nkey; c += THREADS) cells_out[c + 1] = cells[c];
         __syncthreads();
     }

@@ -139,10 +139,18 @@ static int plan(chc_ctx* ctx, size_t cells_cap = 49152) {
     const size_t queues = queue_bytes(true, &q1b, &qfb, &q2b);
     // ring phase: float centroids + the list of (cation, ring) / (ring, ring) tasks that pass the centroid prefilter
     const size_t ring_bytes = al16(12 * (size_t)std::max(T.n_rings, 1));
-    const int rlist_cap = T.n_rings <= 128 ? 1024 : 8192;
+    int rlist_cap = T.n_rings <= 128 ? 1024 : 8192;
+    if (const char* e = getenv("CHACRA_RLIST_CAP")) rlist_cap = std::max(4, std::min(rlist_cap, atoi(e)));   // test hook: overflow -> every ring task the slow way
+    // ring task numbers (cation * n_rings + ring, triangular ring pairs) are 32-bit
+    if ((long long)T.n_cat * T.n_rings + (long long)T.n_rings * (T.n_rings - 1) / 2 > 0x7fffffffll) return CHC_E_TOO_LARGE;
     const size_t tables = 2 * al16(4 * (size_t)T.K * T.K) + al16(sizeof(PairMisc)) + ring_bytes + 4 * (size_t)rlist_cap;
     // ~3 cells per pair atom keeps the cells at the cutoff size for protein-like densities
     if (const char* e = getenv("CHACRA_MAX_CELLS")) cells_cap = std::min<size_t>(cells_cap, (size_t)std::max(2048, atoi(e)));   // test hook
+    // systems the gather binning variant takes (more than 8 192 pair atoms) below 65 536 pair atoms: packed 16-bit counters,
+    // twice the cells in the binning kernel's shared memory
+    const bool gather = T.n_pair > 1024 * 8;
+    B.count16 = T.n_pair <= 65535 && (gather || getenv("CHACRA_COUNT16")) && !getenv("CHACRA_COUNT32") ? 1 : 0;
+    if (gather && B.count16 && cells_cap == 49152) cells_cap = 98304;
     size_t want_cells = std::min<size_t>(cells_cap, std::max<size_t>(2048, 3 * (size_t)T.n_pair));
     const size_t plain_bits = al16(4 * (size_t)((ctx->n_pairs + 31) / 32));
     // shared-memory path: the sorted atoms as slot pairs (x0 x1 y0 y1 | z0 z1) + flag word, filter key and residue rank per
@@ -252,7 +260,7 @@ static int plan(chc_ctx* ctx, size_t cells_cap = 49152) {
         G.total = (int)o;
         ctx->fused_ok = (size_t)G.total <= SMEM_LIMIT;
     }
-    ctx->bin_smem = (int)al16(4 * (size_t)B.max_cells);
+    ctx->bin_smem = (int)al16((gather && B.count16 ? 2 : 4) * (size_t)B.max_cells + 16);
     if ((size_t)L.total > SMEM_LIMIT || (size_t)ctx->bin_smem + 1024 > SMEM_LIMIT) return CHC_E_TOO_LARGE;
     return CHC_OK;
 }

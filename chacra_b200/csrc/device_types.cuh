@@ -97,6 +97,7 @@ struct BinLayout {
     int fixed_bytes;                    // header + spos + aux (multiple of 16): one bulk copy
     int max_cells;                      // capacity of the cells section (entries incl. the end sentinel)
     int cell16;                         // cell starts are unsigned 16-bit (records the pair kernel keeps in shared memory)
+    int count16;                        // gather binning variant: packed 16-bit cell counters in shared memory (n_pair < 65 536)
     long long stride;                   // bytes per record
 };
 

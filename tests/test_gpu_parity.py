@@ -158,7 +158,7 @@ def test_tiny_and_odd_sized_systems(tmp_path, oracle_5xnd, first, last):
     res = o.run(top, top, ALL, frames=frames, collect_near=True)
     want, want_near = _oracle_sets(res)
     for env in ({}, {"CHACRA_FORCE_LARGE": "1"}, {"CHACRA_FORCE_LARGE": "1", "CHACRA_STAMPED_SET": "1", "CHACRA_RING_GRID": "1"}, {"CHACRA_BIN_VARIANT": "0"},
-                {"CHACRA_BIN_VARIANT": "4"}):
+                {"CHACRA_BIN_VARIANT": "0", "CHACRA_COUNT16": "1"}, {"CHACRA_BIN_VARIANT": "4"}):
         os.environ.update(env)
         try:
             run = _engine_run(top, frames, ALL)
@@ -399,3 +399,24 @@ def test_fused_kernel_option_matches_oracle(oracle_5xnd, monkeypatch):
         assert run["engine"].stats()["fused"] == 1
         assert run["contacts"] == want and run["near"] == want_near
         _check_counts(run, res)
+
+
+def test_ring_task_list_overflow_falls_back_to_every_task(oracle_5xnd, monkeypatch):
+    """The ring prefilter lists the (cation, ring) / (ring, ring) tasks worth a float64 evaluation; a list that overflows
+    (CHACRA_RLIST_CAP=4 here) must make the kernel evaluate every task instead -- same pc / ps / ts contacts, on the
+    shared-memory path, on the in-place path and on the in-place path with the coarse ring grid."""
+    import getcontacts_oracle as o
+    top = os.path.join(GOLDEN, "5xnd_topology.pdb")
+    frames = oracle_5xnd["frames"]
+    res = o.run(top, top, ALL, frames=frames, collect_near=True)
+    want, want_near = _oracle_sets(res)
+    monkeypatch.setenv("CHACRA_RLIST_CAP", "4")
+    for env in ({}, {"CHACRA_FORCE_LARGE": "1"}, {"CHACRA_FORCE_LARGE": "1", "CHACRA_RING_GRID": "1"}):
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        run = _engine_run(top, frames, ALL)
+        for k in env:
+            monkeypatch.delenv(k)
+        assert run["contacts"] == want and run["near"] == want_near, env
+        _check_counts(run, res)
+
