@@ -266,7 +266,7 @@ static int plan(chc_ctx* ctx, size_t cells_cap = 49152) {
 }
 
 #ifndef CHC_BUILD_TAG
-#define CHC_BUILD_TAG "r02_v5"
+#define CHC_BUILD_TAG "r02_v6"
 #endif
 extern "C" int chc_abi_version(void) { return CHC_ABI_VERSION; }
 extern "C" const char* chc_build_tag(void) { return CHC_BUILD_TAG; }
