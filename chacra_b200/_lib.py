@@ -97,6 +97,8 @@ SYMBOLS = {
     "chc_get_stats": (C.c_int, [vp, C.POINTER(ChcStats)]),
     "chc_set_timing": (C.c_int, [vp, C.c_int]),
     "chc_xtc_decode": (C.c_int, [vp, vp, C.c_int64, C.c_int32, vp, C.c_int64, C.c_int, vp]),
+    "chc_xtc_decode_ws": (C.c_int, [vp, vp, C.c_int64, C.c_int32, vp, C.c_int64, vp, C.c_int64, C.c_int, vp]),
+    "chc_xtc_work_bytes": (C.c_int64, [C.c_int64, C.c_int32]),
     "chc_write_contacts_tsv": (C.c_int64, [C.c_int, vp, C.c_int64, vp, vp, vp, C.c_int32, C.c_int32, vp, vp, vp, C.c_int32, C.c_int64,
                                          C.c_int64, C.c_int32, C.c_int32]),
     "chc_format_fixed3": (C.c_int, [C.c_float, vp]),

@@ -958,27 +958,73 @@ extern "C" int chc_get_stats(chc_ctx* ctx, chc_stats* out) {
 // ---- XTC decode ---------------------------------------------------------------------------------------
 static_assert(sizeof(XtcFrameMeta) == sizeof(chc_xtc_frame) && sizeof(chc_xtc_frame) == 64, "chc_xtc_frame layout");
 
-extern "C" int chc_xtc_decode(const void* d_blob, const chc_xtc_frame* d_meta, int64_t n_frames, int32_t n_atoms, float* d_xyz,
-                              int64_t frame_stride, int device, void* stream_) {
+// bytes of workspace chc_xtc_decode_ws wants to take n_frames in one batch (any smaller multiple of a frame's share works)
+static inline int64_t xtc_work_per_frame(int32_t n_atoms) { return 8 * (int64_t)n_atoms + 8; }
+
+extern "C" int chc_xtc_decode_ws(const void* d_blob, const chc_xtc_frame* d_meta, int64_t n_frames, int32_t n_atoms, float* d_xyz,
+                                 int64_t frame_stride, void* d_work, int64_t work_bytes, int device, void* stream_) {
     if (n_frames == 0) return CHC_OK;
-    if (!d_blob || !d_meta || !d_xyz || n_frames < 0 || n_frames > 0x7fffffff || n_atoms < 1) return CHC_E_INVALID;
-    if (((uintptr_t)d_blob & 3) != 0) return CHC_E_INVALID;
+    if (!d_blob || !d_meta || !d_xyz || !d_work || n_frames < 0 || n_frames > 0x7fffffff || n_atoms < 1) return CHC_E_INVALID;
+    if (((uintptr_t)d_blob & 3) != 0 || ((uintptr_t)d_work & 15) != 0) return CHC_E_INVALID;
     cudaStream_t stream = (cudaStream_t)stream_;
     if (cudaSetDevice(device) != cudaSuccess) return CHC_E_CUDA;
     if (frame_stride == 0) frame_stride = 3 * (int64_t)n_atoms;
-    unsigned* status = nullptr;
-    if (cudaMalloc(&status, 4) != cudaSuccess) return CHC_E_CUDA;
+    // workspace: [status word, padding to 16 bytes][group counts, batch ints][group records, batch x n_atoms x 8 bytes]
+    const int64_t batch = std::min<int64_t>(std::min<int64_t>(n_frames, 65535), (work_bytes - 64) / xtc_work_per_frame(n_atoms));
+    if (batch < 1) return CHC_E_INVALID;
+    unsigned* status = static_cast<unsigned*>(d_work);
+    int* gcount = reinterpret_cast<int*>(static_cast<unsigned char*>(d_work) + 16);
+    unsigned long long* groups = reinterpret_cast<unsigned long long*>(static_cast<unsigned char*>(d_work) + 16 + ((4 * batch + 15) & ~15ll));
     cudaMemsetAsync(status, 0, 4, stream);
-    const char* tenv = getenv("CHACRA_XTC_THREADS");
-    const int threads = tenv ? atoi(tenv) : 32;    // one frame per thread and the chain is serial: spread the warps over the SMs
-    const int blocks = (int)std::min<int64_t>((n_frames + threads - 1) / threads, 148 * 64);
-    xtc_decode_kernel<<<blocks, threads, 0, stream>>>(static_cast<const unsigned*>(d_blob), reinterpret_cast<const XtcFrameMeta*>(d_meta),
-                                                    (int)n_frames, n_atoms, d_xyz, frame_stride, status);
+    if (getenv("CHACRA_XTC_ONEPASS")) {          // test hook: the first decoder (one thread walks and decodes a whole frame)
+        const char* tenv = getenv("CHACRA_XTC_THREADS");
+        const int threads = tenv ? atoi(tenv) : 32;    // one frame per thread and the chain is serial: spread the warps over the SMs
+        const int blocks = (int)std::min<int64_t>((n_frames + threads - 1) / threads, 148 * 64);
+        xtc_decode_kernel<<<blocks, threads, 0, stream>>>(static_cast<const unsigned*>(d_blob), reinterpret_cast<const XtcFrameMeta*>(d_meta),
+                                                        (int)n_frames, n_atoms, d_xyz, frame_stride, status);
+    } else {
+        // two passes (xtc_decode.cuh): group boundaries by one thread per frame, then one thread per group.  The boundary walk is
+        // a serial chain (~1.1 ms for a 6 500-atom frame) however many frames a launch holds, so the frames go in as few batches
+        // as the workspace for the group records allows (8 bytes, at most one per atom).
+        const int gx = std::max(1, std::min((n_atoms + 127) / 128, 64));
+        for (int64_t f0 = 0; f0 < n_frames; f0 += batch) {
+            const int nb = (int)std::min<int64_t>(batch, n_frames - f0);
+            xtc_index_kernel<<<(nb + 31) / 32, 32, 0, stream>>>(static_cast<const unsigned*>(d_blob), reinterpret_cast<const XtcFrameMeta*>(d_meta),
+                                                               (int)f0, nb, n_atoms, d_xyz, frame_stride, groups, gcount, status);
+            xtc_groups_kernel<<<dim3(gx, nb), 128, 0, stream>>>(static_cast<const unsigned*>(d_blob), reinterpret_cast<const XtcFrameMeta*>(d_meta),
+                                                                (int)f0, n_atoms, d_xyz, frame_stride, groups, gcount);
+        }
+    }
     unsigned st = 0;
     cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaMemcpyAsync(&st, status, 4, cudaMemcpyDeviceToHost, stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
-    cudaFree(status);
     if (e != cudaSuccess) return CHC_E_CUDA;
     return st ? CHC_E_INVALID : CHC_OK;
+}
+
+extern "C" int64_t chc_xtc_work_bytes(int64_t n_frames, int32_t n_atoms) {
+    if (n_frames < 1 || n_atoms < 1) return 64;
+    return 64 + std::min<int64_t>(n_frames, 65535) * xtc_work_per_frame(n_atoms) + 16;
+}
+
+extern "C" int chc_xtc_decode(const void* d_blob, const chc_xtc_frame* d_meta, int64_t n_frames, int32_t n_atoms, float* d_xyz,
+                              int64_t frame_stride, int device, void* stream_) {
+    if (n_frames == 0) return CHC_OK;
+    if (n_frames < 0 || n_atoms < 1) return CHC_E_INVALID;
+    if (cudaSetDevice(device) != cudaSuccess) return CHC_E_CUDA;
+    // the workspace for all frames at once, at most 2 GB, halved until it can be had
+    int64_t bytes = std::min<int64_t>(chc_xtc_work_bytes(n_frames, n_atoms), 2048ll << 20);
+    const int64_t least = 64 + xtc_work_per_frame(n_atoms) + 16;
+    void* work = nullptr;
+    for (;;) {
+        bytes = std::max(bytes, least);
+        if (cudaMalloc(&work, (size_t)bytes) == cudaSuccess) break;
+        cudaGetLastError();
+        if (bytes == least) return CHC_E_NOMEM;
+        bytes /= 2;
+    }
+    const int rc = chc_xtc_decode_ws(d_blob, d_meta, n_frames, n_atoms, d_xyz, frame_stride, work, bytes, device, stream_);
+    cudaFree(work);
+    return rc;
 }

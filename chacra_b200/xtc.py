@@ -3,7 +3,7 @@
 ChACRA hands getcontacts ``state_{i}.xtc`` (``chacra/scripts/process_hremd_output.py:147``), which the reference reads
 through VMD's gromacs molfile plugin (``contact_calc/contact_utils.py:89-116``).  Here the host only walks the frame
 headers (52 bytes + 40 bytes of coding parameters per frame); the compressed bit streams go to the device as they are
-and ``chc_xtc_decode`` (``csrc/xtc_decode.cuh``) turns them into float32 [F][N][3] Angstrom, one thread per frame.
+and ``chc_xtc_decode`` (``csrc/xtc_decode.cuh``) turns them into float32 [F][N][3] Angstrom (group boundaries by one thread per frame, then one thread per group).
 There is no CPU decoder on the product path.
 
 Parity note: no XTC fixture, xdrfile source or XTC-capable package exists in the reference tree or in this image, so
@@ -161,7 +161,13 @@ class XTCFile(FileStager):
         d_meta = torch.from_numpy(meta.view(np.uint8).reshape(-1)).to(dev)
         lib = _lib.load()
         stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
-        rc = lib.chc_xtc_decode(d_blob.data_ptr(), d_meta.data_ptr(), len(meta), self.n_atoms, out.data_ptr(), 0, self.device, stream)
+        # workspace of the two-pass decoder (group records), kept between reads: all frames in one batch when 2 GB allow it
+        need = min(int(lib.chc_xtc_work_bytes(len(meta), self.n_atoms)), 2 << 30)
+        work = self.__dict__.get("_work")
+        if work is None or work.numel() < need or work.device != dev:
+            work = self._work = torch.empty(need, dtype=torch.uint8, device=dev)
+        rc = lib.chc_xtc_decode_ws(d_blob.data_ptr(), d_meta.data_ptr(), len(meta), self.n_atoms, out.data_ptr(), 0, work.data_ptr(),
+                                   work.numel(), self.device, stream)
         if rc != 0:
             raise ValueError("%s: XTC bit stream inconsistent with %d atoms (chc_xtc_decode returned %d)" % (self.path, self.n_atoms, rc))
         self.last_timing = (t_host, time.perf_counter() - t1)   # (waiting for file -> pinned, rest of H2D + decode) seconds

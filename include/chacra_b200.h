@@ -245,6 +245,15 @@ typedef struct chc_xtc_frame {
  * stream; CHC_E_INVALID when a bit stream is inconsistent with n_atoms. */
 int chc_xtc_decode(const void* d_blob, const chc_xtc_frame* d_meta, int64_t n_frames, int32_t n_atoms, float* d_xyz,
                    int64_t frame_stride, int device, void* stream);
+/* The same with a caller-owned workspace (DEVICE, 16-byte aligned; no allocation inside): the decoder runs in two passes --
+ * group boundaries of every frame by one thread per frame, then one thread per group -- and keeps 8 bytes per group (at most one
+ * group per atom) between them.  chc_xtc_work_bytes(n_frames, n_atoms) is the size that takes all frames in one batch; a smaller
+ * workspace (at least chc_xtc_work_bytes(1, n_atoms)) makes the call go through the frames in several batches, each of which
+ * costs the serial boundary walk of one frame (about 1 ms for 6 500 atoms) again.  chc_xtc_decode allocates and frees such a
+ * workspace itself (at most 2 GB). */
+int     chc_xtc_decode_ws(const void* d_blob, const chc_xtc_frame* d_meta, int64_t n_frames, int32_t n_atoms, float* d_xyz,
+                          int64_t frame_stride, void* d_work, int64_t work_bytes, int device, void* stream);
+int64_t chc_xtc_work_bytes(int64_t n_frames, int32_t n_atoms);
 
 /* Contact-list TSV writer (host code, no GPU work; replaces contact_consumer, gc/contact_calc/compute_contacts.py:306-359).
  * rec[n]: records from chc_drain_contacts covering WHOLE frames (reordered in place).  Labels: atom a's text is

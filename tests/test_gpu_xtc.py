@@ -27,7 +27,7 @@ def _write_int_frames(path, frames_ints, precision=1000.0, **kw):
 
 
 @pytest.mark.parametrize("wide", [False, True])
-def test_decoder_matches_oracle_on_every_stream_feature(tmp_path, wide):
+def test_decoder_matches_oracle_on_every_stream_feature(tmp_path, wide, monkeypatch):
     """Random walks with jumps (runs of every length, both radix directions, flag-0 repeats); `wide`: one axis spans
     more than 2^24 grid steps, so the large integers are three separate bit fields instead of one packed number
     (also exercises packed numbers of more than 64 bits when narrow axes are still large)."""
@@ -61,6 +61,9 @@ def test_decoder_matches_oracle_on_every_stream_feature(tmp_path, wide):
     x.CHUNK_BYTES = 20000
     assert np.array_equal(x.read(), want)
     assert np.array_equal(x.read(1, 35, 3), want[1:36:3])
+    # the first decoder (one thread walks and decodes a whole frame) is kept behind a switch: same bits
+    monkeypatch.setenv("CHACRA_XTC_ONEPASS", "1")
+    assert np.array_equal(XTCFile(path).read(), want)
 
 
 def test_small_raw_frames_and_corrupt_streams(tmp_path):
@@ -134,3 +137,39 @@ def test_random_corruption_never_faults(tmp_path):
             outcomes["rejected"] += 1
     assert outcomes["decoded"] + outcomes["rejected"] == 60 and outcomes["rejected"] > 0
     assert np.array_equal(XTCFile(good).read(), want)
+
+
+def test_workspace_sizes_and_the_allocating_entry_point(tmp_path):
+    """chc_xtc_decode_ws with a workspace for all frames, with one that holds three frames (several batches) and with one that is too
+    small, and chc_xtc_decode (which allocates its own): same coordinates, bit for bit."""
+    import ctypes as C
+    import torch
+    from chacra_b200 import _lib
+    from chacra_b200.xtc import XTCFile, _SLACK
+    rng = np.random.default_rng(5)
+    n = 411
+    frames = [np.cumsum(rng.integers(-140, 140, (n, 3)), 0) + rng.integers(-2000, 2000, 3) for _ in range(11)]
+    path = str(tmp_path / "w.xtc")
+    _write_int_frames(path, frames, adapt=True)
+    x = XTCFile(path)
+    want = np.stack([xo.ints_to_angstrom(i) for i in frames])
+    assert np.array_equal(x.read(), want)
+    lib = _lib.load()
+    dev = torch.device("cuda", 0)
+    meta, used = x._stage(np.arange(x.n_frames), 0)
+    d_blob = x._stage_bufs[0][:used + _SLACK].to(dev)
+    d_meta = torch.from_numpy(meta.view(np.uint8).reshape(-1)).to(dev)
+    stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    full = int(lib.chc_xtc_work_bytes(x.n_frames, n))
+    three = 64 + 3 * (8 * n + 8) + 16
+    assert full >= 64 + x.n_frames * (8 * n + 8)
+    for bytes_ in (full, three):
+        out = torch.zeros((x.n_frames, n, 3), dtype=torch.float32, device=dev)
+        work = torch.empty(bytes_, dtype=torch.uint8, device=dev)
+        assert lib.chc_xtc_decode_ws(d_blob.data_ptr(), d_meta.data_ptr(), x.n_frames, n, out.data_ptr(), 0, work.data_ptr(), bytes_, 0, stream) == 0
+        assert np.array_equal(out.cpu().numpy(), want)
+    small = torch.empty(64 + 8 * n, dtype=torch.uint8, device=dev)           # not even one frame's share
+    out = torch.zeros((x.n_frames, n, 3), dtype=torch.float32, device=dev)
+    assert lib.chc_xtc_decode_ws(d_blob.data_ptr(), d_meta.data_ptr(), x.n_frames, n, out.data_ptr(), 0, small.data_ptr(), small.numel(), 0, stream) == -1
+    assert lib.chc_xtc_decode(d_blob.data_ptr(), d_meta.data_ptr(), x.n_frames, n, out.data_ptr(), 0, 0, stream) == 0
+    assert np.array_equal(out.cpu().numpy(), want)
