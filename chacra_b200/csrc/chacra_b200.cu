@@ -265,6 +265,8 @@ static int plan(chc_ctx* ctx, size_t cells_cap = 49152) {
     return CHC_OK;
 }
 
+// names the build of the contact kernels (bin_kernel.cuh, bin_tma_kernel.cuh, pair_kernel.cuh, frame_*.cuh, water_phase.cuh, plan()):
+// bump it with every change to those, and re-capture profiles/ncu_traffic.json (tools/ncu_traffic.py)
 #ifndef CHC_BUILD_TAG
 #define CHC_BUILD_TAG "r02_v6"
 #endif

@@ -190,8 +190,9 @@ typedef struct chc_stats {
 typedef struct chc_ctx chc_ctx;
 
 int  chc_abi_version(void);
-/* Name of this build of the kernels (CHC_BUILD_TAG in chacra_b200.cu); profiles/ncu summaries quote it so that a measured
- * DRAM-traffic figure is only ever attached to the build it was captured from. */
+/* Name of this build of the CONTACT kernels (CHC_BUILD_TAG in chacra_b200.cu: bumped whenever the binning / pair kernels or their
+ * launch plan change); profiles/ncu summaries quote it so that a measured DRAM-traffic figure is only ever attached to the build
+ * of those kernels it was captured from. */
 const char* chc_build_tag(void);
 int  chc_create(chc_ctx** out, const chc_topology* topo, const chc_params* params, int device);
 void chc_destroy(chc_ctx* ctx);
