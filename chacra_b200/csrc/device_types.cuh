@@ -107,12 +107,6 @@ __device__ __forceinline__ float dist2_exact(float ax, float ay, float az, float
     return (dx * dx + dy * dy) + dz * dz;
 }
 
-// superset prefilter only: two fused multiply-adds (|error| <= a few ulp of d2); never decides a contact by itself
-__device__ __forceinline__ float dist2_fused(float ax, float ay, float az, float bx, float by, float bz) {
-    const float dx = ax - bx, dy = ay - by, dz = az - bz;
-    return __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
-}
-
 __device__ __forceinline__ long long pair_index(int ra, int rb, int R) {
     int lo = min(ra, rb), hi = max(ra, rb);
     return (long long)lo * R - ((long long)lo * (lo - 1)) / 2 + (hi - lo);
