@@ -84,7 +84,8 @@ def cpu_twin_rate(pdb_path, xyz0, frames, min_seconds=10.0, threads=None):
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import cpu_twin
     tw = cpu_twin.Twin(pdb_path, xyz0=xyz0, itypes=ITYPES)
-    cores = threads or cpu_twin.load().gc_threads()
+    # every core this process may run on: torchrun exports OMP_NUM_THREADS=1 to its workers, which is not what "all host cores" means
+    cores = threads or max(cpu_twin.load().gc_threads(), len(os.sched_getaffinity(0)))
     tw.run(frames[:max(1, min(len(frames), 4 * cores))], want_contacts=False, threads=cores)      # warm-up (page in, thread pool)
     done, t0 = 0, time.perf_counter()
     while True:

@@ -363,6 +363,10 @@ extern "C" int gc_run(const gc_topo* Tp, const gc_params* Pp, const float* xyz, 
     std::vector<std::vector<uint8_t>> hp(n_frag);
     std::vector<char> hp_on(n_frag, 0);
     const int threads = P.threads > 0 ? P.threads : gc_threads();
+#ifdef _OPENMP
+    // an explicit thread count wins over the environment (torchrun exports OMP_NUM_THREADS=1 to its workers)
+    if (P.threads > 0) { omp_set_dynamic(0); omp_set_num_threads(threads); }
+#endif
     if (hp_wanted) {
 #pragma omp parallel for schedule(dynamic, 1) num_threads(threads)
         for (int64_t k = 0; k < n_frag; ++k) {
