@@ -219,6 +219,85 @@ def extra_config(name, copies, n_states, sample_frames, dev, world, dist, torch)
     return out
 
 
+def xtc_e2e(eng, work, N, dev, torch, merge, steps, barrier):
+    """The same job fed the way ChACRA feeds getcontacts -- state_{i}.xtc -- with the compressed frames already in pinned host memory:
+    per state the XTC bit streams cross PCIe (0.34 of the float32 bytes), are decoded on the GPU (chc_xtc_decode_ws) and go through
+    the contact kernels; counts come back at the end of the step.  The streams are tests/golden/bench_c2_24frames.xtc tiled to the
+    state's length (tests/golden/make_bench_xtc.py); copy + decode of state k+1 run on a second stream under the contacts of state k."""
+    import ctypes as C
+    import numpy as np
+    from chacra_b200 import _lib
+    from chacra_b200.xtc import XTCFile, _SLACK
+    fx = os.path.join(GOLDEN, "bench_c2_24frames.xtc")
+    x = XTCFile(fx, device=dev.index)
+    if x.n_atoms != N:
+        return {"skipped": "fixture holds %d atoms, job has %d" % (x.n_atoms, N)}
+    lib = _lib.load()
+    raw = np.fromfile(fx, dtype=np.uint8)
+    span = raw.shape[0]
+    longest = max(c for _, _, c in work)
+    reps = (longest + x.n_frames - 1) // x.n_frames
+    host = torch.empty(reps * span + _SLACK, dtype=torch.uint8, pin_memory=True)
+    hv = host.numpy()
+    for r in range(reps):
+        hv[r * span:(r + 1) * span] = raw
+    hv[reps * span:] = 0
+    meta = np.tile(x._index, reps)
+    meta["offset"] += np.repeat(np.arange(reps, dtype=np.int64) * span, x.n_frames)
+    meta = meta[:longest]
+    d_meta = torch.from_numpy(meta.view(np.uint8).reshape(-1).copy()).to(dev)
+    ends = (meta["offset"] + ((meta["nbytes"].astype(np.int64) + 3) & ~3))          # bytes of the blob that hold frames [0, cnt)
+    d_blob = [torch.empty(host.numel(), dtype=torch.uint8, device=dev) for _ in range(2)]
+    d_xyz = [torch.empty((longest, N, 3), dtype=torch.float32, device=dev) for _ in range(2)]
+    wbytes = int(lib.chc_xtc_work_bytes(longest, N))
+    d_work = [torch.empty(wbytes, dtype=torch.uint8, device=dev) for _ in range(2)]
+    side = [torch.cuda.Stream(dev), torch.cuda.Stream(dev)]
+    used = [torch.cuda.Event(), torch.cuda.Event()]                               # contacts that read d_xyz[k] have run
+    main = torch.cuda.current_stream(dev)
+    h2d = 0
+
+    def copy_in(k):
+        nonlocal h2d
+        cnt = work[k][2]
+        nbytes = int(ends[cnt - 1]) + _SLACK
+        with torch.cuda.stream(side[k & 1]):
+            side[k & 1].wait_event(used[k & 1])
+            d_blob[k & 1][:nbytes].copy_(host[:nbytes], non_blocking=True)
+        h2d += nbytes
+
+    def step():
+        eng.reset_counts()
+        for e in used:
+            e.record(main)
+        if work:
+            copy_in(0)
+        for k, (s_, first, cnt) in enumerate(work):
+            if k + 1 < len(work):
+                copy_in(k + 1)
+            rc = lib.chc_xtc_decode_ws(d_blob[k & 1].data_ptr(), d_meta.data_ptr(), cnt, N, d_xyz[k & 1].data_ptr(), 0, d_work[k & 1].data_ptr(),
+                                       wbytes, dev.index, C.c_void_p(side[k & 1].cuda_stream))          # returns when the frames are decoded
+            if rc != 0:
+                raise RuntimeError("chc_xtc_decode_ws returned %d" % rc)
+            eng.submit(d_xyz[k & 1][:cnt], s_, first)
+            used[k & 1].record(main)
+        merge(eng.counts_tensor)
+        return eng.counts_tensor.cpu()
+
+    table = step()
+    # tiling sanity: the first frames decode to what the reader gives for the file itself
+    if work and work[0][2] >= x.n_frames:
+        assert torch.equal(d_xyz[0][:x.n_frames], x.read_device()), "tiled XTC blob decodes differently from the file"
+    h2d = 0
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        table = step()
+    barrier()
+    dt = time.perf_counter() - t0
+    return {"seconds": dt, "steps": steps, "h2d_bytes_per_step_rank0": h2d // max(1, steps), "pair_frames_rank0": int(table.sum()),
+            "what": "XTC bit streams in pinned host memory -> H2D -> chc_xtc_decode_ws -> contact kernels -> counts D2H (per rank: its share of the job)"}
+
+
 def cli_rates(path, atoms, torch, dev):
     """The path ChACRA really runs (process_hremd_output.py:139-175): state DCD -> contact-list TSV (--distout) -> frequency TSV
     through the drop-in scripts, and the counts-only variant (--no_contact_output --frequency_output), on 2 000 frames."""
@@ -407,6 +486,19 @@ def main():
     # ---- near-cutoff channel: 1 000 frames of state 0 through the near-tracking instantiation (outside the timed region) ----
     near = None
     extras = {}
+    if not args.no_extras:
+        try:
+            r = xtc_e2e(eng, work, N, dev, torch, merge_count_tables, args.e2e_steps, barrier)
+            if "seconds" in r:
+                secs = r.pop("seconds")
+                if world > 1:
+                    t = torch.tensor([secs], device=dev)
+                    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                    secs = float(t.item())
+                r.update(value=args.e2e_steps * frames_per_step / secs, unit="frames/s")
+            extras["e2e_xtc"] = r
+        except Exception as exc:                         # never lose the main line to an extra
+            extras["e2e_xtc"] = {"error": "%s: %s" % (type(exc).__name__, exc)}
     if rank == 0 and not args.no_extras:
         ne = ContactEngine(topo, ITYPES, n_states=1, track_near=True, near_capacity=1 << 20, device=local)
         xs = FrameGenerator(atoms.xyz, 2000, amplitude=state_amplitude(0, S), device=dev).frames(1000)
