@@ -326,14 +326,15 @@ def cli_rates(path, atoms, torch, dev):
                                        "--frequency_output", os.path.join(tmp, "freqs_direct_0.tsv")])
             t3 = time.perf_counter()
             rates = (out.get("passes") or []) + [n / (t2 - t0)]
-            if out and n / (t2 - t0) < out["value"]:      # 350 MB of text per pass: the box's write-back throttling makes single passes noisy
-                out["passes"] = rates
-                continue
-            out = {"frames": n, "value": n / (t2 - t0), "passes": rates, "unit": "frames/s", "contacts_s": t1 - t0, "frequencies_s": t2 - t1,
-                   "tsv_bytes": os.path.getsize(os.path.join(tmp, "cont_state_0.tsv")),
-                   "what": "get_dynamic_contacts.py --itypes all --distout (DCD in, contact TSV out) + get_contact_frequencies.py, argv to files",
-                   "counts_only": {"value": n / (t3 - t2), "unit": "frames/s",
-                                   "what": "get_dynamic_contacts.py --no_contact_output --frequency_output (DCD in, frequency TSV out)"}}
+            crates = (out.get("counts_only", {}).get("passes") or []) + [n / (t3 - t2)]
+            # 350 MB of text per pass: the box's write-back throttling makes single passes noisy -- best of the passes, all listed
+            if not out or n / (t2 - t0) > out["value"]:
+                out.update({"frames": n, "value": n / (t2 - t0), "unit": "frames/s", "contacts_s": t1 - t0, "frequencies_s": t2 - t1,
+                            "tsv_bytes": os.path.getsize(os.path.join(tmp, "cont_state_0.tsv")),
+                            "what": "get_dynamic_contacts.py --itypes all --distout (DCD in, contact TSV out) + get_contact_frequencies.py, argv to files"})
+            out["passes"] = rates
+            out["counts_only"] = {"value": max(crates), "passes": crates, "unit": "frames/s",
+                                  "what": "get_dynamic_contacts.py --no_contact_output --frequency_output (DCD in, frequency TSV out)"}
     finally:
         os.dup2(saved, 1)
         os.close(saved)
